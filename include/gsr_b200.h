@@ -1,0 +1,162 @@
+/*
+ * gsr_b200.h -- C ABI of the B200-native Gaussian-splatting rasterizer (libgsr_b200.so).
+ *
+ * This is the drop-in boundary for SCORP's rasterizer hot path. Every entry point takes
+ * plain device pointers, sizes and a CUDA stream handle (passed as void*); there are no
+ * torch or C++ types in any signature. All pointers are DEVICE pointers owned by the
+ * caller unless marked "host". The library allocates no device memory: scratch that must
+ * survive until the backward pass is obtained through a caller-supplied allocator callback
+ * (the same shape as the reference's std::function<char*(size_t)> resize lambdas,
+ * reference submodules/diff-gaussian-rasterization/rasterize_points.cu:27-33,75-80).
+ *
+ * Return value: 0 on success, a negative GSR_E* code otherwise; gsr_last_error() returns a
+ * host string describing the last failure on the calling thread. No exception crosses the ABI.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/submodules):
+ *   gsr_rasterize_forward   <- CudaRasterizer::Rasterizer::forward
+ *                              diff-gaussian-rasterization/cuda_rasterizer/rasterizer.h:29-55
+ *                              (called from RasterizeGaussiansCUDA, rasterize_points.cu:36-119)
+ *   gsr_rasterize_backward  <- CudaRasterizer::Rasterizer::backward, rasterizer.h:57-92
+ *                              (RasterizeGaussiansBackwardCUDA, rasterize_points.cu:122-208)
+ *   gsr_mark_visible        <- CudaRasterizer::Rasterizer::markVisible, rasterizer.h:22-27
+ *                              (markVisible, rasterize_points.cu:210-229)
+ *   gsr_surfel_forward      <- diff-surfel-rasterization/cuda_rasterizer/rasterizer.h:29-54
+ *   gsr_surfel_backward     <- diff-surfel-rasterization/cuda_rasterizer/rasterizer.h:56-88
+ *   gsr_knn_dist2           <- SimpleKNN::knn, simple-knn/simple_knn.h:15-19
+ *                              (distCUDA2, simple-knn/spatial.cu:15-26)
+ */
+#ifndef GSR_B200_H_INCLUDED
+#define GSR_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_OK            0
+#define GSR_EINVAL       -1   /* bad argument (null pointer, negative size, ...)        */
+#define GSR_ECUDA        -2   /* a CUDA runtime call or kernel launch failed            */
+#define GSR_EALLOC       -3   /* the allocator callback returned NULL / too little      */
+#define GSR_EUNSUPPORTED -4   /* e.g. SH coefficient count other than 0,1,4,9,16        */
+
+/* Scratch buffers requested through the allocator callback. */
+#define GSR_BUF_GEOM    0     /* per-Gaussian state, kept for backward                  */
+#define GSR_BUF_BINNING 1     /* per-instance sorted lists, kept for backward           */
+#define GSR_BUF_IMAGE   2     /* per-pixel / per-tile state, kept for backward          */
+
+/* Must return a device pointer to at least `bytes` bytes, 256-byte aligned, that stays
+ * valid until the matching backward has run. Called on the calling host thread. */
+typedef void* (*gsr_alloc_fn)(void* user, int which, size_t bytes);
+
+/* Mirrors GaussianRasterizationSettings (diff_gaussian_rasterization/__init__.py:160-172).
+ * bg[3], viewmatrix[16], projmatrix[16], campos[3] are DEVICE pointers (the reference keeps
+ * them as CUDA tensors); matrices are the transposed, column-major-indexed 4x4s of
+ * gs3dgs/scene/cameras.py:82-97. */
+typedef struct GsrSettings {
+    int32_t image_height;
+    int32_t image_width;
+    float   tanfovx;
+    float   tanfovy;
+    float   scale_modifier;
+    int32_t sh_degree;
+    int32_t prefiltered;
+    int32_t debug;          /* !=0: synchronise + check after every stage (auxiliary.h:166-173) */
+    const float* bg;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* campos;
+} GsrSettings;
+
+const char* gsr_last_error(void);
+int         gsr_version(void);
+
+/* ---- 3DGS (diff_gaussian_rasterization) ------------------------------------------------
+ * P Gaussians, M SH coefficients per Gaussian (0 when colors_precomp is given).
+ * Optional inputs are NULL when absent (the reference's 0-element tensor sentinel):
+ *   exactly one of shs[P*M*3] / colors_precomp[P*3];
+ *   exactly one of (scales[P*3], rotations[P*4]) / cov3D_precomp[P*6].
+ * Outputs: out_color[3*H*W], out_depth[H*W], out_alpha[H*W], radii[P] (int32).
+ * *num_rendered (host) receives the number of (Gaussian, tile) instances. */
+int gsr_rasterize_forward(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations,
+    const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream);
+
+/* Workspace for the backward pass (per-Gaussian gradient accumulators); the caller passes a
+ * device buffer of this many bytes. It need not be zeroed. */
+size_t gsr_backward_workspace_bytes(int P);
+
+/* R = num_rendered from the forward. geom/binning/image are the buffers the forward obtained
+ * through `alloc` (read-only here: backward may run several times per forward).
+ * Every dL_d* output is fully written (zeros for invisible Gaussians): no pre-zeroing needed.
+ * Shapes: dL_dmeans2D[P*3], dL_dcolors[P*3], dL_dopacity[P], dL_dmeans3D[P*3],
+ * dL_dcov3D[P*6], dL_dsh[P*M*3], dL_dscales[P*3], dL_drotations[P*4]. */
+int gsr_rasterize_backward(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream);
+
+/* present[P] (1 byte each) = view-space z > 0.2 */
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* ---- introspection of the private scratch layout (tests, golden-vector comparison) ------
+ * Byte offsets from the (256-byte aligned) base of each buffer. Index meaning:
+ * geom:    0 rec (P x 48 B: xy, conic, opacity, depth, power threshold, rgb), 1 cov3D (6P f32),
+ *          2 clamped (P u8, bit c = channel c clamped), 3 tiles_touched (P u32),
+ *          4 tile_count (tiles u32), 5 counters (4 u32: [0] = num_rendered)
+ * image:   0 ranges (tiles x uint2), 1 n_contrib (W*H u32)
+ * binning: 0 point_list (N u32), 1 point_list_keys (N u64), 2 sort scratch (N u64) */
+void gsr_geom_layout(int P, int tiles, size_t off[6], size_t* total);
+void gsr_image_layout(int W, int H, size_t off[2], size_t* total);
+void gsr_binning_layout(int N, size_t off[3], size_t* total);
+
+/* ---- 2DGS surfels (diff_surfel_rasterization) ------------------------------------------
+ * scales[P*2]; transMat_precomp[P*9] replaces cov3D_precomp; out_others[7*H*W] with channels
+ * depth 0, alpha 1, normal 2-4, median depth 5, distortion 6 (auxiliary.h:23-27). */
+int gsr_surfel_forward(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations,
+    const float* transMat_precomp,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream);
+
+size_t gsr_surfel_backward_workspace_bytes(int P);
+
+int gsr_surfel_backward(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* transMat_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* dL_dout_color, const float* dL_dout_others,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dtransMat, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream);
+
+void gsr_surfel_geom_layout(int P, int tiles, size_t off[6], size_t* total);
+void gsr_surfel_image_layout(int W, int H, size_t off[4], size_t* total);
+
+/* ---- simple_knn.distCUDA2 ---------------------------------------------------------------
+ * out[P] = mean squared distance to the 3 nearest other points. tmp: device scratch of
+ * gsr_knn_workspace_bytes(P) bytes. */
+size_t gsr_knn_workspace_bytes(int P);
+int gsr_knn_dist2(int P, const float* xyz, float* out, void* tmp, size_t tmp_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_B200_H_INCLUDED */

@@ -1,0 +1,110 @@
+// oracle/ref_shim_dgr.cu -- TEST INFRASTRUCTURE, not product code.
+//
+// A C-ABI wrapper (written for this repo) around the UNMODIFIED reference 3DGS
+// rasterizer library, compiled from the sources where they lie under
+// /root/reference/submodules/diff-gaussian-rasterization/cuda_rasterizer/.
+// It lets tests and bench.py drive CudaRasterizer::Rasterizer::{forward,backward,
+// markVisible} (reference rasterizer.h:19-86) from Python/ctypes without the torch
+// glue, and exposes the private scratch layout (rasterizer_impl.h:23-73) so the
+// golden-vector dumper can slice intermediates out of the three byte buffers.
+//
+// Nothing here is linked into, imported by or called from scorp_b200/.
+#include <cstddef>
+#include <cstdint>
+#include <functional>
+#include <stdexcept>
+#include <cuda_runtime.h>
+#include "cuda_rasterizer/rasterizer.h"
+#include "cuda_rasterizer/rasterizer_impl.h"
+
+extern "C" {
+
+// which: 0 = geometry, 1 = binning, 2 = image. Returns a device pointer of >= bytes.
+typedef char* (*ref_alloc_fn)(void* ctx, int which, size_t bytes);
+
+int ref_dgr_forward(ref_alloc_fn alloc, void* ctx,
+                    int P, int D, int M, const float* background, int width, int height,
+                    const float* means3D, const float* shs, const float* colors_precomp,
+                    const float* opacities, const float* scales, float scale_modifier,
+                    const float* rotations, const float* cov3D_precomp,
+                    const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                    float tan_fovx, float tan_fovy, int prefiltered,
+                    float* out_color, float* out_depth, float* out_alpha, int* radii, int debug)
+{
+    try {
+        return CudaRasterizer::Rasterizer::forward(
+            [=](size_t n) { return alloc(ctx, 0, n); },
+            [=](size_t n) { return alloc(ctx, 1, n); },
+            [=](size_t n) { return alloc(ctx, 2, n); },
+            P, D, M, background, width, height, means3D, shs, colors_precomp, opacities,
+            scales, scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, cam_pos,
+            tan_fovx, tan_fovy, prefiltered != 0, out_color, out_depth, out_alpha, radii, debug != 0);
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
+
+int ref_dgr_backward(int P, int D, int M, int R, const float* background, int width, int height,
+                     const float* means3D, const float* shs, const float* colors_precomp,
+                     const float* alphas, const float* scales, float scale_modifier,
+                     const float* rotations, const float* cov3D_precomp,
+                     const float* viewmatrix, const float* projmatrix, const float* campos,
+                     float tan_fovx, float tan_fovy, const int* radii,
+                     char* geom_buffer, char* binning_buffer, char* image_buffer,
+                     const float* dL_dpix, const float* dL_dpix_depth, const float* dL_dalphas,
+                     float* dL_dmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                     float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D, float* dL_dsh,
+                     float* dL_dscale, float* dL_drot, int debug)
+{
+    try {
+        CudaRasterizer::Rasterizer::backward(
+            P, D, M, R, background, width, height, means3D, shs, colors_precomp, alphas, scales,
+            scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx,
+            tan_fovy, radii, geom_buffer, binning_buffer, image_buffer, dL_dpix, dL_dpix_depth,
+            dL_dalphas, dL_dmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth, dL_dmean3D,
+            dL_dcov3D, dL_dsh, dL_dscale, dL_drot, debug != 0);
+        return 0;
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
+
+void ref_dgr_mark_visible(int P, float* means3D, float* viewmatrix, float* projmatrix, unsigned char* present)
+{
+    CudaRasterizer::Rasterizer::markVisible(P, means3D, viewmatrix, projmatrix, (bool*)present);
+}
+
+// Byte offsets of every sub-array inside the three scratch buffers, relative to a
+// 128-byte aligned base, in the carve order of rasterizer_impl.cu:155-193.
+// geom[10]: depths, clamped, internal_radii, means2D, cov3D, conic_opacity, rgb,
+//           tiles_touched, scanning_space, point_offsets
+void ref_dgr_geom_layout(size_t P, size_t* off, size_t* total)
+{
+    char* chunk = nullptr;
+    auto g = CudaRasterizer::GeometryState::fromChunk(chunk, P);
+    off[0] = (size_t)g.depths; off[1] = (size_t)g.clamped; off[2] = (size_t)g.internal_radii;
+    off[3] = (size_t)g.means2D; off[4] = (size_t)g.cov3D; off[5] = (size_t)g.conic_opacity;
+    off[6] = (size_t)g.rgb; off[7] = (size_t)g.tiles_touched; off[8] = (size_t)g.scanning_space;
+    off[9] = (size_t)g.point_offsets;
+    *total = (size_t)chunk;
+}
+// img[2]: n_contrib, ranges
+void ref_dgr_image_layout(size_t N, size_t* off, size_t* total)
+{
+    char* chunk = nullptr;
+    auto s = CudaRasterizer::ImageState::fromChunk(chunk, N);
+    off[0] = (size_t)s.n_contrib; off[1] = (size_t)s.ranges;
+    *total = (size_t)chunk;
+}
+// bin[5]: point_list, point_list_unsorted, point_list_keys, point_list_keys_unsorted, sort temp
+void ref_dgr_binning_layout(size_t N, size_t* off, size_t* total)
+{
+    char* chunk = nullptr;
+    auto b = CudaRasterizer::BinningState::fromChunk(chunk, N);
+    off[0] = (size_t)b.point_list; off[1] = (size_t)b.point_list_unsorted;
+    off[2] = (size_t)b.point_list_keys; off[3] = (size_t)b.point_list_keys_unsorted;
+    off[4] = (size_t)b.list_sorting_space;
+    *total = (size_t)chunk;
+}
+
+}  // extern "C"

@@ -1,0 +1,178 @@
+// api.cu -- extern "C" entry points of libgsr_b200.so (3DGS path, markVisible, layouts).
+// Orchestration mirrors CudaRasterizer::Rasterizer::forward/backward
+// (reference rasterizer_impl.cu:197-339, :343-446) with the stages of this library.
+#include "common.cuh"
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace gsr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return GSR_OK;
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return GSR_ECUDA;
+}
+// debug mode: synchronise and surface asynchronous errors after each stage (auxiliary.h:166-173)
+int stage_check(const GsrSettings* s, cudaStream_t st, const char* what) {
+    if (!s->debug) return GSR_OK;
+    return check_cuda(cudaStreamSynchronize(st), what);
+}
+
+static bool sh_count_ok(int M) { return M == 0 || M == 1 || M == 4 || M == 9 || M == 16; }
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" {
+
+const char* gsr_last_error(void) { return g_err; }
+int gsr_version(void) { return 100; }
+
+void gsr_geom_layout(int P, int tiles, size_t off[6], size_t* total) { *total = carve_geom(nullptr, P, tiles, nullptr, off); }
+void gsr_image_layout(int W, int H, size_t off[2], size_t* total) { *total = carve_image(nullptr, W, H, nullptr, off); }
+void gsr_binning_layout(int N, size_t off[3], size_t* total) { *total = carve_binning(nullptr, N, nullptr, off); }
+
+size_t gsr_backward_workspace_bytes(int P) { return align_up((size_t)(P > 0 ? P : 1) * ACC_STRIDE * sizeof(float)); }
+
+int gsr_rasterize_forward(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
+    *num_rendered = 0;
+    const int W = s->image_width, H = s->image_height;
+    if (P < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d W=%d H=%d", P, W, H); return GSR_EINVAL; }
+    if (!out_color || !out_depth || !out_alpha) { set_error("null output image"); return GSR_EINVAL; }
+    const size_t hw = (size_t)W * H;
+    int rc;
+    if (P == 0) {   // rasterize_points.cu:83: zero outputs, nothing else
+        if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, 3 * hw * 4, st), "memset color"))) return rc;
+        if ((rc = check_cuda(cudaMemsetAsync(out_depth, 0, hw * 4, st), "memset depth"))) return rc;
+        return check_cuda(cudaMemsetAsync(out_alpha, 0, hw * 4, st), "memset alpha");
+    }
+    if (!means3D || !opacities || !radii || !s->bg || !s->viewmatrix || !s->projmatrix || !s->campos) {
+        set_error("null required input"); return GSR_EINVAL;
+    }
+    if ((shs == nullptr) == (colors_precomp == nullptr)) { set_error("provide exactly one of shs / colors_precomp"); return GSR_EINVAL; }
+    if (((scales == nullptr) || (rotations == nullptr)) == (cov3D_precomp == nullptr)) {
+        set_error("provide exactly one of scales+rotations / cov3D_precomp"); return GSR_EINVAL;
+    }
+    if (shs && (!sh_count_ok(M) || M == 0 || (s->sh_degree + 1) * (s->sh_degree + 1) > M || s->sh_degree < 0 || s->sh_degree > 3)) {
+        set_error("unsupported SH layout: M=%d degree=%d", M, s->sh_degree); return GSR_EUNSUPPORTED;
+    }
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, tiles = gx * gy;
+
+    GeomState g; ImageState img; BinningState bin;
+    char* gbase = (char*)alloc(alloc_user, GSR_BUF_GEOM, carve_geom(nullptr, P, tiles, nullptr));
+    char* ibase = (char*)alloc(alloc_user, GSR_BUF_IMAGE, carve_image(nullptr, W, H, nullptr));
+    if (!gbase || !ibase) { set_error("allocator returned NULL"); return GSR_EALLOC; }
+    carve_geom(gbase, P, tiles, &g);
+    carve_image(ibase, W, H, &img);
+
+    // tile_count and counters are adjacent at the end of the geometry buffer: one memset
+    const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + 16;
+    if ((rc = check_cuda(cudaMemsetAsync(g.tile_count, 0, zero_bytes, st), "memset tile counters"))) return rc;
+
+    FwdArgs a;
+    a.P = P; a.M = shs ? M : 0; a.D = s->sh_degree; a.W = W; a.H = H; a.gx = gx; a.gy = gy;
+    a.tanfovx = s->tanfovx; a.tanfovy = s->tanfovy;
+    a.focal_y = H / (2.0f * s->tanfovy); a.focal_x = W / (2.0f * s->tanfovx);     // rasterizer_impl.cu:224-225
+    a.scale_modifier = s->scale_modifier;
+    a.means3D = means3D; a.shs = shs; a.colors_precomp = colors_precomp; a.opacities = opacities;
+    a.scales = scales; a.rotations = rotations; a.cov3D_precomp = cov3D_precomp;
+    a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos; a.bg = s->bg;
+    a.prefiltered = s->prefiltered != 0;
+    if ((rc = check_cuda(launch_preprocess(a, g, radii, st), "preprocess launch"))) return rc;
+    if ((rc = stage_check(s, st, "preprocess"))) return rc;
+
+    // number of instances -> host (the one blocking point, as rasterizer_impl.cu:282)
+    uint32_t n_host = 0;
+    if ((rc = check_cuda(cudaMemcpyAsync(&n_host, g.counters, 4, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
+    if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
+    const int N = (int)n_host;
+    *num_rendered = N;
+
+    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr));
+    if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
+    carve_binning(bbase, N, &bin);
+
+    if ((rc = check_cuda(launch_binning(P, gx, gy, N, g, radii, img, bin, st), "binning launch"))) return rc;
+    if ((rc = stage_check(s, st, "binning"))) return rc;
+    if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st),
+                         "render forward launch"))) return rc;
+    return stage_check(s, st, "render forward");
+}
+
+int gsr_rasterize_backward(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream)
+{
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!s) { set_error("null settings"); return GSR_EINVAL; }
+    if (P == 0) return GSR_OK;
+    const int W = s->image_width, H = s->image_height;
+    if (!geom || !binning || !image || !radii || !means3D || !out_alpha || !dL_dout_color || !dL_dout_depth || !dL_dout_alpha ||
+        !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations || !workspace) {
+        set_error("null required pointer in backward"); return GSR_EINVAL;
+    }
+    if (shs && !dL_dsh) { set_error("dL_dsh is NULL but shs given"); return GSR_EINVAL; }
+    if (workspace_bytes < gsr_backward_workspace_bytes(P)) { set_error("workspace too small"); return GSR_EINVAL; }
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, tiles = gx * gy;
+    GeomState g; ImageState img; BinningState bin;
+    carve_geom((char*)geom, P, tiles, &g);
+    carve_image((char*)image, W, H, &img);
+    carve_binning((char*)binning, R, &bin);
+
+    float* acc = (float*)workspace;
+    int rc;
+    if ((rc = check_cuda(cudaMemsetAsync(acc, 0, (size_t)P * ACC_STRIDE * sizeof(float), st), "memset accumulators"))) return rc;
+    if (R > 0) {
+        if ((rc = check_cuda(launch_render_backward(W, H, gx, gy, g, img, bin, s->bg, out_alpha, dL_dout_color,
+                                                    dL_dout_depth, dL_dout_alpha, acc, st), "render backward launch"))) return rc;
+        if ((rc = stage_check(s, st, "render backward"))) return rc;
+    }
+    BwdArgs b;
+    b.P = P; b.M = shs ? M : 0; b.D = s->sh_degree; b.W = W; b.H = H;
+    b.tanfovx = s->tanfovx; b.tanfovy = s->tanfovy;
+    b.focal_y = H / (2.0f * s->tanfovy); b.focal_x = W / (2.0f * s->tanfovx);
+    b.scale_modifier = s->scale_modifier;
+    b.means3D = means3D; b.shs = shs; b.colors_precomp = colors_precomp; b.scales = scales; b.rotations = rotations;
+    b.cov_precomp = cov3D_precomp != nullptr;
+    b.cov3D = cov3D_precomp ? cov3D_precomp : g.cov3D;
+    b.view = s->viewmatrix; b.proj = s->projmatrix; b.campos = s->campos;
+    b.radii = radii; b.clamped = g.clamped; b.acc = acc;
+    b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
+    b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
+    if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
+    return stage_check(s, st, "preprocess backward");
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream)
+{
+    (void)projmatrix;   // the reference computes p_proj and never uses it (auxiliary.h:147-154)
+    if (P == 0) return GSR_OK;
+    if (P < 0 || !means3D || !viewmatrix || !present) { set_error("bad argument to gsr_mark_visible"); return GSR_EINVAL; }
+    return check_cuda(launch_mark_visible(P, means3D, viewmatrix, present, (cudaStream_t)stream), "mark_visible launch");
+}
+
+}  // extern "C"

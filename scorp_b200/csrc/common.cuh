@@ -1,0 +1,176 @@
+// common.cuh -- shared declarations for the sm_100a Gaussian-splatting kernels.
+//
+// Conventions (reference: submodules/diff-gaussian-rasterization/cuda_rasterizer/):
+//  * 16x16 pixel tiles (config.h:15-17); one CTA of 256 threads per tile in the blend kernels.
+//  * viewmatrix/projmatrix are indexed column-major, m[4*col+row] (auxiliary.h:58-87).
+//  * Integer-deciding arithmetic (depth key, radius, tile rect) is written with explicit
+//    __fmul_rn/__fadd_rn/__fmaf_rn so the rounding sequence is fixed by the source and equals
+//    the sequence nvcc 12.9 emits for the reference (default -fmad contraction); see DESIGN.md.
+#pragma once
+#include <cstdint>
+#include <cstddef>
+#include <cuda_runtime.h>
+#include "../../include/gsr_b200.h"
+
+namespace gsr {
+
+constexpr int TILE = 16;            // BLOCK_X == BLOCK_Y == 16 (config.h:16-17)
+constexpr int TILE_PIX = TILE * TILE;
+constexpr int BATCH = 256;          // Gaussians staged per round (== BLOCK_SIZE in the reference)
+
+// Per-Gaussian render record, 48 bytes, 16-byte aligned: what the blend kernels stage.
+struct __align__(16) GaussRec {
+    float x, y;          // pixel-space mean           (points_xy_image)
+    float ca, cb;        // conic.x, conic.y           (conic_opacity.xy)
+    float cc, opacity;   // conic.z, opacity           (conic_opacity.zw)
+    float depth;         // view-space z               (depths)
+    float thr;           // conservative power threshold: power < thr  =>  alpha < 1/255
+    float r, g, b;       // colour                     (rgb / colors_precomp)
+    float pad;
+};
+static_assert(sizeof(GaussRec) == 48, "GaussRec must be 48 bytes");
+
+// Private scratch layouts (see gsr_*_layout in include/gsr_b200.h).
+struct GeomState {
+    GaussRec* rec;
+    float*    cov3D;
+    uint8_t*  clamped;
+    uint32_t* tiles_touched;
+    uint32_t* tile_count;
+    uint32_t* counters;
+};
+struct ImageState {
+    uint2*    ranges;
+    uint32_t* n_contrib;
+};
+struct BinningState {
+    uint32_t* point_list;
+    uint64_t* point_list_keys;
+    uint64_t* scratch;
+};
+
+inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
+
+inline size_t carve_geom(char* base, int P, int tiles, GeomState* g, size_t* off = nullptr) {
+    size_t o = 0, k = 0;
+    auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes); if (off) off[k] = at; ++k; return at; };
+    size_t a0 = take((size_t)P * sizeof(GaussRec));
+    size_t a1 = take((size_t)P * 6 * sizeof(float));
+    size_t a2 = take((size_t)P);
+    size_t a3 = take((size_t)P * 4);
+    size_t a4 = take((size_t)tiles * 4);
+    size_t a5 = take(16);
+    if (g) {
+        g->rec = (GaussRec*)(base + a0); g->cov3D = (float*)(base + a1);
+        g->clamped = (uint8_t*)(base + a2); g->tiles_touched = (uint32_t*)(base + a3);
+        g->tile_count = (uint32_t*)(base + a4); g->counters = (uint32_t*)(base + a5);
+    }
+    return o;
+}
+inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off = nullptr) {
+    int tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    size_t o = 0;
+    size_t a0 = o; o = align_up(o + (size_t)tiles * sizeof(uint2));
+    size_t a1 = o; o = align_up(o + (size_t)W * H * 4);
+    if (off) { off[0] = a0; off[1] = a1; }
+    if (s) { s->ranges = (uint2*)(base + a0); s->n_contrib = (uint32_t*)(base + a1); }
+    return o;
+}
+inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nullptr) {
+    size_t n = (size_t)(N > 0 ? N : 1);
+    size_t o = 0;
+    size_t a0 = o; o = align_up(o + n * 4);
+    size_t a1 = o; o = align_up(o + n * 8);
+    size_t a2 = o; o = align_up(o + n * 8);
+    if (off) { off[0] = a0; off[1] = a1; off[2] = a2; }
+    if (b) { b->point_list = (uint32_t*)(base + a0); b->point_list_keys = (uint64_t*)(base + a1);
+             b->scratch = (uint64_t*)(base + a2); }
+    return o;
+}
+
+// error plumbing (api.cu)
+void set_error(const char* fmt, ...);
+int  check_cuda(cudaError_t e, const char* what);
+int  stage_check(const GsrSettings* s, cudaStream_t st, const char* what);
+
+#ifdef __CUDACC__
+// ---- exact-rounding helpers -------------------------------------------------------------
+__device__ __forceinline__ float mulr(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float addr(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ float fmar(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ float divr(float a, float b) { return __fdiv_rn(a, b); }
+
+// row r of (matrix * [p,1]) with the reference's rounding sequence
+// (transformPoint4x3/4x4, auxiliary.h:58-80: FMUL(y*m4) FFMA(x,m0) FFMA(z,m8) FADD(m12)).
+__device__ __forceinline__ float xform_row(const float* __restrict__ m, int r, float x, float y, float z) {
+    float t = mulr(y, m[4 + r]);
+    t = fmar(x, m[r], t);
+    t = fmar(z, m[8 + r], t);
+    return addr(t, m[12 + r]);
+}
+
+// ndc2Pix (auxiliary.h:41-44): evaluated in double, DFMA-contracted as nvcc does.
+__device__ __forceinline__ float ndc_to_pix(float v, int S) {
+    double d = __dadd_rn((double)v, 1.0);
+    d = __fma_rn(d, (double)S, -1.0);
+    d = __dmul_rn(d, 0.5);
+    return (float)d;
+}
+
+// getRect (auxiliary.h:46-56). Float divisions by 16 are exact multiplications by 1/16.
+__device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx, int gy,
+                                          uint32_t& x0, uint32_t& y0, uint32_t& x1, uint32_t& y1) {
+    const float rf = (float)radius;
+    x0 = min((uint32_t)gx, (uint32_t)max(0, (int)mulr(subr(px, rf), 0.0625f)));
+    y0 = min((uint32_t)gy, (uint32_t)max(0, (int)mulr(subr(py, rf), 0.0625f)));
+    x1 = min((uint32_t)gx, (uint32_t)max(0, (int)mulr(addr(addr(addr(px, rf), 16.0f), -1.0f), 0.0625f)));
+    y1 = min((uint32_t)gy, (uint32_t)max(0, (int)mulr(addr(addr(addr(py, rf), 16.0f), -1.0f), 0.0625f)));
+}
+
+// cp.async 16-byte global->shared (LDGSTS), L2-only caching: the records are read once per CTA.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" :: "r"(d), "l"(gsrc));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" :: "n"(N)); }
+#endif  // __CUDACC__
+
+// kernel launchers (one per .cu)
+struct FwdArgs {
+    int P, M, D, W, H, gx, gy;
+    float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+    const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
+    const float *view, *proj, *campos, *bg;
+    bool prefiltered;
+};
+cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
+cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
+cudaError_t launch_binning(int P, int gx, int gy, int N, const GeomState& g, const int32_t* radii,
+                           const ImageState& img, const BinningState& bin, cudaStream_t st);
+cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
+                                  const BinningState& bin, const float* bg,
+                                  float* out_color, float* out_depth, float* out_alpha, cudaStream_t st);
+cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
+                                   const BinningState& bin, const float* bg, const float* out_alpha,
+                                   const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
+                                   float* acc, cudaStream_t st);
+struct BwdArgs {
+    int P, M, D, W, H;
+    float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+    const float *means3D, *shs, *colors_precomp, *scales, *rotations, *cov3D;  // cov3D: precomp or geom
+    bool cov_precomp;
+    const float *view, *proj, *campos;
+    const int32_t* radii;
+    const uint8_t* clamped;
+    const float* acc;  // 12 floats per Gaussian from the blend backward
+    float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drotations;
+};
+cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st);
+
+// accumulator slots written by the blend backward (12 floats = 48 B per Gaussian)
+enum { ACC_MX = 0, ACC_MY = 1, ACC_CA = 2, ACC_CB = 3, ACC_CC = 4, ACC_OP = 5,
+       ACC_R = 6, ACC_G = 7, ACC_B = 8, ACC_D = 9, ACC_STRIDE = 12 };
+
+}  // namespace gsr

@@ -1,0 +1,221 @@
+// preprocess_bwd.cu -- per-Gaussian backward: conic -> cov3D/mean, projection and depth -> mean,
+// SH backward, cov3D -> scale/rotation, in ONE pass that also writes every output row (zeros for
+// invisible Gaussians), so no gradient tensor needs a memset.
+//
+// Replaces computeCov2DCUDA (reference backward.cu:144-274), preprocessCUDA (:347-412),
+// computeColorFromSH backward (:20-139) and computeCov3D backward (:278-341), plus the ten
+// torch::zeros of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:158-167).
+#include "common.cuh"
+
+namespace gsr {
+
+struct V3 { float x, y, z; };
+__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
+__device__ __forceinline__ V3 operator*(float s, V3 a) { return { s * a.x, s * a.y, s * a.z }; }
+__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+__device__ __forceinline__ V3 ld3(const float* p) { return { __ldg(p), __ldg(p + 1), __ldg(p + 2) }; }
+__device__ __forceinline__ void st3(float* p, V3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
+
+// SH backward (backward.cu:20-139). Writes dL_dsh[0..M) (zeros beyond the active degree) and
+// returns the colour-induced part of dL_dmean.
+__device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict__ sh, V3 pos, V3 campos,
+                                          V3 dRGB, float* __restrict__ dsh) {
+    const V3 dir_orig = { pos.x - campos.x, pos.y - campos.y, pos.z - campos.z };
+    const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
+    const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
+    const float C1 = 0.4886025119029199f;
+    const float C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
+    const float C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                          -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
+    V3 gx = { 0, 0, 0 }, gy = { 0, 0, 0 }, gz = { 0, 0, 0 };   // dRGB/dx, /dy, /dz
+    float basis[16];
+    basis[0] = 0.28209479177387814f;
+    int used = 1;
+    if (D > 0) {
+        basis[1] = -C1 * y; basis[2] = C1 * z; basis[3] = -C1 * x;
+        gx = -C1 * ld3(sh + 9); gy = -C1 * ld3(sh + 3); gz = C1 * ld3(sh + 6);
+        used = 4;
+        if (D > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            basis[4] = C2[0] * xy; basis[5] = C2[1] * yz; basis[6] = C2[2] * (2.f * zz - xx - yy);
+            basis[7] = C2[3] * xz; basis[8] = C2[4] * (xx - yy);
+            const V3 s4 = ld3(sh + 12), s5 = ld3(sh + 15), s6 = ld3(sh + 18), s7 = ld3(sh + 21), s8 = ld3(sh + 24);
+            gx = gx + (C2[0] * y) * s4 + (C2[2] * 2.f * -x) * s6 + (C2[3] * z) * s7 + (C2[4] * 2.f * x) * s8;
+            gy = gy + (C2[0] * x) * s4 + (C2[1] * z) * s5 + (C2[2] * 2.f * -y) * s6 + (C2[4] * 2.f * -y) * s8;
+            gz = gz + (C2[1] * y) * s5 + (C2[2] * 2.f * 2.f * z) * s6 + (C2[3] * x) * s7;
+            used = 9;
+            if (D > 2) {
+                basis[9] = C3[0] * y * (3.f * xx - yy); basis[10] = C3[1] * xy * z;
+                basis[11] = C3[2] * y * (4.f * zz - xx - yy); basis[12] = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
+                basis[13] = C3[4] * x * (4.f * zz - xx - yy); basis[14] = C3[5] * z * (xx - yy);
+                basis[15] = C3[6] * x * (xx - 3.f * yy);
+                const V3 s9 = ld3(sh + 27), s10 = ld3(sh + 30), s11 = ld3(sh + 33), s12 = ld3(sh + 36),
+                         s13 = ld3(sh + 39), s14 = ld3(sh + 42), s15 = ld3(sh + 45);
+                gx = gx + (C3[0] * 3.f * 2.f * xy) * s9 + (C3[1] * yz) * s10 + (C3[2] * -2.f * xy) * s11
+                        + (C3[3] * -3.f * 2.f * xz) * s12 + (C3[4] * (-3.f * xx + 4.f * zz - yy)) * s13
+                        + (C3[5] * 2.f * xz) * s14 + (C3[6] * 3.f * (xx - yy)) * s15;
+                gy = gy + (C3[0] * 3.f * (xx - yy)) * s9 + (C3[1] * xz) * s10 + (C3[2] * (-3.f * yy + 4.f * zz - xx)) * s11
+                        + (C3[3] * -3.f * 2.f * yz) * s12 + (C3[4] * -2.f * xy) * s13 + (C3[5] * -2.f * yz) * s14
+                        + (C3[6] * -3.f * 2.f * xy) * s15;
+                gz = gz + (C3[1] * xy) * s10 + (C3[2] * 4.f * 2.f * yz) * s11 + (C3[3] * 3.f * (2.f * zz - xx - yy)) * s12
+                        + (C3[4] * 4.f * 2.f * xz) * s13 + (C3[5] * (xx - yy)) * s14;
+                used = 16;
+            }
+        }
+    }
+    for (int k = 0; k < M; ++k) {
+        const float bk = (k < used) ? basis[k < 16 ? k : 15] : 0.0f;
+        st3(dsh + 3 * k, bk * dRGB);
+    }
+    // through the normalisation of the view direction (dnormvdv, auxiliary.h:107-117)
+    const V3 ddir = { dot(gx, dRGB), dot(gy, dRGB), dot(gz, dRGB) };
+    const V3 v = dir_orig;
+    const float sum2 = dot(v, v);
+    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    V3 dmean;
+    dmean.x = ((sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * invsum32;
+    dmean.y = (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32;
+    dmean.z = (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32;
+    return dmean;
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_backward_kernel(BwdArgs a) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= a.P) return;
+    const bool vis = a.radii[idx] > 0;
+
+    float dcov[6] = { 0, 0, 0, 0, 0, 0 };
+    V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, dscale = { 0, 0, 0 };
+    float4 drot = { 0, 0, 0, 0 };
+    float dop = 0.0f;
+    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+
+    if (vis) {
+        const float* ac = a.acc + (size_t)idx * ACC_STRIDE;
+        const float4 q0 = __ldg(reinterpret_cast<const float4*>(ac));
+        const float4 q1 = __ldg(reinterpret_cast<const float4*>(ac) + 1);
+        const float4 q2 = __ldg(reinterpret_cast<const float4*>(ac) + 2);
+        dm2d = { q0.x, q0.y, 0.0f };
+        const float dconx = q0.z, dcony = q0.w, dconw = q1.x;
+        dop = q1.y;
+        dcol = { q1.z, q1.w, q2.x };
+        const float ddepth = q2.y;
+
+        const V3 m = ld3(a.means3D + 3 * idx);
+        const float* v = a.view;
+        const float* p = a.proj;
+        const float* c = a.cov3D + 6 * (size_t)idx;
+        const float c0 = __ldg(c), c1 = __ldg(c + 1), c2 = __ldg(c + 2), c3 = __ldg(c + 3), c4 = __ldg(c + 4), c5 = __ldg(c + 5);
+
+        // ---- conic -> cov2D -> cov3D, T, J, t (backward.cu:144-274)
+        float tx = v[0] * m.x + v[4] * m.y + v[8] * m.z + v[12];
+        float ty = v[1] * m.x + v[5] * m.y + v[9] * m.z + v[13];
+        const float tz = v[2] * m.x + v[6] * m.y + v[10] * m.z + v[14];
+        const float limx = 1.3f * a.tanfovx, limy = 1.3f * a.tanfovy;
+        const float txtz = tx / tz, tytz = ty / tz;
+        tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+        ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+        const float J00 = a.focal_x / tz, J02 = -(a.focal_x * tx) / (tz * tz);
+        const float J11 = a.focal_y / tz, J12 = -(a.focal_y * ty) / (tz * tz);
+        const float T00 = v[0] * J00 + v[2] * J02, T01 = v[4] * J00 + v[6] * J02, T02 = v[8] * J00 + v[10] * J02;
+        const float T10 = v[1] * J11 + v[2] * J12, T11 = v[5] * J11 + v[6] * J12, T12 = v[9] * J11 + v[10] * J12;
+        const float X0 = T00 * c0 + T01 * c1 + T02 * c2, X1 = T00 * c1 + T01 * c3 + T02 * c4, X2 = T00 * c2 + T01 * c4 + T02 * c5;
+        const float Y0 = T10 * c0 + T11 * c1 + T12 * c2, Y1 = T10 * c1 + T11 * c3 + T12 * c4, Y2 = T10 * c2 + T11 * c4 + T12 * c5;
+        const float ca = T00 * X0 + T01 * X1 + T02 * X2 + 0.3f;
+        const float cb = T00 * Y0 + T01 * Y1 + T02 * Y2;
+        const float cc = T10 * Y0 + T11 * Y1 + T12 * Y2 + 0.3f;
+        const float denom = ca * cc - cb * cb;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        float da = 0.f, db = 0.f, dc = 0.f;
+        if (denom2inv != 0.f) {
+            da = denom2inv * (-cc * cc * dconx + 2 * cb * cc * dcony + (denom - ca * cc) * dconw);
+            dc = denom2inv * (-ca * ca * dconw + 2 * ca * cb * dcony + (denom - ca * cc) * dconx);
+            db = denom2inv * 2 * (cb * cc * dconx - (denom + 2 * cb * cb) * dcony + ca * cb * dconw);
+            dcov[0] = T00 * T00 * da + T00 * T10 * db + T10 * T10 * dc;
+            dcov[3] = T01 * T01 * da + T01 * T11 * db + T11 * T11 * dc;
+            dcov[5] = T02 * T02 * da + T02 * T12 * db + T12 * T12 * dc;
+            dcov[1] = 2 * T00 * T01 * da + (T00 * T11 + T01 * T10) * db + 2 * T10 * T11 * dc;
+            dcov[2] = 2 * T00 * T02 * da + (T00 * T12 + T02 * T10) * db + 2 * T10 * T12 * dc;
+            dcov[4] = 2 * T02 * T01 * da + (T01 * T12 + T02 * T11) * db + 2 * T11 * T12 * dc;
+        }
+        const float dT00 = 2 * X0 * da + Y0 * db, dT01 = 2 * X1 * da + Y1 * db, dT02 = 2 * X2 * da + Y2 * db;
+        const float dT10 = 2 * Y0 * dc + X0 * db, dT11 = 2 * Y1 * dc + X1 * db, dT12 = 2 * Y2 * dc + X2 * db;
+        const float dJ00 = v[0] * dT00 + v[4] * dT01 + v[8] * dT02;
+        const float dJ02 = v[2] * dT00 + v[6] * dT01 + v[10] * dT02;
+        const float dJ11 = v[1] * dT10 + v[5] * dT11 + v[9] * dT12;
+        const float dJ12 = v[2] * dT10 + v[6] * dT11 + v[10] * dT12;
+        const float itz = 1.f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+        const float dtx = x_grad_mul * -a.focal_x * itz2 * dJ02;
+        const float dty = y_grad_mul * -a.focal_y * itz2 * dJ12;
+        const float dtz = -a.focal_x * itz2 * dJ00 - a.focal_y * itz2 * dJ11
+                        + (2 * a.focal_x * tx) * itz3 * dJ02 + (2 * a.focal_y * ty) * itz3 * dJ12;
+        dmean = { v[0] * dtx + v[1] * dty + v[2] * dtz, v[4] * dtx + v[5] * dty + v[6] * dtz, v[8] * dtx + v[9] * dty + v[10] * dtz };
+
+        // ---- screen-space mean and depth -> mean (backward.cu:371-403)
+        const float hw_ = p[3] * m.x + p[7] * m.y + p[11] * m.z + p[15];
+        const float m_w = 1.0f / (hw_ + 0.0000001f);
+        const float mul1 = (p[0] * m.x + p[4] * m.y + p[8] * m.z + p[12]) * m_w * m_w;
+        const float mul2 = (p[1] * m.x + p[5] * m.y + p[9] * m.z + p[13]) * m_w * m_w;
+        dmean.x += (p[0] * m_w - p[3] * mul1) * dm2d.x + (p[1] * m_w - p[3] * mul2) * dm2d.y;
+        dmean.y += (p[4] * m_w - p[7] * mul1) * dm2d.x + (p[5] * m_w - p[7] * mul2) * dm2d.y;
+        dmean.z += (p[8] * m_w - p[11] * mul1) * dm2d.x + (p[9] * m_w - p[11] * mul2) * dm2d.y;
+        const float mul3 = v[2] * m.x + v[6] * m.y + v[10] * m.z + v[14];
+        dmean.x += (v[2] - v[3] * mul3) * ddepth;
+        dmean.y += (v[6] - v[7] * mul3) * ddepth;
+        dmean.z += (v[10] - v[11] * mul3) * ddepth;
+
+        // ---- colour -> SH (+ mean)
+        if (a.shs) {
+            const uint8_t cl = a.clamped[idx];
+            const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
+            dmean = dmean + sh_backward(a.D, a.M, a.shs + (size_t)idx * a.M * 3, m, ld3(a.campos), dRGB, dsh);
+        }
+
+        // ---- cov3D -> scale, rotation (backward.cu:278-341)
+        if (!a.cov_precomp) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+            const float r = q.x, x = q.y, y = q.z, z = q.w;
+            const V3 s = a.scale_modifier * ld3(a.scales + 3 * idx);
+            // rows of R-hat (R-hat(row,col) = glm R[col][row])
+            const V3 R0 = { 1.f - 2.f * (y * y + z * z), 2.f * (x * y + r * z), 2.f * (x * z - r * y) };
+            const V3 R1 = { 2.f * (x * y - r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z + r * x) };
+            const V3 R2 = { 2.f * (x * z + r * y), 2.f * (y * z - r * x), 1.f - 2.f * (x * x + y * y) };
+            const V3 S0 = { dcov[0], 0.5f * dcov[1], 0.5f * dcov[2] };
+            const V3 S1 = { 0.5f * dcov[1], dcov[3], 0.5f * dcov[4] };
+            const V3 S2 = { 0.5f * dcov[2], 0.5f * dcov[4], dcov[5] };
+            auto rowmul = [&](V3 rr, float sc) {   // 2 * sc * rr * dSigma
+                V3 o = { rr.x * S0.x + rr.y * S1.x + rr.z * S2.x, rr.x * S0.y + rr.y * S1.y + rr.z * S2.y,
+                         rr.x * S0.z + rr.y * S1.z + rr.z * S2.z };
+                return (2.0f * sc) * o;
+            };
+            const V3 dM0 = rowmul(R0, s.x), dM1 = rowmul(R1, s.y), dM2 = rowmul(R2, s.z);
+            dscale = { dot(R0, dM0), dot(R1, dM1), dot(R2, dM2) };
+            const V3 N0 = s.x * dM0, N1 = s.y * dM1, N2 = s.z * dM2;
+            drot.x = 2 * z * (N0.y - N1.x) + 2 * y * (N2.x - N0.z) + 2 * x * (N1.z - N2.y);
+            drot.y = 2 * y * (N1.x + N0.y) + 2 * z * (N2.x + N0.z) + 2 * r * (N1.z - N2.y) - 4 * x * (N2.z + N1.y);
+            drot.z = 2 * x * (N1.x + N0.y) + 2 * r * (N2.x - N0.z) + 2 * z * (N1.z + N2.y) - 4 * y * (N2.z + N0.x);
+            drot.w = 2 * r * (N0.y - N1.x) + 2 * x * (N2.x + N0.z) + 2 * y * (N1.z + N2.y) - 4 * z * (N1.y + N0.x);
+        }
+    }
+    if (dsh && (!vis || !a.shs)) for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.0f;
+
+    st3(a.dL_dmeans3D + 3 * idx, dmean);
+    st3(a.dL_dmeans2D + 3 * idx, dm2d);
+    st3(a.dL_dcolors + 3 * idx, dcol);
+    a.dL_dopacity[idx] = dop;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+    st3(a.dL_dscales + 3 * idx, dscale);
+    reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
+}
+
+cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st) {
+    preprocess_backward_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+}  // namespace gsr
