@@ -1,0 +1,160 @@
+"""`_C` level of the 3DGS package: same three entry points, argument order and return tuples as
+the reference's pybind11 module (reference submodules/diff-gaussian-rasterization/ext.cpp:15-19,
+rasterize_points.h:18-70), implemented by calling libgsr_b200.so through its C ABI.
+
+This file owns what the reference's torch glue owned (rasterize_points.cu:36-229): output
+allocation, the three scratch buffers (handed to the library through an allocator callback,
+like the reference's resize lambdas at rasterize_points.cu:27-33) and pointer extraction.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _lib
+from .._lib import GsrSettings, ptr
+
+
+def _f32c(t: torch.Tensor, device) -> torch.Tensor:
+    """contiguous fp32 on `device`; 0-element sentinels (CPU or CUDA) pass through."""
+    if t is None or t.numel() == 0:
+        return t
+    if t.dtype != torch.float32:
+        t = t.float()
+    if t.device != device:
+        t = t.to(device)
+    return t.contiguous()
+
+
+class _Arena:
+    """Allocator handed to the library: one uint8 tensor per scratch buffer."""
+
+    def __init__(self, device):
+        self.device = device
+        self.bufs = {}
+        self.error = None
+        self.fn = _lib.ALLOC_FN(self._alloc)
+
+    def _alloc(self, _user, which, nbytes):
+        try:
+            t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
+            self.bufs[which] = t
+            return t.data_ptr()
+        except Exception as ex:  # never let an exception cross the C ABI
+            self.error = ex
+            return None
+
+    def get(self, which):
+        t = self.bufs.get(which)
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+def _settings(bg, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier, degree,
+              prefiltered, debug):
+    s = GsrSettings()
+    s.image_height, s.image_width = int(H), int(W)
+    s.tanfovx, s.tanfovy, s.scale_modifier = float(tan_fovx), float(tan_fovy), float(scale_modifier)
+    s.sh_degree, s.prefiltered, s.debug = int(degree), int(bool(prefiltered)), int(bool(debug))
+    s.bg, s.viewmatrix, s.projmatrix, s.campos = ptr(bg), ptr(viewmatrix), ptr(projmatrix), ptr(campos)
+    return s
+
+
+def _stream(device):
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                        image_width, sh, degree, campos, prefiltered, debug):
+    """-> (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)"""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")   # rasterize_points.cu:57-59
+    if not means3D.is_cuda:
+        raise _lib.GsrError("means3D must be a CUDA tensor: this rasterizer has no CPU path")
+    lib = _lib.lib()
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    means3D = _f32c(means3D, dev); colors = _f32c(colors, dev); opacity = _f32c(opacity, dev)
+    scales = _f32c(scales, dev); rotations = _f32c(rotations, dev); cov3D_precomp = _f32c(cov3D_precomp, dev)
+    sh = _f32c(sh, dev)
+    background = _f32c(background, dev); viewmatrix = _f32c(viewmatrix, dev)
+    projmatrix = _f32c(projmatrix, dev); campos = _f32c(campos, dev)
+
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_depth = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    out_alpha = torch.empty((1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    arena = _Arena(dev)
+    s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
+                  degree, prefiltered, debug)
+    n = C.c_int(0)
+    with torch.cuda.device(dev):
+        rc = lib.gsr_rasterize_forward(
+            C.byref(s), P, M, ptr(means3D), ptr(sh), ptr(colors), ptr(opacity), ptr(scales), ptr(rotations),
+            ptr(cov3D_precomp), out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(),
+            ptr(radii), arena.fn, None, C.byref(n), _stream(dev))
+    if arena.error is not None:
+        raise arena.error
+    _lib.check(rc, "gsr_rasterize_forward")
+    return (n.value, out_color, out_depth, out_alpha, radii,
+            arena.get(_lib.GSR_BUF_GEOM), arena.get(_lib.GSR_BUF_BINNING), arena.get(_lib.GSR_BUF_IMAGE))
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, alpha, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)"""
+    lib = _lib.lib()
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    means3D = _f32c(means3D, dev); colors = _f32c(colors, dev); scales = _f32c(scales, dev)
+    rotations = _f32c(rotations, dev); cov3D_precomp = _f32c(cov3D_precomp, dev); sh = _f32c(sh, dev)
+    background = _f32c(background, dev); viewmatrix = _f32c(viewmatrix, dev)
+    projmatrix = _f32c(projmatrix, dev); campos = _f32c(campos, dev)
+    dL_dout_color = _f32c(dL_dout_color, dev); dL_dout_depth = _f32c(dL_dout_depth, dev)
+    dL_dout_alpha = _f32c(dL_dout_alpha, dev); alpha = _f32c(alpha, dev)
+
+    # one arena for all gradients (fully written by the library: no zero fill needed)
+    widths = (3, 3, 1, 3, 6, 3 * M, 3, 4)
+    flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
+    outs, o = [], 0
+    for w in widths:
+        outs.append(flat[o:o + P * w]); o += P * w
+    g_m2d, g_col, g_op, g_m3d, g_cov, g_sh, g_sc, g_rot = outs
+    if P != 0:
+        ws_bytes = lib.gsr_backward_workspace_bytes(P)
+        ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
+                      degree, False, debug)
+        with torch.cuda.device(dev):
+            rc = lib.gsr_rasterize_backward(
+                C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),
+                ptr(cov3D_precomp), ptr(radii), ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer),
+                ptr(alpha), ptr(dL_dout_color), ptr(dL_dout_depth), ptr(dL_dout_alpha),
+                ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_cov), ptr(g_sh), ptr(g_sc), ptr(g_rot),
+                ws.data_ptr(), ws_bytes, _stream(dev))
+        _lib.check(rc, "gsr_rasterize_backward")
+    return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),
+            g_sh.view(P, M, 3), g_sc.view(P, 3), g_rot.view(P, 4))
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """bool[P]: view-space z > 0.2 (rasterize_points.cu:210-229)."""
+    lib = _lib.lib()
+    if not means3D.is_cuda:
+        raise _lib.GsrError("means3D must be a CUDA tensor")
+    dev = means3D.device
+    P = means3D.size(0)
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        means3D = _f32c(means3D, dev); viewmatrix = _f32c(viewmatrix, dev); projmatrix = _f32c(projmatrix, dev)
+        with torch.cuda.device(dev):
+            rc = lib.gsr_mark_visible(P, ptr(means3D), ptr(viewmatrix), ptr(projmatrix), present.data_ptr(),
+                                      _stream(dev))
+        _lib.check(rc, "gsr_mark_visible")
+    return present

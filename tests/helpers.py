@@ -1,0 +1,110 @@
+"""Shared test helpers: run the product (through its reference-shaped `_C` level, i.e. the C ABI),
+the reference CUDA build (oracle/_ref via oracle/ref_cuda.py) and compare."""
+from __future__ import annotations
+
+import ctypes as C
+import sys
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parent.parent
+if str(ROOT) not in sys.path:
+    sys.path.insert(0, str(ROOT))
+
+from scorp_b200 import _lib, synth  # noqa: E402
+
+
+def empty():
+    return torch.Tensor([])
+
+
+def ours_forward(scene, cam, colors_precomp=None, cov3D_precomp=None, scale_modifier=1.0, debug=False):
+    from scorp_b200.diff_gaussian_rasterization import _C
+    shs = empty() if colors_precomp is not None else scene.shs
+    col = colors_precomp if colors_precomp is not None else empty()
+    sc = empty() if cov3D_precomp is not None else scene.scales
+    rot = empty() if cov3D_precomp is not None else scene.rotations
+    cov = cov3D_precomp if cov3D_precomp is not None else empty()
+    out = _C.rasterize_gaussians(scene.bg, scene.means3D, col, scene.opacities, sc, rot, scale_modifier, cov,
+                                 cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, shs,
+                                 scene.sh_degree, cam.campos, False, debug)
+    keys = ("num_rendered", "color", "depth", "alpha", "radii", "geom", "binning", "image")
+    d = dict(zip(keys, out))
+    d.update(P=scene.P, H=cam.H, W=cam.W, args=(shs, col, sc, rot, cov, scale_modifier))
+    return d
+
+
+def ours_backward(scene, cam, fwd, grads, debug=False):
+    from scorp_b200.diff_gaussian_rasterization import _C
+    shs, col, sc, rot, cov, smod = fwd["args"]
+    out = _C.rasterize_gaussians_backward(scene.bg, scene.means3D, fwd["radii"], col, sc, rot, smod, cov,
+                                          cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0],
+                                          grads[1], grads[2], shs, scene.sh_degree, cam.campos, fwd["geom"],
+                                          fwd["num_rendered"], fwd["binning"], fwd["image"], fwd["alpha"], debug)
+    keys = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")
+    return dict(zip(keys, out))
+
+
+def ours_intermediates(fwd):
+    """Slice the product's private scratch (gsr_*_layout) into the reference's named arrays."""
+    lib = _lib.lib()
+    P, H, W, N = fwd["P"], fwd["H"], fwd["W"], fwd["num_rendered"]
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    off = (C.c_size_t * 6)(); tot = C.c_size_t(0)
+    lib.gsr_geom_layout(P, tiles, off, C.byref(tot))
+    g = fwd["geom"]
+    rec = g[off[0]: off[0] + 48 * P].view(torch.float32).view(P, 12)
+    res = dict(means2D=rec[:, 0:2], conic_opacity=rec[:, 2:6], depths=rec[:, 6], rgb=rec[:, 8:11],
+               cov3D=g[off[1]: off[1] + 24 * P].view(torch.float32).view(P, 6),
+               clamped=g[off[2]: off[2] + P],
+               tiles_touched=g[off[3]: off[3] + 4 * P].view(torch.int32))
+    ioff = (C.c_size_t * 2)()
+    lib.gsr_image_layout(W, H, ioff, C.byref(tot))
+    im = fwd["image"]
+    res["ranges"] = im[ioff[0]: ioff[0] + 8 * tiles].view(torch.int32).view(tiles, 2)
+    res["n_contrib"] = im[ioff[1]: ioff[1] + 4 * H * W].view(torch.int32).view(H, W)
+    boff = (C.c_size_t * 3)()
+    lib.gsr_binning_layout(N, boff, C.byref(tot))
+    b = fwd["binning"]
+    if N > 0:
+        res["point_list"] = b[boff[0]: boff[0] + 4 * N].view(torch.int32)
+        res["point_list_keys"] = b[boff[1]: boff[1] + 8 * N].view(torch.int64)
+    else:
+        res["point_list"] = torch.zeros(0, dtype=torch.int32, device=g.device)
+        res["point_list_keys"] = torch.zeros(0, dtype=torch.int64, device=g.device)
+    return res
+
+
+def ref_forward(scene, cam, colors_precomp=None, cov3D_precomp=None, scale_modifier=1.0):
+    from oracle import ref_cuda
+    shs = None if colors_precomp is not None else scene.shs
+    sc = None if cov3D_precomp is not None else scene.scales
+    rot = None if cov3D_precomp is not None else scene.rotations
+    out = ref_cuda.dgr_forward(scene.bg, scene.means3D, colors_precomp, scene.opacities, sc, rot, scale_modifier,
+                               cov3D_precomp, cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H,
+                               cam.W, shs, scene.sh_degree, cam.campos)
+    out["args"] = (shs, colors_precomp, sc, rot, cov3D_precomp, scale_modifier)
+    return out
+
+
+def ref_backward(scene, cam, fwd, grads):
+    from oracle import ref_cuda
+    shs, col, sc, rot, cov, smod = fwd["args"]
+    return ref_cuda.dgr_backward(fwd, scene.bg, scene.means3D, col, sc, rot, smod, cov, cam.viewmatrix,
+                                 cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0], grads[1], grads[2], shs,
+                                 scene.sh_degree, cam.campos)
+
+
+def close(a, b, rtol=1e-4, atol_scale=1e-6):
+    """rtol 1e-4 with atol = 1e-6 * max|b|. Returns (ok, max_violation_ratio)."""
+    a = a.double().flatten(); b = b.double().flatten()
+    atol = atol_scale * float(b.abs().max()) if b.numel() else 0.0
+    err = (a - b).abs()
+    tol = atol + rtol * b.abs()
+    bad = err > tol
+    return (not bool(bad.any())), float((err / tol.clamp_min(1e-300)).max()) if b.numel() else 0.0
+
+
+def make(name, device="cuda", **kw):
+    return synth.make_scene(name, **kw).to(device)
