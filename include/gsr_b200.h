@@ -72,6 +72,15 @@ typedef struct GsrSettings {
 const char* gsr_last_error(void);
 int         gsr_version(void);
 
+/* Optional per-stage device timing (no reference counterpart; the reference only has the
+ * caller-side torch.cuda.Event pair of train_3dgs.py:48-49). When enabled, CUDA events are
+ * recorded on the caller's stream between stages; gsr_profile_read waits for the recorded
+ * passes (up to 64 since enable) and fills ms[GSR_PROF_STAGES] with their mean: 0 preprocess fwd, 1 binning, 2 blend fwd, 3 blend bwd (incl.
+ * accumulator memset), 4 preprocess bwd; -1 where nothing was recorded. */
+#define GSR_PROF_STAGES 5
+void gsr_profile_enable(int on);
+int  gsr_profile_read(float* ms);
+
 /* ---- 3DGS (diff_gaussian_rasterization) ------------------------------------------------
  * P Gaussians, M SH coefficients per Gaussian (0 when colors_precomp is given).
  * Optional inputs are NULL when absent (the reference's 0-element tensor sentinel):

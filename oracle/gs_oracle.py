@@ -1,0 +1,137 @@
+"""TEST INFRASTRUCTURE (checker): ctypes/numpy driver of oracle/libgs_oracle.so, the plain-C CPU
+restatement of the reference rasterizers (oracle/gs_oracle.c). Only tests/, __graft_entry__.smoke()
+and bench.py's cpu_baseline / reference legs may import this; nothing under scorp_b200/ does."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB = HERE / "libgs_oracle.so"
+_lib = None
+
+
+def build():
+    subprocess.run(["make", "-s", "-C", str(HERE), "oracle"], check=True)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not LIB.exists():
+            build()
+        _lib = C.CDLL(str(LIB))
+        _lib.gs_oracle_forward.restype = C.c_void_p
+        _lib.gs_oracle_num_rendered.restype = C.c_int64
+        _lib.gs_oracle_num_rendered.argtypes = [C.c_void_p]
+        _lib.gs_oracle_array.restype = C.c_void_p
+        _lib.gs_oracle_array.argtypes = [C.c_void_p, C.c_int]
+        _lib.gs_oracle_free.argtypes = [C.c_void_p]
+    return _lib
+
+
+def _f(a):
+    """contiguous float32 numpy (or None for absent/empty)."""
+    if a is None:
+        return None
+    if hasattr(a, "detach"):
+        a = a.detach().cpu().numpy()
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a if a.size else None
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+_ARRAYS = dict(depths=(0, np.float32, 1), means2D=(1, np.float32, 2), cov3D=(2, np.float32, 6),
+               conic_opacity=(3, np.float32, 4), rgb=(4, np.float32, 3), clamped=(5, np.uint8, 3),
+               tiles_touched=(6, np.uint32, 1), point_offsets=(7, np.uint32, 1))
+
+
+class Forward:
+    """Result of the oracle forward: outputs, intermediates and the state needed by backward."""
+
+    def __init__(self, **kw):
+        self.__dict__.update(kw)
+
+    def __del__(self):
+        st = self.__dict__.get("state")
+        if st and _lib is not None:
+            try:
+                _lib.gs_oracle_free(C.c_void_p(st))
+            except Exception:
+                pass
+            self.state = None
+
+
+def forward(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, cov3D_precomp, view, proj,
+            tanfovx, tanfovy, H, W, shs, degree, campos, threads=None):
+    L = lib()
+    if threads:
+        os.environ["OMP_NUM_THREADS"] = str(threads)
+    bg, means3D, colors_precomp, opacities = _f(bg), _f(means3D), _f(colors_precomp), _f(opacities)
+    scales, rotations, cov3D_precomp, view, proj, campos, shs = map(_f, (scales, rotations, cov3D_precomp, view, proj, campos, shs))
+    P = 0 if means3D is None else means3D.shape[0]
+    M = 0 if shs is None else shs.shape[1]
+    color = np.zeros((3, H, W), np.float32); depth = np.zeros((1, H, W), np.float32)
+    alpha = np.zeros((1, H, W), np.float32); radii = np.zeros((P,), np.int32)
+    st = L.gs_oracle_forward(C.c_int(P), C.c_int(degree), C.c_int(M), _p(bg), C.c_int(W), C.c_int(H), _p(means3D),
+                             _p(shs), _p(colors_precomp), _p(opacities), _p(scales), C.c_float(scale_modifier),
+                             _p(rotations), _p(cov3D_precomp), _p(view), _p(proj), _p(campos), C.c_float(tanfovx),
+                             C.c_float(tanfovy), _p(color), _p(depth), _p(alpha), _p(radii))
+    if not st:
+        raise RuntimeError("oracle forward failed (need shs or colors_precomp)")
+    N = int(L.gs_oracle_num_rendered(st))
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def arr(which, dtype, shape):
+        n = int(np.prod(shape))
+        if n == 0:
+            return np.zeros(shape, dtype)
+        ptr = L.gs_oracle_array(st, which)
+        buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape).copy()
+
+    inter = {k: arr(w, dt, (P, c) if c > 1 else (P,)) for k, (w, dt, c) in _ARRAYS.items()}
+    inter["point_list_keys"] = arr(8, np.uint64, (N,))
+    inter["point_list"] = arr(9, np.uint32, (N,))
+    inter["ranges"] = arr(10, np.uint32, (tiles, 2))
+    inter["n_contrib"] = arr(11, np.uint32, (H, W))
+    keep = dict(bg=bg, means3D=means3D, colors_precomp=colors_precomp, scales=scales, rotations=rotations,
+                cov3D_precomp=cov3D_precomp, view=view, proj=proj, campos=campos, shs=shs)
+    return Forward(state=st, color=color, depth=depth, alpha=alpha, radii=radii, num_rendered=N, inter=inter,
+                   P=P, M=M, H=H, W=W, degree=degree, scale_modifier=scale_modifier, tanfovx=tanfovx,
+                   tanfovy=tanfovy, keep=keep)
+
+
+def backward(fwd: Forward, dL_dcolor, dL_ddepth, dL_dalpha):
+    L = lib()
+    k = fwd.keep
+    P, M = fwd.P, fwd.M
+    g = dict(means2D=np.zeros((P, 3), np.float32), conic=np.zeros((P, 4), np.float32),
+             opacity=np.zeros((P, 1), np.float32), colors=np.zeros((P, 3), np.float32),
+             depths=np.zeros((P, 1), np.float32), means3D=np.zeros((P, 3), np.float32),
+             cov3D=np.zeros((P, 6), np.float32), sh=np.zeros((P, M, 3), np.float32),
+             scales=np.zeros((P, 3), np.float32), rotations=np.zeros((P, 4), np.float32))
+    dc, dd, da = _f(dL_dcolor), _f(dL_ddepth), _f(dL_dalpha)
+    L.gs_oracle_backward(C.c_void_p(fwd.state), C.c_int(fwd.degree), C.c_int(M), _p(k["bg"]), _p(k["means3D"]),
+                         _p(k["shs"]), _p(k["colors_precomp"]), _p(fwd.alpha), _p(k["scales"]),
+                         C.c_float(fwd.scale_modifier), _p(k["rotations"]), _p(k["cov3D_precomp"]), _p(k["view"]),
+                         _p(k["proj"]), _p(k["campos"]), C.c_float(fwd.tanfovx), C.c_float(fwd.tanfovy),
+                         _p(dc), _p(dd), _p(da), _p(g["means2D"]), _p(g["conic"]), _p(g["opacity"]), _p(g["colors"]),
+                         _p(g["depths"]), _p(g["means3D"]), _p(g["cov3D"]), _p(g["sh"]) if M else None,
+                         _p(g["scales"]), _p(g["rotations"]))
+    return g
+
+
+def mark_visible(means3D, view, proj):
+    L = lib()
+    m, v, p = _f(means3D), _f(view), _f(proj)
+    out = np.zeros((m.shape[0],), np.uint8)
+    L.gs_oracle_mark_visible(C.c_int(m.shape[0]), _p(m), _p(v), _p(p), _p(out))
+    return out.astype(bool)

@@ -60,7 +60,7 @@ def _slice(buf, base_off, nbytes, dtype, shape):
 
 
 def dgr_forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D, view, proj,
-                tanfovx, tanfovy, H, W, sh, degree, campos, prefiltered=False, debug=False):
+                tanfovx, tanfovy, H, W, sh, degree, campos, prefiltered=False, debug=False, sync=True):
     """Reference Rasterizer::forward. Returns dict with outputs, buffers and sliced intermediates."""
     lib = _load("dgr")
     lib.ref_dgr_forward.restype = C.c_int
@@ -70,13 +70,15 @@ def dgr_forward(bg, means3D, colors, opacity, scales, rotations, scale_modifier,
     color = torch.zeros(3, H, W, device=dev); depth = torch.zeros(1, H, W, device=dev)
     alpha = torch.zeros(1, H, W, device=dev); radii = torch.zeros(P, dtype=torch.int32, device=dev)
     ar = _Arena(dev)
-    torch.cuda.synchronize(dev)
+    if sync:
+        torch.cuda.synchronize(dev)
     n = lib.ref_dgr_forward(ar.fn, None, C.c_int(P), C.c_int(degree), C.c_int(M), _p(bg), C.c_int(W), C.c_int(H),
                             _p(means3D), _p(sh), _p(colors), _p(opacity), _p(scales), C.c_float(scale_modifier),
                             _p(rotations), _p(cov3D), _p(view), _p(proj), _p(campos), C.c_float(tanfovx),
                             C.c_float(tanfovy), C.c_int(int(prefiltered)), _p(color), _p(depth), _p(alpha),
                             _p(radii), C.c_int(int(debug)))
-    torch.cuda.synchronize(dev)
+    if sync:
+        torch.cuda.synchronize(dev)
     if n < 0:
         raise RuntimeError("reference forward raised")
     return dict(num_rendered=n, color=color, depth=depth, alpha=alpha, radii=radii,
@@ -115,7 +117,7 @@ def dgr_intermediates(out):
 
 
 def dgr_backward(fwd, bg, means3D, colors, scales, rotations, scale_modifier, cov3D, view, proj, tanfovx,
-                 tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh, degree, campos, debug=False):
+                 tanfovy, dL_dcolor, dL_ddepth, dL_dalpha, sh, degree, campos, debug=False, sync=True):
     """Reference Rasterizer::backward with the ten zero-filled gradient tensors of the torch glue."""
     lib = _load("dgr")
     lib.ref_dgr_backward.restype = C.c_int
@@ -124,7 +126,8 @@ def dgr_backward(fwd, bg, means3D, colors, scales, rotations, scale_modifier, co
     z = lambda *s: torch.zeros(*s, device=dev)
     g = dict(means2D=z(P, 3), conic=z(P, 2, 2), opacity=z(P, 1), colors=z(P, 3), depths=z(P, 1), means3D=z(P, 3),
              cov3D=z(P, 6), sh=z(P, M, 3), scales=z(P, 3), rotations=z(P, 4))
-    torch.cuda.synchronize(dev)
+    if sync:
+        torch.cuda.synchronize(dev)
     rc = lib.ref_dgr_backward(C.c_int(P), C.c_int(degree), C.c_int(M), C.c_int(fwd["num_rendered"]), _p(bg),
                               C.c_int(W), C.c_int(H), _p(means3D), _p(sh), _p(colors), _p(fwd["alpha"]), _p(scales),
                               C.c_float(scale_modifier), _p(rotations), _p(cov3D), _p(view), _p(proj), _p(campos),
@@ -133,7 +136,8 @@ def dgr_backward(fwd, bg, means3D, colors, scales, rotations, scale_modifier, co
                               _p(dL_dcolor), _p(dL_ddepth), _p(dL_dalpha), _p(g["means2D"]), _p(g["conic"]),
                               _p(g["opacity"]), _p(g["colors"]), _p(g["depths"]), _p(g["means3D"]), _p(g["cov3D"]),
                               _p(g["sh"]), _p(g["scales"]), _p(g["rotations"]), C.c_int(int(debug)))
-    torch.cuda.synchronize(dev)
+    if sync:
+        torch.cuda.synchronize(dev)
     if rc != 0:
         raise RuntimeError("reference backward raised")
     return g

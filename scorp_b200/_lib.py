@@ -34,6 +34,8 @@ _P = c_void_p
 SIGNATURES = {
     "gsr_last_error": (C.c_char_p, []),
     "gsr_version": (c_int, []),
+    "gsr_profile_enable": (None, [c_int]),
+    "gsr_profile_read": (c_int, [C.POINTER(c_float)]),
     "gsr_rasterize_forward": (c_int, [C.POINTER(GsrSettings), c_int, c_int] + [_P] * 7 + [_P] * 4
                               + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_backward_workspace_bytes": (c_size_t, [c_int]),

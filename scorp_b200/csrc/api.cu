@@ -24,6 +24,27 @@ int stage_check(const GsrSettings* s, cudaStream_t st, const char* what) {
     return check_cuda(cudaStreamSynchronize(st), what);
 }
 
+// ---- optional per-stage timing (bench.py's live roofline numbers) --------------------------
+// When enabled, an event is recorded on the caller's stream after every stage; gsr_profile_read
+// synchronises on the last event of each pass and returns the elapsed times.
+constexpr int PROF_RING = 64, PROF_EV = 7;
+struct StageProf {
+    bool on = false, made = false;
+    int n_fwd = 0, n_bwd = 0;                 // passes recorded since enable (ring of PROF_RING)
+    cudaEvent_t ev[PROF_RING][PROF_EV] = {};
+};
+static StageProf g_prof;
+// events: 0 start fwd, 1 after preprocess, 2 after binning, 3 after blend fwd,
+//         4 start bwd, 5 after blend bwd, 6 after preprocess bwd
+void prof_mark(int i, cudaStream_t st) {
+    if (!g_prof.on) return;
+    if (!g_prof.made) { for (auto& r : g_prof.ev) for (auto& e : r) cudaEventCreate(&e); g_prof.made = true; }
+    const int slot = (i < 4 ? g_prof.n_fwd : g_prof.n_bwd) % PROF_RING;
+    cudaEventRecord(g_prof.ev[slot][i], st);
+    if (i == 3) ++g_prof.n_fwd;
+    if (i == 6) ++g_prof.n_bwd;
+}
+
 static bool sh_count_ok(int M) { return M == 0 || M == 1 || M == 4 || M == 9 || M == 16; }
 
 }  // namespace gsr
@@ -34,6 +55,29 @@ extern "C" {
 
 const char* gsr_last_error(void) { return g_err; }
 int gsr_version(void) { return 100; }
+
+void gsr_profile_enable(int on) { g_prof.on = on != 0; g_prof.n_fwd = g_prof.n_bwd = 0; }
+int gsr_profile_read(float* ms) {
+    if (!ms) { set_error("null ms"); return GSR_EINVAL; }
+    for (int i = 0; i < GSR_PROF_STAGES; ++i) ms[i] = -1.0f;
+    if (!g_prof.made) return GSR_OK;
+    const int nf = g_prof.n_fwd < PROF_RING ? g_prof.n_fwd : PROF_RING;
+    const int nb = g_prof.n_bwd < PROF_RING ? g_prof.n_bwd : PROF_RING;
+    float acc[GSR_PROF_STAGES] = {0, 0, 0, 0, 0};
+    for (int k = 0; k < nf; ++k) {
+        if (cudaEventSynchronize(g_prof.ev[k][3]) != cudaSuccess) { set_error("event sync"); return GSR_ECUDA; }
+        for (int i = 0; i < 3; ++i) { float t = 0; cudaEventElapsedTime(&t, g_prof.ev[k][i], g_prof.ev[k][i + 1]); acc[i] += t; }
+    }
+    for (int k = 0; k < nb; ++k) {
+        if (cudaEventSynchronize(g_prof.ev[k][6]) != cudaSuccess) { set_error("event sync"); return GSR_ECUDA; }
+        float t = 0;
+        cudaEventElapsedTime(&t, g_prof.ev[k][4], g_prof.ev[k][5]); acc[3] += t;
+        cudaEventElapsedTime(&t, g_prof.ev[k][5], g_prof.ev[k][6]); acc[4] += t;
+    }
+    for (int i = 0; i < 3; ++i) if (nf) ms[i] = acc[i] / nf;
+    for (int i = 3; i < 5; ++i) if (nb) ms[i] = acc[i] / nb;
+    return GSR_OK;
+}
 
 void gsr_geom_layout(int P, int tiles, size_t off[6], size_t* total) { *total = carve_geom(nullptr, P, tiles, nullptr, off); }
 void gsr_image_layout(int W, int H, size_t off[2], size_t* total) { *total = carve_image(nullptr, W, H, nullptr, off); }
@@ -84,6 +128,7 @@ int gsr_rasterize_forward(
     const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + 16;
     if ((rc = check_cuda(cudaMemsetAsync(g.tile_count, 0, zero_bytes, st), "memset tile counters"))) return rc;
 
+    prof_mark(0, st);
     FwdArgs a;
     a.P = P; a.M = shs ? M : 0; a.D = s->sh_degree; a.W = W; a.H = H; a.gx = gx; a.gy = gy;
     a.tanfovx = s->tanfovx; a.tanfovy = s->tanfovy;
@@ -95,6 +140,7 @@ int gsr_rasterize_forward(
     a.prefiltered = s->prefiltered != 0;
     if ((rc = check_cuda(launch_preprocess(a, g, radii, st), "preprocess launch"))) return rc;
     if ((rc = stage_check(s, st, "preprocess"))) return rc;
+    prof_mark(1, st);
 
     // number of instances -> host (the one blocking point, as rasterizer_impl.cu:282)
     uint32_t n_host = 0;
@@ -109,8 +155,10 @@ int gsr_rasterize_forward(
 
     if ((rc = check_cuda(launch_binning(P, gx, gy, N, g, radii, img, bin, st), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
+    prof_mark(2, st);
     if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st),
                          "render forward launch"))) return rc;
+    prof_mark(3, st);
     return stage_check(s, st, "render forward");
 }
 
@@ -144,12 +192,14 @@ int gsr_rasterize_backward(
 
     float* acc = (float*)workspace;
     int rc;
+    prof_mark(4, st);
     if ((rc = check_cuda(cudaMemsetAsync(acc, 0, (size_t)P * ACC_STRIDE * sizeof(float), st), "memset accumulators"))) return rc;
     if (R > 0) {
         if ((rc = check_cuda(launch_render_backward(W, H, gx, gy, g, img, bin, s->bg, out_alpha, dL_dout_color,
                                                     dL_dout_depth, dL_dout_alpha, acc, st), "render backward launch"))) return rc;
         if ((rc = stage_check(s, st, "render backward"))) return rc;
     }
+    prof_mark(5, st);
     BwdArgs b;
     b.P = P; b.M = shs ? M : 0; b.D = s->sh_degree; b.W = W; b.H = H;
     b.tanfovx = s->tanfovx; b.tanfovy = s->tanfovy;
@@ -163,6 +213,7 @@ int gsr_rasterize_backward(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
+    prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");
 }
 

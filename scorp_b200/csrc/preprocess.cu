@@ -154,7 +154,9 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
 #pragma unroll
                 for (int k = 0; k < 6; ++k) c3[k] = __ldg(a.cov3D_precomp + 6 * idx + k);
             } else {
-                const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+                // scalar loads: the caller's tensor may be a view at any 4-byte offset
+                const float* qp = a.rotations + 4 * (size_t)idx;
+                const float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
                 cov3d_from_scale_rot(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2),
                                      a.scale_modifier, q.x, q.y, q.z, q.w, c3);
 #pragma unroll

@@ -177,7 +177,8 @@ preprocess_backward_kernel(BwdArgs a) {
 
         // ---- cov3D -> scale, rotation (backward.cu:278-341)
         if (!a.cov_precomp) {
-            const float4 q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+            const float* qp = a.rotations + 4 * (size_t)idx;
+            const float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
             const float r = q.x, x = q.y, y = q.z, z = q.w;
             const V3 s = a.scale_modifier * ld3(a.scales + 3 * idx);
             // rows of R-hat (R-hat(row,col) = glm R[col][row])
@@ -210,7 +211,8 @@ preprocess_backward_kernel(BwdArgs a) {
 #pragma unroll
     for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
     st3(a.dL_dscales + 3 * idx, dscale);
-    reinterpret_cast<float4*>(a.dL_drotations)[idx] = drot;
+    float* dq = a.dL_drotations + 4 * (size_t)idx;     // scalar: output may sit at any 4-byte offset
+    dq[0] = drot.x; dq[1] = drot.y; dq[2] = drot.z; dq[3] = drot.w;
 }
 
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st) {

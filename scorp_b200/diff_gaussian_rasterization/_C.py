@@ -119,13 +119,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     dL_dout_color = _f32c(dL_dout_color, dev); dL_dout_depth = _f32c(dL_dout_depth, dev)
     dL_dout_alpha = _f32c(dL_dout_alpha, dev); alpha = _f32c(alpha, dev)
 
-    # one arena for all gradients (fully written by the library: no zero fill needed)
-    widths = (3, 3, 1, 3, 6, 3 * M, 3, 4)
+    # One arena for all gradients (fully written by the library: no zero fill needed). The five
+    # parameter gradients come first and are contiguous, so a view-sharded trainer can sum them
+    # across ranks with ONE allreduce over arena[:P * PARAM_GRAD_FLOATS(M)].
+    widths = (3, 3 * M, 1, 3, 4, 3, 3, 6)      # means3D, sh, opacity, scales, rotations | means2D, colors, cov3D
     flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
     outs, o = [], 0
     for w in widths:
         outs.append(flat[o:o + P * w]); o += P * w
-    g_m2d, g_col, g_op, g_m3d, g_cov, g_sh, g_sc, g_rot = outs
+    g_m3d, g_sh, g_op, g_sc, g_rot, g_m2d, g_col, g_cov = outs
     if P != 0:
         ws_bytes = lib.gsr_backward_workspace_bytes(P)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -141,6 +143,20 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         _lib.check(rc, "gsr_rasterize_backward")
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),
             g_sh.view(P, M, 3), g_sc.view(P, 3), g_rot.view(P, 4))
+
+
+def param_grad_floats(M: int) -> int:
+    """floats per Gaussian at the head of the gradient arena: means3D, sh, opacity, scales, rotations."""
+    return 3 + 3 * M + 1 + 3 + 4
+
+
+def grad_arena(grad_means3D: torch.Tensor) -> torch.Tensor:
+    """The flat arena a backward result lives in (its first P*param_grad_floats(M) floats are the
+    parameter gradients)."""
+    base = grad_means3D._base
+    while base is not None and base._base is not None:
+        base = base._base
+    return base
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):
