@@ -39,6 +39,7 @@ from scorp_b200 import synth
 
 METRIC = "3dgs_rasterizer_fwd_bwd_throughput"
 UNIT = "Mpix/s"
+PRIME = 8       # untimed set-up iterations of each arm before its warm-up (allocator growth, lazy module init)
 
 
 def parse():
@@ -222,9 +223,18 @@ def run_ours(args, rank, world, local):
     h_out = torch.empty(1, dtype=torch.float32).pin_memory()
     hw = H * W
 
+    copy_stream = torch.cuda.Stream(dev)
+    d_gr_buf = torch.empty_like(h_grads, device=dev)
+
     def step_e2e():
+        # camera first (the forward needs it); the image-shaped upstream gradients are only needed by
+        # the backward, so their H2D runs on a copy stream underneath the forward
+        main = torch.cuda.current_stream(dev)
         d_cam = h_cam.to(dev, non_blocking=True)
-        d_gr = h_grads.to(dev, non_blocking=True)
+        copy_stream.wait_stream(main)
+        with torch.cuda.stream(copy_stream):
+            d_gr_buf.copy_(h_grads, non_blocking=True)
+        d_gr = d_gr_buf
         rs = dgr.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, d_cam[35:38], 1.0,
                                                d_cam[0:16].view(4, 4), d_cam[16:32].view(4, 4), sc.sh_degree,
                                                d_cam[32:35], False, False)
@@ -233,6 +243,7 @@ def run_ours(args, rank, world, local):
         color, radii, depth, alpha = dgr.GaussianRasterizer(rs)(
             means3D=params[0], means2D=torch.zeros_like(params[0], requires_grad=True), shs=params[1],
             opacities=params[2], scales=params[3], rotations=params[4])
+        main.wait_stream(copy_stream)
         torch.autograd.backward([color, depth, alpha],
                                 [d_gr[:3 * hw].view(3, H, W), d_gr[3 * hw:4 * hw].view(1, H, W), d_gr[4 * hw:].view(1, H, W)])
         if world > 1:
@@ -240,6 +251,8 @@ def run_ours(args, rank, world, local):
         h_out.copy_(color.sum().view(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)
 
+    for _ in range(PRIME):          # setup, not warm-up: caching-allocator growth for the autograd path
+        step_e2e()
     ms_e2e_total, _ = time_steps(step_e2e, args.steps, args.warmup, world)
     ms_e2e = ms_e2e_total / args.steps
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e, stages=list(st), clocks=clocks,
@@ -292,6 +305,8 @@ def run_reference(args, rank, world, local):
         h_out.copy_(f["color"].sum().view(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
+    for _ in range(PRIME):
+        step_e2e()
     ms_e2e_total, _ = time_steps(step_e2e, args.steps, args.warmup, world)
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=f["num_rendered"], ms_step=ms_total / args.steps,
                 ms_e2e=ms_e2e_total / args.steps, stages=None, clocks=clocks,
@@ -326,7 +341,7 @@ def main():
                    "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"},
         "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": r["d2h"],
-                "note": "public API + autograd; camera and upstream-gradient maps copied from pinned host memory, scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
+                "note": "public API + autograd; camera and upstream-gradient maps copied from pinned host memory each step (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
     }
     if args.impl == "ours":

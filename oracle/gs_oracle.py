@@ -80,6 +80,10 @@ def forward(bg, means3D, colors_precomp, opacities, scales, rotations, scale_mod
     M = 0 if shs is None else shs.shape[1]
     color = np.zeros((3, H, W), np.float32); depth = np.zeros((1, H, W), np.float32)
     alpha = np.zeros((1, H, W), np.float32); radii = np.zeros((P,), np.int32)
+    if P == 0:      # the torch glue skips the rasterizer entirely: zero images (rasterize_points.cu:83)
+        return Forward(state=None, color=color, depth=depth, alpha=alpha, radii=radii, num_rendered=0, inter={},
+                       P=0, M=M, H=H, W=W, degree=degree, scale_modifier=scale_modifier, tanfovx=tanfovx,
+                       tanfovy=tanfovy, keep={})
     st = L.gs_oracle_forward(C.c_int(P), C.c_int(degree), C.c_int(M), _p(bg), C.c_int(W), C.c_int(H), _p(means3D),
                              _p(shs), _p(colors_precomp), _p(opacities), _p(scales), C.c_float(scale_modifier),
                              _p(rotations), _p(cov3D_precomp), _p(view), _p(proj), _p(campos), C.c_float(tanfovx),

@@ -90,7 +90,7 @@ def test_oracle_edge_cases():
     f = O.forward(d["bg"], np.zeros((0, 3), np.float32), None, np.zeros((0, 1), np.float32), np.zeros((0, 3), np.float32),
                   np.zeros((0, 4), np.float32), 1.0, None, d["viewmatrix"], d["projmatrix"], 0.6, 0.4, 32, 48,
                   np.zeros((0, 1, 3), np.float32), 0, d["campos"])
-    assert f.num_rendered == 0 and np.all(f.color == d["bg"].reshape(3, 1, 1))
+    assert f.num_rendered == 0 and float(np.abs(f.color).max()) == 0.0     # rasterize_points.cu:83
     # everything behind the camera: culled, background only
     m = d["means3D"].copy(); m[:, 2] = -3.0
     f = O.forward(d["bg"], m, None, d["opacities"], d["scales"], d["rotations"], 1.0, None, d["viewmatrix"],
