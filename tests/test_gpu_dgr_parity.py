@@ -139,7 +139,9 @@ def test_other_views_and_scale_modifier():
 def test_mark_visible_matches_reference():
     ref_cuda = _need_ref()
     from scorp_b200.diff_gaussian_rasterization import _C
-    sc = h.make("C1", P=30_000, n_views=2); cam = sc.cameras[1]
+    sc = h.make("C1", P=30_000)
+    cam = synth.make_camera(512, 512, T=(0.0, 0.0, -5.0))      # view z = world z - 5: part of the cube is behind
+    cam.viewmatrix = cam.viewmatrix.cuda(); cam.projmatrix = cam.projmatrix.cuda()
     ours = _C.mark_visible(sc.means3D, cam.viewmatrix, cam.projmatrix)
     ref = ref_cuda.dgr_mark_visible(sc.means3D, cam.viewmatrix, cam.projmatrix)
     assert torch.equal(ours, ref) and 0 < int(ours.sum()) < sc.P
