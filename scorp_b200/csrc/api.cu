@@ -153,7 +153,7 @@ int gsr_rasterize_forward(
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
     carve_binning(bbase, N, &bin);
 
-    if ((rc = check_cuda(launch_binning(P, gx, gy, N, g, radii, img, bin, st), "binning launch"))) return rc;
+    if ((rc = check_cuda(launch_binning(P, gx, gy, N, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
     if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st),

@@ -50,17 +50,20 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
 // ---- 3. scatter instances into tile segments ----------------------------------------------
 // tile_count is consumed as a cursor (atomicSub), leaving it zero.
 __global__ void __launch_bounds__(256)
-scatter_kernel(int P, int gx, int gy, const GaussRec* __restrict__ rec, const int32_t* __restrict__ radii,
+scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
+               const int32_t* __restrict__ radii,
                uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
     if (idx >= P) return;
     const int rad = radii[idx];
     if (rad <= 0) return;
-    const float4 a = __ldg(reinterpret_cast<const float4*>(rec + idx));
-    const float4 b = __ldg(reinterpret_cast<const float4*>(rec + idx) + 1);
+    // every record type starts with the pixel-space centre (x, y); the depth sits at depth_off bytes
+    const char* rp = recs + (size_t)idx * rec_stride;
+    const float2 a = __ldg(reinterpret_cast<const float2*>(rp));
+    const float depth = __ldg(reinterpret_cast<const float*>(rp + depth_off));
     uint32_t x0, y0, x1, y1;
     tile_rect(a.x, a.y, rad, gx, gy, x0, y0, x1, y1);
-    const uint64_t key = ((uint64_t)__float_as_uint(b.z) << 32) | (uint32_t)idx;
+    const uint64_t key = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
     for (uint32_t y = y0; y < y1; ++y)
         for (uint32_t x = x0; x < x1; ++x) {
             const uint32_t t = y * gx + x;
@@ -158,13 +161,15 @@ tile_sort_kernel(int tiles, const uint2* __restrict__ ranges, uint64_t* __restri
     }
 }
 
-cudaError_t launch_binning(int P, int gx, int gy, int N, const GeomState& g, const int32_t* radii,
-                           const ImageState& img, const BinningState& bin, cudaStream_t st) {
+cudaError_t launch_binning(int P, int gx, int gy, int N, const void* recs, int rec_stride, int depth_off,
+                           uint32_t* tile_count, const int32_t* radii, uint2* ranges, const BinningState& bin,
+                           cudaStream_t st) {
     const int tiles = gx * gy;
-    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, g.tile_count, img.ranges);
+    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges);
     if (N > 0) {
-        scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, g.rec, radii, g.tile_count, img.ranges, bin.scratch);
-        tile_sort_kernel<<<tiles, SORT_THREADS, 0, st>>>(tiles, img.ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+        scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
+                                                        tile_count, ranges, bin.scratch);
+        tile_sort_kernel<<<tiles, SORT_THREADS, 0, st>>>(tiles, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
     }
     return cudaGetLastError();
 }

@@ -147,8 +147,9 @@ struct FwdArgs {
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
-cudaError_t launch_binning(int P, int gx, int gy, int N, const GeomState& g, const int32_t* radii,
-                           const ImageState& img, const BinningState& bin, cudaStream_t st);
+cudaError_t launch_binning(int P, int gx, int gy, int N, const void* recs, int rec_stride, int depth_off,
+                           uint32_t* tile_count, const int32_t* radii, uint2* ranges, const BinningState& bin,
+                           cudaStream_t st);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st);

@@ -9,68 +9,10 @@
 // with an explicit rounding sequence equal to what nvcc emits for the reference; conic and rgb
 // follow the same sequences so the blend inputs are bit-identical too.
 #include "common.cuh"
+#include "sh.cuh"
 #include <cfloat>
 
 namespace gsr {
-
-constexpr float kC0 = 0.28209479177387814f;
-constexpr float kC1 = 0.4886025119029199f;
-
-struct Sh3 { float r, g, b; };
-
-// Loads coefficient k (3 floats) of one Gaussian. VEC: 48 floats were preloaded as float4s.
-template <bool VEC>
-struct ShReader {
-    const float* base;     // scalar path: pointer to this Gaussian's coefficients
-    float4 v[VEC ? 12 : 1];
-    __device__ __forceinline__ Sh3 get(int k) const {
-        if constexpr (VEC) {
-            const float* f = reinterpret_cast<const float*>(v);
-            return { f[3 * k], f[3 * k + 1], f[3 * k + 2] };
-        } else {
-            return { __ldg(base + 3 * k), __ldg(base + 3 * k + 1), __ldg(base + 3 * k + 2) };
-        }
-    }
-};
-
-__device__ __forceinline__ void sh_axpy(Sh3& acc, float w, const Sh3& c) {
-    acc.r = fmar(w, c.r, acc.r); acc.g = fmar(w, c.g, acc.g); acc.b = fmar(w, c.b, acc.b);
-}
-
-// SH -> RGB for degree D (forward.cu:20-71), same rounding sequence as the reference build.
-template <bool VEC>
-__device__ __forceinline__ Sh3 eval_sh(int D, const ShReader<VEC>& sh, float x, float y, float z) {
-    Sh3 c0 = sh.get(0);
-    Sh3 res = { mulr(c0.r, kC0), mulr(c0.g, kC0), mulr(c0.b, kC0) };
-    if (D > 0) {
-        sh_axpy(res, -mulr(y, kC1), sh.get(1));
-        sh_axpy(res,  mulr(z, kC1), sh.get(2));
-        sh_axpy(res, -mulr(x, kC1), sh.get(3));
-        if (D > 1) {
-            const float xx = mulr(x, x), yy = mulr(y, y), zz = mulr(z, z);
-            const float xy = mulr(x, y), yz = mulr(y, z), xz = mulr(x, z);
-            const float zz2 = addr(zz, zz);
-            const float xx_yy = subr(xx, yy);
-            sh_axpy(res, mulr(xy, 1.0925484305920792f), sh.get(4));
-            sh_axpy(res, mulr(yz, -1.0925484305920792f), sh.get(5));
-            sh_axpy(res, mulr(subr(subr(zz2, xx), yy), 0.31539156525252005f), sh.get(6));
-            sh_axpy(res, mulr(xz, -1.0925484305920792f), sh.get(7));
-            sh_axpy(res, mulr(xx_yy, 0.5462742152960396f), sh.get(8));
-            if (D > 2) {
-                const float t4z = subr(fmar(zz, 4.0f, -xx), yy);   // 4zz - xx - yy
-                sh_axpy(res, mulr(mulr(y, -0.5900435899266435f), fmar(xx, 3.0f, -yy)), sh.get(9));
-                sh_axpy(res, mulr(z, mulr(xy, 2.890611442640554f)), sh.get(10));
-                sh_axpy(res, mulr(mulr(y, -0.4570457994644658f), t4z), sh.get(11));
-                sh_axpy(res, mulr(mulr(z, 0.3731763325901154f), fmar(yy, -3.0f, fmar(xx, -3.0f, zz2))), sh.get(12));
-                sh_axpy(res, mulr(mulr(x, -0.4570457994644658f), t4z), sh.get(13));
-                sh_axpy(res, mulr(mulr(z, 1.445305721320277f), xx_yy), sh.get(14));
-                sh_axpy(res, mulr(mulr(x, -0.5900435899266435f), fmar(yy, -3.0f, xx)), sh.get(15));
-            }
-        }
-    }
-    res.r = addr(res.r, 0.5f); res.g = addr(res.g, 0.5f); res.b = addr(res.b, 0.5f);
-    return res;
-}
 
 // Sigma = (S R)^T (S R) from scale*mod and the un-normalised quaternion (forward.cu:118-152).
 __device__ __forceinline__ void cov3d_from_scale_rot(float sx, float sy, float sz, float mod,

@@ -6,79 +6,9 @@
 // computeColorFromSH backward (:20-139) and computeCov3D backward (:278-341), plus the ten
 // torch::zeros of RasterizeGaussiansBackwardCUDA (rasterize_points.cu:158-167).
 #include "common.cuh"
+#include "sh.cuh"
 
 namespace gsr {
-
-struct V3 { float x, y, z; };
-__device__ __forceinline__ V3 operator+(V3 a, V3 b) { return { a.x + b.x, a.y + b.y, a.z + b.z }; }
-__device__ __forceinline__ V3 operator*(float s, V3 a) { return { s * a.x, s * a.y, s * a.z }; }
-__device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
-
-__device__ __forceinline__ V3 ld3(const float* p) { return { __ldg(p), __ldg(p + 1), __ldg(p + 2) }; }
-__device__ __forceinline__ void st3(float* p, V3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
-
-// SH backward (backward.cu:20-139). Writes dL_dsh[0..M) (zeros beyond the active degree) and
-// returns the colour-induced part of dL_dmean.
-__device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict__ sh, V3 pos, V3 campos,
-                                          V3 dRGB, float* __restrict__ dsh) {
-    const V3 dir_orig = { pos.x - campos.x, pos.y - campos.y, pos.z - campos.z };
-    const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
-    const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
-    const float C1 = 0.4886025119029199f;
-    const float C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
-    const float C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
-                          -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
-    V3 gx = { 0, 0, 0 }, gy = { 0, 0, 0 }, gz = { 0, 0, 0 };   // dRGB/dx, /dy, /dz
-    float basis[16];
-    basis[0] = 0.28209479177387814f;
-    int used = 1;
-    if (D > 0) {
-        basis[1] = -C1 * y; basis[2] = C1 * z; basis[3] = -C1 * x;
-        gx = -C1 * ld3(sh + 9); gy = -C1 * ld3(sh + 3); gz = C1 * ld3(sh + 6);
-        used = 4;
-        if (D > 1) {
-            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            basis[4] = C2[0] * xy; basis[5] = C2[1] * yz; basis[6] = C2[2] * (2.f * zz - xx - yy);
-            basis[7] = C2[3] * xz; basis[8] = C2[4] * (xx - yy);
-            const V3 s4 = ld3(sh + 12), s5 = ld3(sh + 15), s6 = ld3(sh + 18), s7 = ld3(sh + 21), s8 = ld3(sh + 24);
-            gx = gx + (C2[0] * y) * s4 + (C2[2] * 2.f * -x) * s6 + (C2[3] * z) * s7 + (C2[4] * 2.f * x) * s8;
-            gy = gy + (C2[0] * x) * s4 + (C2[1] * z) * s5 + (C2[2] * 2.f * -y) * s6 + (C2[4] * 2.f * -y) * s8;
-            gz = gz + (C2[1] * y) * s5 + (C2[2] * 2.f * 2.f * z) * s6 + (C2[3] * x) * s7;
-            used = 9;
-            if (D > 2) {
-                basis[9] = C3[0] * y * (3.f * xx - yy); basis[10] = C3[1] * xy * z;
-                basis[11] = C3[2] * y * (4.f * zz - xx - yy); basis[12] = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                basis[13] = C3[4] * x * (4.f * zz - xx - yy); basis[14] = C3[5] * z * (xx - yy);
-                basis[15] = C3[6] * x * (xx - 3.f * yy);
-                const V3 s9 = ld3(sh + 27), s10 = ld3(sh + 30), s11 = ld3(sh + 33), s12 = ld3(sh + 36),
-                         s13 = ld3(sh + 39), s14 = ld3(sh + 42), s15 = ld3(sh + 45);
-                gx = gx + (C3[0] * 3.f * 2.f * xy) * s9 + (C3[1] * yz) * s10 + (C3[2] * -2.f * xy) * s11
-                        + (C3[3] * -3.f * 2.f * xz) * s12 + (C3[4] * (-3.f * xx + 4.f * zz - yy)) * s13
-                        + (C3[5] * 2.f * xz) * s14 + (C3[6] * 3.f * (xx - yy)) * s15;
-                gy = gy + (C3[0] * 3.f * (xx - yy)) * s9 + (C3[1] * xz) * s10 + (C3[2] * (-3.f * yy + 4.f * zz - xx)) * s11
-                        + (C3[3] * -3.f * 2.f * yz) * s12 + (C3[4] * -2.f * xy) * s13 + (C3[5] * -2.f * yz) * s14
-                        + (C3[6] * -3.f * 2.f * xy) * s15;
-                gz = gz + (C3[1] * xy) * s10 + (C3[2] * 4.f * 2.f * yz) * s11 + (C3[3] * 3.f * (2.f * zz - xx - yy)) * s12
-                        + (C3[4] * 4.f * 2.f * xz) * s13 + (C3[5] * (xx - yy)) * s14;
-                used = 16;
-            }
-        }
-    }
-    for (int k = 0; k < M; ++k) {
-        const float bk = (k < used) ? basis[k < 16 ? k : 15] : 0.0f;
-        st3(dsh + 3 * k, bk * dRGB);
-    }
-    // through the normalisation of the view direction (dnormvdv, auxiliary.h:107-117)
-    const V3 ddir = { dot(gx, dRGB), dot(gy, dRGB), dot(gz, dRGB) };
-    const V3 v = dir_orig;
-    const float sum2 = dot(v, v);
-    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
-    V3 dmean;
-    dmean.x = ((sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * invsum32;
-    dmean.y = (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32;
-    dmean.z = (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32;
-    return dmean;
-}
 
 __global__ void __launch_bounds__(256)
 preprocess_backward_kernel(BwdArgs a) {

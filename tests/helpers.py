@@ -108,3 +108,84 @@ def close(a, b, rtol=1e-4, atol_scale=1e-6):
 
 def make(name, device="cuda", **kw):
     return synth.make_scene(name, **kw).to(device)
+
+
+# ---- 2DGS surfels ---------------------------------------------------------------------------------
+
+def ours_surfel_forward(scene, cam, colors_precomp=None, transMat_precomp=None, scale_modifier=1.0, debug=False):
+    from scorp_b200.diff_surfel_rasterization import _C
+    shs = empty() if colors_precomp is not None else scene.shs
+    col = colors_precomp if colors_precomp is not None else empty()
+    sc = empty() if transMat_precomp is not None else scene.scales
+    rot = empty() if transMat_precomp is not None else scene.rotations
+    tm = transMat_precomp if transMat_precomp is not None else empty()
+    out = _C.rasterize_gaussians(scene.bg, scene.means3D, col, scene.opacities, sc, rot, scale_modifier, tm,
+                                 cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, shs,
+                                 scene.sh_degree, cam.campos, False, debug)
+    keys = ("num_rendered", "color", "others", "radii", "geom", "binning", "image")
+    d = dict(zip(keys, out))
+    d.update(P=scene.P, H=cam.H, W=cam.W, args=(shs, col, sc, rot, tm, scale_modifier))
+    return d
+
+
+def ours_surfel_backward(scene, cam, fwd, grads, debug=False):
+    from scorp_b200.diff_surfel_rasterization import _C
+    shs, col, sc, rot, tm, smod = fwd["args"]
+    out = _C.rasterize_gaussians_backward(scene.bg, scene.means3D, fwd["radii"], col, sc, rot, smod, tm,
+                                          cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0],
+                                          grads[1], shs, scene.sh_degree, cam.campos, fwd["geom"],
+                                          fwd["num_rendered"], fwd["binning"], fwd["image"], debug)
+    keys = ("means2D", "colors", "opacity", "means3D", "transMat", "sh", "scales", "rotations")
+    return dict(zip(keys, out))
+
+
+def ours_surfel_intermediates(fwd):
+    lib = _lib.lib()
+    P, H, W, N = fwd["P"], fwd["H"], fwd["W"], fwd["num_rendered"]
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+    off = (C.c_size_t * 6)(); tot = C.c_size_t(0)
+    lib.gsr_surfel_geom_layout(P, tiles, off, C.byref(tot))
+    g = fwd["geom"]
+    rec = g[off[0]: off[0] + 96 * P].view(torch.float32).view(P, 24)
+    res = dict(means2D=rec[:, 0:2], transMat=rec[:, 2:11], normal_opacity=rec[:, 11:15], rgb=rec[:, 15:18],
+               depths=rec[:, 18], box=rec[:, 20:24],
+               clamped=g[off[1]: off[1] + P],
+               tiles_touched=g[off[2]: off[2] + 4 * P].view(torch.int32))
+    ioff = (C.c_size_t * 4)()
+    lib.gsr_surfel_image_layout(W, H, ioff, C.byref(tot))
+    im = fwd["image"]
+    stride = ioff[2] - ioff[1]
+    plane = lambda k, dt: im[ioff[1] + k * stride: ioff[1] + k * stride + 4 * H * W].view(dt).view(H, W)
+    res["ranges"] = im[ioff[0]: ioff[0] + 8 * tiles].view(torch.int32).view(tiles, 2)
+    res["n_contrib"] = plane(0, torch.int32); res["median_contrib"] = plane(1, torch.int32)
+    res["final_T"] = plane(2, torch.float32); res["M1"] = plane(3, torch.float32); res["M2"] = plane(4, torch.float32)
+    boff = (C.c_size_t * 3)()
+    lib.gsr_binning_layout(N, boff, C.byref(tot))
+    b = fwd["binning"]
+    if N > 0:
+        res["point_list"] = b[boff[0]: boff[0] + 4 * N].view(torch.int32)
+        res["point_list_keys"] = b[boff[1]: boff[1] + 8 * N].view(torch.int64)
+    else:
+        res["point_list"] = torch.zeros(0, dtype=torch.int32, device=g.device)
+        res["point_list_keys"] = torch.zeros(0, dtype=torch.int64, device=g.device)
+    return res
+
+
+def ref_surfel_forward(scene, cam, colors_precomp=None, transMat_precomp=None, scale_modifier=1.0):
+    from oracle import ref_cuda
+    shs = None if colors_precomp is not None else scene.shs
+    sc = None if transMat_precomp is not None else scene.scales
+    rot = None if transMat_precomp is not None else scene.rotations
+    out = ref_cuda.dsr_forward(scene.bg, scene.means3D, colors_precomp, scene.opacities, sc, rot, scale_modifier,
+                               transMat_precomp, cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H,
+                               cam.W, shs, scene.sh_degree, cam.campos)
+    out["args"] = (shs, colors_precomp, sc, rot, transMat_precomp, scale_modifier)
+    return out
+
+
+def ref_surfel_backward(scene, cam, fwd, grads):
+    from oracle import ref_cuda
+    shs, col, sc, rot, tm, smod = fwd["args"]
+    return ref_cuda.dsr_backward(fwd, scene.bg, scene.means3D, col, sc, rot, smod, tm, cam.viewmatrix,
+                                 cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0], grads[1], shs,
+                                 scene.sh_degree, cam.campos)
