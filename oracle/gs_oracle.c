@@ -44,7 +44,7 @@ typedef struct GsOracle {
 } GsOracle;
 
 /* forward.cu:20-71 */
-static vec3 computeColorFromSH(int idx, int deg, int max_coeffs, const float* means, const float* campos,
+vec3 orc_computeColorFromSH(int idx, int deg, int max_coeffs, const float* means, const float* campos,
                                const float* shs, uint8_t* clamped) {
     vec3 pos = v3(means[3 * idx], means[3 * idx + 1], means[3 * idx + 2]);
     vec3 dir = v3(pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]);
@@ -214,7 +214,7 @@ GsOracle* gs_oracle_forward(int P, int D, int M, const float* bg, int W, int H,
         getRect(pix_x, pix_y, (int)my_radius, s->gx, s->gy, &x0, &y0, &x1, &y1);
         if ((x1 - x0) * (y1 - y0) == 0) continue;
         if (colors_precomp == NULL) {
-            vec3 c = computeColorFromSH(idx, D, M, means3D, campos, shs, s->clamped);
+            vec3 c = orc_computeColorFromSH(idx, D, M, means3D, campos, shs, s->clamped);
             s->rgb[3 * idx] = c.x; s->rgb[3 * idx + 1] = c.y; s->rgb[3 * idx + 2] = c.z;
         }
         s->depths[idx] = p_view.z;
@@ -352,7 +352,7 @@ static void render_tile_backward(const GsOracle* s, int tile, const float* bg, c
 }
 
 /* backward.cu:20-139 */
-static void sh_backward(int idx, int deg, int max_coeffs, const float* means, const float* campos, const float* shs,
+void orc_sh_backward(int idx, int deg, int max_coeffs, const float* means, const float* campos, const float* shs,
                         const uint8_t* clamped, const float* dL_dcolor, float* dL_dmeans, float* dL_dshs) {
     vec3 pos = v3(means[3 * idx], means[3 * idx + 1], means[3 * idx + 2]);
     vec3 dir_orig = v3(pos.x - campos[0], pos.y - campos[1], pos.z - campos[2]);
@@ -550,7 +550,7 @@ void gs_oracle_backward(const GsOracle* s, int D, int M, const float* bg,
         dL_dmean3D[3 * idx + 0] += (view[2] - view[3] * mul3) * dL_ddepth[idx];
         dL_dmean3D[3 * idx + 1] += (view[6] - view[7] * mul3) * dL_ddepth[idx];
         dL_dmean3D[3 * idx + 2] += (view[10] - view[11] * mul3) * dL_ddepth[idx];
-        if (shs) sh_backward(idx, D, M, means3D, campos, shs, s->clamped, dL_dcolor, dL_dmean3D, dL_dsh);
+        if (shs) orc_sh_backward(idx, D, M, means3D, campos, shs, s->clamped, dL_dcolor, dL_dmean3D, dL_dsh);
         if (scales) cov3d_backward(idx, scales + 3 * (size_t)idx, scale_modifier, rotations + 4 * (size_t)idx, dL_dcov3D, dL_dscale, dL_drot);
     }
 }

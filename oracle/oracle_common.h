@@ -115,4 +115,12 @@ static inline void sort_pairs_stable(uint64_t* keys, uint32_t* vals, size_t n, i
     free(k2); free(v2);
 }
 
+
+/* shared by the 3DGS and the surfel restatements (the two reference submodules carry identical
+ * copies: forward.cu:20-71, backward.cu:20-139); defined in gs_oracle.c. clamped: 3 bytes per Gaussian. */
+vec3 orc_computeColorFromSH(int idx, int deg, int max_coeffs, const float* means, const float* campos,
+                            const float* shs, uint8_t* clamped);
+void orc_sh_backward(int idx, int deg, int max_coeffs, const float* means, const float* campos, const float* shs,
+                     const uint8_t* clamped, const float* dL_dcolor, float* dL_dmeans, float* dL_dshs);
+
 #endif

@@ -72,21 +72,26 @@ __device__ __forceinline__ void surfel_transmat(float px, float py, float pz, fl
     normal.z = view[2] * L[2][0] + view[6] * L[2][1] + view[10] * L[2][2];
 }
 
-// forward.cu:119-145 with glm's dot = (a*b).x + .y + .z and glm::max(a, b) = (a < b) ? b : a
-__device__ __forceinline__ bool surfel_aabb(const M3& T, float cutoff, float2& center, float2& extent) {
-    const float t0 = cutoff * cutoff, t1 = cutoff * cutoff, t2 = -1.0f;
-    const float d = t0 * (T.c[2][0] * T.c[2][0]) + t1 * (T.c[2][1] * T.c[2][1]) + t2 * (T.c[2][2] * T.c[2][2]);
+// forward.cu:119-145. Explicit rounding sequence = what the reference build executes (nvcc 12.9, default
+// -fmad: NVVM contracts the glm dot products, ptxas additionally fuses d's last term and reassociates
+// p*p - (q9 - w) into fma(p, p, w - q9)); verified bit-exact against the reference on the B200.
+// glm::max(a, b) compiles to FMNMX (NaN -> 1e-4).
+__device__ __forceinline__ bool surfel_aabb(const M3& T, float2& center, float2& extent) {
+    const float T20 = T.c[2][0], T21 = T.c[2][1], T22 = T.c[2][2];
+    const float d = fmar(-T22, T22, fmar(mulr(T20, T20), 9.0f, mulr(mulr(T21, T21), 9.0f)));
     if (d == 0.0f) return false;
-    const float inv = 1 / d;
-    const float f0 = inv * t0, f1 = inv * t1, f2 = inv * t2;
-    const float p_x = f0 * (T.c[0][0] * T.c[2][0]) + f1 * (T.c[0][1] * T.c[2][1]) + f2 * (T.c[0][2] * T.c[2][2]);
-    const float p_y = f0 * (T.c[1][0] * T.c[2][0]) + f1 * (T.c[1][1] * T.c[2][1]) + f2 * (T.c[1][2] * T.c[2][2]);
-    const float q_x = f0 * (T.c[0][0] * T.c[0][0]) + f1 * (T.c[0][1] * T.c[0][1]) + f2 * (T.c[0][2] * T.c[0][2]);
-    const float q_y = f0 * (T.c[1][0] * T.c[1][0]) + f1 * (T.c[1][1] * T.c[1][1]) + f2 * (T.c[1][2] * T.c[1][2]);
-    const float h0x = p_x * p_x - q_x, h0y = p_y * p_y - q_y;
-    const float mx = (1e-4f < h0x) ? h0x : 1e-4f, my = (1e-4f < h0y) ? h0y : 1e-4f;
-    center = make_float2(p_x, p_y);
-    extent = make_float2(sqrtf(mx), sqrtf(my));
+    const float inv = __frcp_rn(d);
+    const float f9 = mulr(inv, 9.0f);
+    float p[2], h0[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const float a0 = T.c[k][0], a1 = T.c[k][1], a2 = T.c[k][2];
+        p[k] = fmar(-mulr(a2, T22), inv, fmar(f9, mulr(a0, T20), mulr(f9, mulr(a1, T21))));
+        const float q9 = fmar(f9, mulr(a0, a0), mulr(f9, mulr(a1, a1)));
+        h0[k] = fmar(p[k], p[k], fmar(mulr(a2, a2), inv, -q9));
+    }
+    center = make_float2(p[0], p[1]);
+    extent = make_float2(__fsqrt_rn(fmaxf(h0[0], 1e-4f)), __fsqrt_rn(fmaxf(h0[1], 1e-4f)));
     return true;
 }
 
@@ -155,7 +160,7 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
             normal.x = mult * normal.x; normal.y = mult * normal.y; normal.z = mult * normal.z;
 
             float2 center, extent;
-            if (!surfel_aabb(T, 3.0f, center, extent)) break;
+            if (!surfel_aabb(T, center, extent)) break;
             const float radius = ceilf(fmaxf(fmaxf(extent.x, extent.y), 3.0f * 0.707106f));
             const int rad = (int)radius;
             uint32_t x0, y0, x1, y1;
