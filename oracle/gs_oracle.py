@@ -139,3 +139,113 @@ def mark_visible(means3D, view, proj):
     out = np.zeros((m.shape[0],), np.uint8)
     L.gs_oracle_mark_visible(C.c_int(m.shape[0]), _p(m), _p(v), _p(p), _p(out))
     return out.astype(bool)
+
+
+# ---- 2DGS surfels (oracle/surfel_oracle.c) ---------------------------------------------------------
+
+_S_ARRAYS = dict(depths=(0, np.float32, 1), means2D=(1, np.float32, 2), transMat=(2, np.float32, 9),
+                 normal_opacity=(3, np.float32, 4), rgb=(4, np.float32, 3), clamped=(5, np.uint8, 3),
+                 tiles_touched=(6, np.uint32, 1), point_offsets=(7, np.uint32, 1))
+
+
+class SurfelForward(Forward):
+    def __del__(self):
+        st = self.__dict__.get("state")
+        if st and _lib is not None:
+            try:
+                _lib.surfel_oracle_free(C.c_void_p(st))
+            except Exception:
+                pass
+            self.state = None
+
+
+def _slib():
+    L = lib()
+    if not getattr(L, "_surfel_bound", False):
+        L.surfel_oracle_forward.restype = C.c_void_p
+        L.surfel_oracle_num_rendered.restype = C.c_int64
+        L.surfel_oracle_num_rendered.argtypes = [C.c_void_p]
+        L.surfel_oracle_array.restype = C.c_void_p
+        L.surfel_oracle_array.argtypes = [C.c_void_p, C.c_int]
+        L.surfel_oracle_free.argtypes = [C.c_void_p]
+        L._surfel_bound = True
+    return L
+
+
+def surfel_forward(bg, means3D, colors_precomp, opacities, scales, rotations, scale_modifier, transMat_precomp,
+                   view, proj, tanfovx, tanfovy, H, W, shs, degree, campos, threads=None):
+    """Restatement of the surfel Rasterizer::forward: color[3,H,W], others[7,H,W], radii + every intermediate."""
+    L = _slib()
+    if threads:
+        os.environ["OMP_NUM_THREADS"] = str(threads)
+    bg, means3D, colors_precomp, opacities = _f(bg), _f(means3D), _f(colors_precomp), _f(opacities)
+    scales, rotations, transMat_precomp, view, proj, campos, shs = map(
+        _f, (scales, rotations, transMat_precomp, view, proj, campos, shs))
+    P = 0 if means3D is None else means3D.shape[0]
+    M = 0 if shs is None else shs.shape[1]
+    color = np.zeros((3, H, W), np.float32); others = np.zeros((7, H, W), np.float32)
+    radii = np.zeros((P,), np.int32)
+    base = dict(P=P, M=M, H=H, W=W, degree=degree, scale_modifier=scale_modifier, tanfovx=tanfovx, tanfovy=tanfovy)
+    if P == 0:
+        return SurfelForward(state=None, color=color, others=others, radii=radii, num_rendered=0, inter={}, keep={}, **base)
+    st = L.surfel_oracle_forward(C.c_int(P), C.c_int(degree), C.c_int(M), _p(bg), C.c_int(W), C.c_int(H), _p(means3D),
+                                 _p(shs), _p(colors_precomp), _p(opacities), _p(scales), C.c_float(scale_modifier),
+                                 _p(rotations), _p(transMat_precomp), _p(view), _p(proj), _p(campos),
+                                 C.c_float(tanfovx), C.c_float(tanfovy), _p(color), _p(others), _p(radii))
+    if not st:
+        raise RuntimeError("surfel oracle forward failed (need shs or colors_precomp)")
+    N = int(L.surfel_oracle_num_rendered(st))
+    tiles = ((W + 15) // 16) * ((H + 15) // 16)
+
+    def arr(which, dtype, shape):
+        n = int(np.prod(shape))
+        if n == 0:
+            return np.zeros(shape, dtype)
+        ptr = L.surfel_oracle_array(st, which)
+        buf = (C.c_char * (n * np.dtype(dtype).itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape).copy()
+
+    inter = {k: arr(w, dt, (P, c) if c > 1 else (P,)) for k, (w, dt, c) in _S_ARRAYS.items()}
+    inter["point_list_keys"] = arr(8, np.uint64, (N,))
+    inter["point_list"] = arr(9, np.uint32, (N,))
+    inter["ranges"] = arr(10, np.uint32, (tiles, 2))
+    inter["n_contrib"] = arr(11, np.uint32, (H, W)); inter["median_contrib"] = arr(12, np.uint32, (H, W))
+    inter["final_T"] = arr(13, np.float32, (H, W)); inter["M1"] = arr(14, np.float32, (H, W))
+    inter["M2"] = arr(15, np.float32, (H, W))
+    keep = dict(bg=bg, means3D=means3D, colors_precomp=colors_precomp, scales=scales, rotations=rotations,
+                transMat_precomp=transMat_precomp, view=view, proj=proj, campos=campos, shs=shs)
+    return SurfelForward(state=st, color=color, others=others, radii=radii, num_rendered=N, inter=inter, keep=keep, **base)
+
+
+def surfel_backward(fwd: SurfelForward, dL_dcolor, dL_dothers):
+    L = _slib()
+    k = fwd.keep
+    P, M = fwd.P, fwd.M
+    g = dict(means2D=np.zeros((P, 3), np.float32), normal=np.zeros((P, 3), np.float32),
+             opacity=np.zeros((P, 1), np.float32), colors=np.zeros((P, 3), np.float32),
+             means3D=np.zeros((P, 3), np.float32), transMat=np.zeros((P, 9), np.float32),
+             sh=np.zeros((P, M, 3), np.float32), scales=np.zeros((P, 2), np.float32),
+             rotations=np.zeros((P, 4), np.float32))
+    if P == 0:
+        return g
+    dc, do = _f(dL_dcolor), _f(dL_dothers)
+    L.surfel_oracle_backward(C.c_void_p(fwd.state), C.c_int(fwd.degree), C.c_int(M), _p(k["bg"]), _p(k["means3D"]),
+                             _p(k["shs"]), _p(k["colors_precomp"]), _p(k["scales"]), C.c_float(fwd.scale_modifier),
+                             _p(k["rotations"]), _p(k["transMat_precomp"]), _p(k["view"]), _p(k["proj"]),
+                             _p(k["campos"]), C.c_float(fwd.tanfovx), C.c_float(fwd.tanfovy), _p(dc), _p(do),
+                             _p(g["means2D"]), _p(g["normal"]), _p(g["opacity"]), _p(g["colors"]), _p(g["means3D"]),
+                             _p(g["transMat"]), _p(g["sh"]) if M else None, _p(g["scales"]), _p(g["rotations"]))
+    return g
+
+
+# ---- simple-knn (oracle/knn_oracle.c) ---------------------------------------------------------------
+
+def knn_dist2(points, brute=False):
+    """Restatement of SimpleKNN::knn (Morton order + 1024-point boxes), or the exhaustive cross-check."""
+    L = lib()
+    pts = _f(points)
+    P = 0 if pts is None else pts.shape[0]
+    out = np.zeros((P,), np.float32)
+    if P:
+        (L.knn_oracle_brute if brute else L.knn_oracle)(C.c_int(P), _p(pts), _p(out))
+    return out
