@@ -50,6 +50,7 @@ def parse():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", default="C2", choices=list(synth.CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--views-per-rank", type=int, default=0, help="views each rank renders per step (0: the config's default)")
     return ap.parse_args()
 
 
@@ -148,8 +149,16 @@ def time_steps(step, K, W, world, sampler=None):
     return float(ms.item()), clocks
 
 
-def stage_bytes(P, M, Pvis, N, W, H):
+def stage_bytes(P, M, Pvis, N, W, H, surfel=False):
     """Algorithmic bytes per launch group (DESIGN.md 'Kernels')."""
+    if surfel:
+        return {
+            "preprocess_fwd": P * (40 + 12 * M) + Pvis * 87,
+            "binning": 8 * P + 44 * N,
+            "blend_fwd": 64 * N + 60 * W * H,
+            "blend_bwd": 2 * 76 * Pvis + 68 * N + (60 + 40) * W * H,
+            "preprocess_bwd": Pvis * ((76 + 36 + 40 + 12 * M) + (12 + 8 + 16 + 36 + 12 + 12 * M)),
+        }
     return {
         "preprocess_fwd": P * (44 + 12 * M) + Pvis * 75,
         "binning": 8 * P + 44 * N,
@@ -160,157 +169,251 @@ def stage_bytes(P, M, Pvis, N, W, H):
 
 
 STAGES = ["preprocess_fwd", "binning", "blend_fwd", "blend_bwd", "preprocess_bwd"]
+STAGE_KERNEL = {"blend_bwd": "render_backward", "blend_fwd": "render_forward", "preprocess_bwd": "preprocess_backward",
+                "preprocess_fwd": "preprocess", "binning": "scatter+tile_sort"}
+
+
+def ncu_traffic(cfg_name, stage):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the stage's dominant kernel, from the committed
+    `ncu --set full` capture (profiles/ncu_traffic.json, written by tools/ncu_summary.py); None when not captured."""
+    p = ROOT / "profiles" / "ncu_traffic.json"
+    try:
+        return json.loads(p.read_text()).get(cfg_name, {}).get(stage)
+    except Exception:
+        return None
+
+
+def out_channels(surfel):
+    return (3, 7) if surfel else (3, 1, 1)
 
 
 def cpu_baseline(cfg_name, W, H):
     """One fwd+bwd iteration of the workload through the CPU oracle port, all host cores."""
     from oracle import gs_oracle as O
+    surfel = synth.CONFIGS[cfg_name]["surfel"]
     sc = synth.make_scene(cfg_name); cam = sc.cameras[0]
-    grads = synth.upstream_grads(cam.W, cam.H, 1)
+    grads = synth.upstream_grads(cam.W, cam.H, 1, channels=out_channels(surfel))
     cores = os.cpu_count() or 1
     os.environ["OMP_NUM_THREADS"] = str(cores)
     t0 = time.perf_counter()
-    f = O.forward(sc.bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, cam.viewmatrix,
-                  cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, cam.campos)
-    O.backward(f, *grads)
+    fn_f, fn_b = (O.surfel_forward, O.surfel_backward) if surfel else (O.forward, O.backward)
+    f = fn_f(sc.bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, cam.viewmatrix,
+             cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, cam.campos)
+    fwd_only = synth.CONFIGS[cfg_name].get("forward_only", False)
+    if not fwd_only:
+        fn_b(f, *grads)
     dt = time.perf_counter() - t0
+    src = "oracle/surfel_oracle.c" if surfel else "oracle/gs_oracle.c"
     return {"value": (W * H / 1e6) / dt, "unit": UNIT, "cores": cores, "kind": "port",
             "ms_per_step": dt * 1e3,
-            "sample": f"1 fwd+bwd iteration of the full {cfg_name} workload (oracle/gs_oracle.c, OpenMP)"}
+            "sample": f"1 {'forward' if fwd_only else 'fwd+bwd'} iteration (one view) of the full {cfg_name} workload ({src}, OpenMP)"}
 
 
-def run_ours(args, rank, world, local):
-    from scorp_b200 import _lib
-    import scorp_b200.diff_gaussian_rasterization as dgr
-    from scorp_b200.diff_gaussian_rasterization import _C
-    lib = _lib.lib()
-    dev = torch.device("cuda", local)
-    n_views = max(world, 1)
-    sc = synth.make_scene(args.config, n_views=n_views).to(dev)
-    cam = sc.cameras[rank % n_views]
-    W, H, P, M = cam.W, cam.H, sc.P, sc.shs.shape[1]
-    grads = [g.to(dev) for g in synth.upstream_grads(W, H, 1 + rank)]
-    E = torch.Tensor([])
-    nparam = _C.param_grad_floats(M) * P
+class Ours:
+    """The product through its reference-shaped `_C` level (C ABI) and through the public autograd API."""
+    name = "ours"
 
-    def step_resident():
-        out = _C.rasterize_gaussians(sc.bg, sc.means3D, E, sc.opacities, sc.scales, sc.rotations, 1.0, E,
-                                     cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, H, W, sc.shs,
-                                     sc.sh_degree, cam.campos, False, False)
-        n, color, depth, alpha, radii, geom, binning, img = out
-        g = _C.rasterize_gaussians_backward(sc.bg, sc.means3D, radii, E, sc.scales, sc.rotations, 1.0, E,
-                                            cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0],
-                                            grads[1], grads[2], sc.shs, sc.sh_degree, cam.campos, geom, n, binning,
-                                            img, alpha, False)
-        if world > 1:
-            dist.all_reduce(_C.grad_arena(g[3])[:nparam])
-        return n, radii
+    def __init__(self, surfel):
+        from scorp_b200 import _lib
+        self.surfel = surfel
+        if surfel:
+            import scorp_b200.diff_surfel_rasterization as mod
+            from scorp_b200.diff_surfel_rasterization import _C
+        else:
+            import scorp_b200.diff_gaussian_rasterization as mod
+            from scorp_b200.diff_gaussian_rasterization import _C
+        self.mod, self.C, self.lib = mod, _C, _lib.lib()
+        self.E = torch.Tensor([])
 
-    n, radii = step_resident()
-    Pvis = int((radii > 0).sum())
-    sampler = ClockSampler(local) if rank == 0 else None
-    lib.gsr_profile_enable(1)
-    ms_total, clocks = time_steps(step_resident, args.steps, args.warmup, world, sampler)
-    st = (C.c_float * 5)()
-    lib.gsr_profile_read(st)
-    lib.gsr_profile_enable(0)
-    ms_step = ms_total / args.steps
+    def fwd_bwd(self, sc, cam, bg, view, proj, campos, grads, fwd_only):
+        C_, E = self.C, self.E
+        out = C_.rasterize_gaussians(bg, sc.means3D, E, sc.opacities, sc.scales, sc.rotations, 1.0, E, view, proj,
+                                     cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, False, False)
+        if self.surfel:
+            n, color, others, radii, geom, binning, img = out
+            if fwd_only:
+                return n, radii, color, None
+            g = C_.rasterize_gaussians_backward(bg, sc.means3D, radii, E, sc.scales, sc.rotations, 1.0, E, view, proj,
+                                                cam.tanfovx, cam.tanfovy, grads[0], grads[1], sc.shs, sc.sh_degree,
+                                                campos, geom, n, binning, img, False)
+        else:
+            n, color, depth, alpha, radii, geom, binning, img = out
+            if fwd_only:
+                return n, radii, color, None
+            g = C_.rasterize_gaussians_backward(bg, sc.means3D, radii, E, sc.scales, sc.rotations, 1.0, E, view, proj,
+                                                cam.tanfovx, cam.tanfovy, grads[0], grads[1], grads[2], sc.shs,
+                                                sc.sh_degree, campos, geom, n, binning, img, alpha, False)
+        return n, radii, color, g[3]          # g[3] = dL_dmeans3D, the head of the gradient arena
 
-    # ---- end to end through the public API with host inputs
-    params = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)]
-    h_cam = torch.cat([cam.viewmatrix.flatten(), cam.projmatrix.flatten(), cam.campos, sc.bg]).cpu().pin_memory()
-    h_grads = torch.cat([g.flatten() for g in grads]).cpu().pin_memory()
-    h_out = torch.empty(1, dtype=torch.float32).pin_memory()
-    hw = H * W
+    def accumulate(self, total, g_means3D, P, M):
+        from scorp_b200 import multiview as mv
+        return mv.accumulate_param_grads(total, g_means3D, P, M, self.surfel)
 
-    copy_stream = torch.cuda.Stream(dev)
-    d_gr_buf = torch.empty_like(h_grads, device=dev)
+    def reduce(self, g, P, M):
+        """g: dL_dmeans3D of one backward (a view of its arena) or an already accumulated head."""
+        from scorp_b200 import multiview as mv
+        n = P * mv.param_grad_floats(M, self.surfel)
+        head = g if (g.dim() == 1 and g.numel() == n) else mv.arena_of(g)[:n]
+        mv.allreduce_param_grads(head)
 
-    def step_e2e():
-        # camera first (the forward needs it); the image-shaped upstream gradients are only needed by
-        # the backward, so their H2D runs on a copy stream underneath the forward
-        main = torch.cuda.current_stream(dev)
-        d_cam = h_cam.to(dev, non_blocking=True)
-        copy_stream.wait_stream(main)
-        with torch.cuda.stream(copy_stream):
-            d_gr_buf.copy_(h_grads, non_blocking=True)
-        d_gr = d_gr_buf
-        rs = dgr.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, d_cam[35:38], 1.0,
-                                               d_cam[0:16].view(4, 4), d_cam[16:32].view(4, 4), sc.sh_degree,
-                                               d_cam[32:35], False, False)
+    def e2e_step(self, sc, cam, params, d_cam, d_gr, fwd_only, world):
+        H, W, hw = cam.H, cam.W, cam.H * cam.W
+        rs = self.mod.GaussianRasterizationSettings(H, W, cam.tanfovx, cam.tanfovy, d_cam[35:38], 1.0,
+                                                    d_cam[0:16].view(4, 4), d_cam[16:32].view(4, 4), sc.sh_degree,
+                                                    d_cam[32:35], False, False)
         for p in params:
             p.grad = None
-        color, radii, depth, alpha = dgr.GaussianRasterizer(rs)(
-            means3D=params[0], means2D=torch.zeros_like(params[0], requires_grad=True), shs=params[1],
-            opacities=params[2], scales=params[3], rotations=params[4])
-        main.wait_stream(copy_stream)
-        torch.autograd.backward([color, depth, alpha],
-                                [d_gr[:3 * hw].view(3, H, W), d_gr[3 * hw:4 * hw].view(1, H, W), d_gr[4 * hw:].view(1, H, W)])
+        rast = self.mod.GaussianRasterizer(rs)
+        with torch.set_grad_enabled(not fwd_only):
+            outs = rast(means3D=params[0], means2D=torch.zeros_like(params[0], requires_grad=not fwd_only),
+                        shs=params[1], opacities=params[2], scales=params[3], rotations=params[4])
+        if fwd_only:
+            return outs[0]
+        gr = d_gr()
+        if self.surfel:
+            torch.autograd.backward([outs[0], outs[2]], [gr[:3 * hw].view(3, H, W), gr[3 * hw:].view(7, H, W)])
+        else:
+            torch.autograd.backward([outs[0], outs[2], outs[3]],
+                                    [gr[:3 * hw].view(3, H, W), gr[3 * hw:4 * hw].view(1, H, W), gr[4 * hw:].view(1, H, W)])
         if world > 1:
-            dist.all_reduce(_C.grad_arena(params[0].grad)[:nparam])
-        h_out.copy_(color.sum().view(1), non_blocking=True)
+            self.reduce(params[0].grad, sc.P, sc.shs.shape[1])
+        return outs[0]
+
+
+class Reference:
+    """The UNMODIFIED reference CUDA (oracle/_ref) with what its torch glue does around it: fresh outputs, three
+    scratch buffers and the zero-filled gradient tensors per call."""
+    name = "reference"
+
+    def __init__(self, surfel):
+        from oracle import ref_cuda
+        self.surfel, self.rc = surfel, ref_cuda
+        self.ok = ref_cuda.available("dsr" if surfel else "dgr")
+
+    def fwd_bwd(self, sc, cam, bg, view, proj, campos, grads, fwd_only):
+        rc = self.rc
+        if self.surfel:
+            f = rc.dsr_forward(bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, view, proj,
+                               cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, sync=False)
+            if fwd_only:
+                return f["num_rendered"], f["radii"], f["color"], None
+            g = rc.dsr_backward(f, bg, sc.means3D, None, sc.scales, sc.rotations, 1.0, None, view, proj, cam.tanfovx,
+                                cam.tanfovy, grads[0], grads[1], sc.shs, sc.sh_degree, campos, sync=False)
+        else:
+            f = rc.dgr_forward(bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, view, proj,
+                               cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, sync=False)
+            if fwd_only:
+                return f["num_rendered"], f["radii"], f["color"], None
+            g = rc.dgr_backward(f, bg, sc.means3D, None, sc.scales, sc.rotations, 1.0, None, view, proj, cam.tanfovx,
+                                cam.tanfovy, grads[0], grads[1], grads[2], sc.shs, sc.sh_degree, campos, sync=False)
+        return f["num_rendered"], f["radii"], f["color"], g
+
+    KEYS = ("means3D", "sh", "opacity", "scales", "rotations")
+
+    def accumulate(self, total, g, P, M):
+        if total is None:
+            return {k: g[k].clone() for k in self.KEYS}
+        for k in self.KEYS:
+            total[k].add_(g[k])
+        return total
+
+    def reduce(self, g, P, M):
+        for k in self.KEYS:      # five tensors, five collectives
+            dist.all_reduce(g[k])
+
+    def e2e_step(self, sc, cam, params, d_cam, d_gr, fwd_only, world):
+        H, W, hw = cam.H, cam.W, cam.H * cam.W
+        gr = None
+        if not fwd_only:
+            g_ = d_gr()
+            gr = ([g_[:3 * hw].view(3, H, W), g_[3 * hw:].view(7, H, W)] if self.surfel else
+                  [g_[:3 * hw].view(3, H, W), g_[3 * hw:4 * hw].view(1, H, W), g_[4 * hw:].view(1, H, W)])
+        n, radii, color, g = self.fwd_bwd(sc, cam, d_cam[35:38].contiguous(), d_cam[0:16].contiguous(),
+                                          d_cam[16:32].contiguous(), d_cam[32:35].contiguous(), gr, fwd_only)
+        if world > 1 and g is not None:
+            self.reduce(g, sc.P, sc.shs.shape[1])
+        return color
+
+
+def run(arm, args, rank, world, local):
+    cfg = synth.CONFIGS[args.config]
+    surfel, fwd_only = cfg["surfel"], cfg.get("forward_only", False)
+    dev = torch.device("cuda", local)
+    vpr = args.views_per_rank or cfg.get("views_per_rank", 1)
+    n_views = world * vpr
+    rots = synth.random_rotations(n_views, seed=128) if fwd_only else None      # stand-in for rotations_128.npz
+    sc = synth.make_scene(args.config, n_views=n_views, rotations_npz=rots).to(dev)
+    from scorp_b200 import multiview as mv
+    my_views = mv.views_for_rank(n_views, rank, world)
+    cams = [sc.cameras[v] for v in my_views]
+    W, H, P, M = cams[0].W, cams[0].H, sc.P, sc.shs.shape[1]
+    grads = [[g.to(dev) for g in synth.upstream_grads(W, H, 1 + v, channels=out_channels(surfel))] for v in my_views]
+
+    def step_resident():
+        last, total = None, None
+        for cam, gr in zip(cams, grads):
+            n, radii, color, g = arm.fwd_bwd(sc, cam, sc.bg, cam.viewmatrix, cam.projmatrix, cam.campos, gr, fwd_only)
+            last = (n, radii, g)
+            if world > 1 and not fwd_only and len(cams) > 1:
+                total = arm.accumulate(total, g, P, M)      # several views per rank: local sum first
+        # one exchange per step
+        if world > 1 and not fwd_only:
+            arm.reduce(total if total is not None else last[2], P, M)
+        return last
+
+    n, radii, _ = step_resident()
+    Pvis = int((radii > 0).sum())
+    sampler = ClockSampler(local) if rank == 0 else None
+    stages = None
+    if arm.name == "ours":
+        arm.lib.gsr_profile_enable(1)
+    ms_total, clocks = time_steps(step_resident, args.steps, args.warmup, world, sampler)
+    if arm.name == "ours":
+        st = (C.c_float * 5)()
+        arm.lib.gsr_profile_read(st)
+        arm.lib.gsr_profile_enable(0)
+        stages = list(st)
+    ms_step = ms_total / args.steps
+
+    # ---- end to end: public API (ours: GaussianRasterizer + autograd), per-view host inputs from pinned memory
+    params = [t.clone().requires_grad_(not fwd_only) for t in (sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)]
+    h_cams = [torch.cat([c.viewmatrix.flatten(), c.projmatrix.flatten(), c.campos, sc.bg]).cpu().pin_memory() for c in cams]
+    h_grads = [torch.cat([g.flatten() for g in gr]).cpu().pin_memory() for gr in grads]
+    h_out = torch.empty(1, dtype=torch.float32).pin_memory()
+    copy_stream = torch.cuda.Stream(dev)
+    d_gr_buf = torch.empty_like(h_grads[0], device=dev)
+
+    def step_e2e():
+        main = torch.cuda.current_stream(dev)
+        acc = None
+        for cam, h_cam, h_gr in zip(cams, h_cams, h_grads):
+            d_cam = h_cam.to(dev, non_blocking=True)
+            if not fwd_only:
+                # the image-shaped upstream gradients are only needed by the backward: their H2D runs on a copy
+                # stream underneath the forward
+                copy_stream.wait_stream(main)
+                with torch.cuda.stream(copy_stream):
+                    d_gr_buf.copy_(h_gr, non_blocking=True)
+
+            def d_gr():
+                main.wait_stream(copy_stream)
+                return d_gr_buf
+            color = arm.e2e_step(sc, cam, params, d_cam, d_gr, fwd_only, world)
+            s = color.sum().view(1)
+            acc = s if acc is None else acc + s
+        h_out.copy_(acc, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)
 
     for _ in range(PRIME):          # setup, not warm-up: caching-allocator growth for the autograd path
         step_e2e()
     ms_e2e_total, _ = time_steps(step_e2e, args.steps, args.warmup, world)
-    ms_e2e = ms_e2e_total / args.steps
-    return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e, stages=list(st), clocks=clocks,
-                h2d=(h_cam.numel() + h_grads.numel()) * 4, d2h=4, launches=7 * args.steps)
-
-
-def run_reference(args, rank, world, local):
-    """The UNMODIFIED reference CUDA (oracle/_ref/libref_dgr.so) with what its torch glue does around it:
-    fresh outputs, three scratch buffers and ten zero-filled gradient tensors per call."""
-    sys.path.insert(0, str(ROOT / "tests"))
-    from oracle import ref_cuda
-    if not ref_cuda.available("dgr"):
-        return None
-    dev = torch.device("cuda", local)
-    n_views = max(world, 1)
-    sc = synth.make_scene(args.config, n_views=n_views).to(dev)
-    cam = sc.cameras[rank % n_views]
-    W, H, P, M = cam.W, cam.H, sc.P, sc.shs.shape[1]
-    grads = [g.to(dev) for g in synth.upstream_grads(W, H, 1 + rank)]
-
-    def fwd_bwd(bg, view, proj, campos, gr):
-        f = ref_cuda.dgr_forward(bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, view, proj,
-                                 cam.tanfovx, cam.tanfovy, H, W, sc.shs, sc.sh_degree, campos, sync=False)
-        g = ref_cuda.dgr_backward(f, bg, sc.means3D, None, sc.scales, sc.rotations, 1.0, None, view, proj,
-                                  cam.tanfovx, cam.tanfovy, gr[0], gr[1], gr[2], sc.shs, sc.sh_degree, campos,
-                                  sync=False)
-        if world > 1:
-            for k in ("means3D", "sh", "opacity", "scales", "rotations"):
-                dist.all_reduce(g[k])
-        return f, g
-
-    def step_resident():
-        return fwd_bwd(sc.bg, cam.viewmatrix, cam.projmatrix, cam.campos, grads)
-
-    f, _ = step_resident()
-    Pvis = int((f["radii"] > 0).sum())
-    sampler = ClockSampler(local) if rank == 0 else None
-    ms_total, clocks = time_steps(step_resident, args.steps, args.warmup, world, sampler)
-    h_cam = torch.cat([cam.viewmatrix.flatten(), cam.projmatrix.flatten(), cam.campos, sc.bg]).cpu().pin_memory()
-    h_grads = torch.cat([g.flatten() for g in grads]).cpu().pin_memory()
-    h_out = torch.empty(1, dtype=torch.float32).pin_memory()
-    hw = H * W
-
-    def step_e2e():
-        d_cam = h_cam.to(dev, non_blocking=True)
-        d_gr = h_grads.to(dev, non_blocking=True)
-        gr = [d_gr[:3 * hw].view(3, H, W), d_gr[3 * hw:4 * hw].view(1, H, W), d_gr[4 * hw:].view(1, H, W)]
-        f, g = fwd_bwd(d_cam[35:38].contiguous(), d_cam[0:16].contiguous(), d_cam[16:32].contiguous(),
-                       d_cam[32:35].contiguous(), gr)
-        h_out.copy_(f["color"].sum().view(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
-
-    for _ in range(PRIME):
-        step_e2e()
-    ms_e2e_total, _ = time_steps(step_e2e, args.steps, args.warmup, world)
-    return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=f["num_rendered"], ms_step=ms_total / args.steps,
-                ms_e2e=ms_e2e_total / args.steps, stages=None, clocks=clocks,
-                h2d=(h_cam.numel() + h_grads.numel()) * 4, d2h=4, launches=0)
+    launches = 0
+    if arm.name == "ours":
+        launches = (4 if fwd_only else 7) * len(cams) * args.steps      # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd)
+    return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
+                clocks=clocks, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
+                h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
+                d2h=4, launches=launches)
 
 
 def main():
@@ -318,43 +421,55 @@ def main():
     rank, world, local = setup_dist(args)
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the rasterizer has no CPU path")
-    r = run_ours(args, rank, world, local) if args.impl == "ours" else run_reference(args, rank, world, local)
+    surfel = synth.CONFIGS[args.config]["surfel"]
+    arm = Ours(surfel) if args.impl == "ours" else Reference(surfel)
+    if args.impl == "reference" and not arm.ok:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    r = run(arm, args, rank, world, local)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    if r is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libref_dgr.so not built (needs /root/reference at build time)"}))
-        return
     W, H = r["W"], r["H"]
-    mpix = W * H / 1e6
-    value = world * mpix / (r["ms_step"] * 1e-3)
-    e2e_v = world * mpix / (r["ms_e2e"] * 1e-3)
+    mpix = W * H * r["views"] / 1e6
+    value = mpix / (r["ms_step"] * 1e-3)
+    e2e_v = mpix / (r["ms_e2e"] * 1e-3)
     peak, peak_src = peaks()
+    mode = "forward only" if r["fwd_only"] else "fwd+bwd"
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": r["ms_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "f32", "data": "synthetic (seeded scene, scorp_b200/synth.py; no dataset ships with the reference)",
-        "config": {"workload": synth.CONFIGS[args.config]["desc"], "id": args.config, "P": r["P"], "sh_coeffs": r["M"],
-                   "width": W, "height": H, "visible": r["Pvis"], "num_rendered": r["N"],
-                   "views_per_step": world, "parallelism": f"view-sharded dp{world}" if world > 1 else "single GPU",
-                   "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"},
+        "metric": METRIC if not r["fwd_only"] else "3dgs_rasterizer_fwd_throughput", "value": value, "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": r["ms_step"], "ms_per_view": r["ms_step"] / r["vpr"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic (seeded scene, scorp_b200/synth.py; no dataset ships with the reference)",
+        "config": {"workload": synth.CONFIGS[args.config]["desc"], "id": args.config, "mode": mode, "P": r["P"],
+                   "sh_coeffs": r["M"], "width": W, "height": H, "visible": r["Pvis"], "num_rendered": r["N"],
+                   "views_per_step": r["views"], "views_per_rank": r["vpr"],
+                   "parallelism": f"view-sharded dp{world}, one allreduce over the parameter-gradient arena" if world > 1 else "single GPU",
+                   "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"
+                         if r["P"] * (44 + 12 * r["M"]) > 126e6 else "working set below the 126 MB L2: numbers are L2-warm, as in the reference's own loop"},
         "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": r["d2h"],
-                "note": "public API + autograd; camera and upstream-gradient maps copied from pinned host memory each step (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
+                "note": "public API + autograd; per view the camera and the upstream-gradient maps are copied from pinned host memory (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
     }
     if args.impl == "ours":
-        sb = stage_bytes(r["P"], r["M"], r["Pvis"], r["N"], W, H)
+        sb = stage_bytes(r["P"], r["M"], r["Pvis"], r["N"], W, H, r["surfel"])
         stages = []
         for name, ms in zip(STAGES, r["stages"]):
-            gbs = sb[name] / (ms * 1e-3) / 1e9 if ms and ms > 0 else None
-            stages.append({"stage": name, "ms": ms, "algorithmic_bytes": sb[name], "achieved_gbs": gbs,
+            ms_v = ms if ms and ms > 0 else None
+            gbs = sb[name] / (ms_v * 1e-3) / 1e9 if ms_v else None
+            stages.append({"stage": name, "ms": ms_v, "algorithmic_bytes": sb[name], "achieved_gbs": gbs,
                            "frac": gbs / peak if gbs else None})
         dom = max(stages, key=lambda s: s["ms"] or 0)
         line["roofline"] = {"bound": "hbm", "kernel": dom["stage"], "achieved": dom["achieved_gbs"], "peak": peak,
-                            "peak_source": peak_src, "unit": "GB/s", "frac": dom["frac"], "traffic": None,
-                            "note": "blend stages are SM-issue bound (DESIGN.md); HBM fraction reported for the contract",
+                            "peak_source": peak_src, "unit": "GB/s", "frac": dom["frac"],
+                            "traffic": ncu_traffic(args.config, dom["stage"]),
+                            "note": "per view, last view of the step; blend stages are SM-issue bound (DESIGN.md 5), the HBM fraction is reported for the contract",
                             "stages": stages}
         if not args.no_cpu_baseline:
             try:

@@ -23,7 +23,7 @@ CONFIGS = {
                desc="large scene: 6M Gaussians, SH3, 1920x1080, 8 views sharded by camera"),
     "C4": dict(P=1_000_000, sh_degree=3, W=1297, H=840, s0=0.012, seed=1004, surfel=True,
                desc="train_2dgs: 1M surfels, SH3, 1297x840, colour + 7-channel map fwd+bwd"),
-    "C5": dict(P=200_000, sh_degree=0, W=512, H=512, s0=0.03, seed=1005, surfel=False,
+    "C5": dict(P=200_000, sh_degree=0, W=512, H=512, s0=0.03, seed=1005, surfel=False, forward_only=True, views_per_rank=16,
                desc="align_3dgs pose sweep: 200k Gaussians, SH0, 512x512, forward only x128 rotations"),
 }
 
@@ -103,6 +103,19 @@ def orbit_camera(W, H, Robj):
 def yaw(deg):
     a = math.radians(deg)
     return np.array([[math.cos(a), 0, math.sin(a)], [0, 1, 0], [-math.sin(a), 0, math.cos(a)]])
+
+
+def random_rotations(n, seed=128):
+    """n seeded uniform random rotation matrices (float64 (n,3,3)) -- a stand-in with the shape and role of the
+    reference's rotation_matrices/rotations_128.npz, which does not travel to the GPU box."""
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    q = torch.randn(n, 4, generator=g, dtype=torch.float64)
+    q = q / q.norm(dim=1, keepdim=True)
+    r, x, y, z = q.unbind(1)
+    R = torch.stack([1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], 1).view(n, 3, 3)
+    return R.numpy()
 
 
 def make_scene(name="C1", P=None, n_views=1, W=None, H=None, sh_degree=None, seed=None, random_bg=False,
