@@ -89,7 +89,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+                                          "-lms", "200", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
             self.th = threading.Thread(target=self._read, daemon=True); self.th.start()
         except Exception:
             self.proc = None
@@ -129,24 +129,37 @@ def barrier(world):
         dist.barrier()
 
 
+def prime(step, min_seconds=1.0, min_steps=PRIME):
+    """Untimed set-up before the W warm-ups: caching-allocator growth, lazy module loading, first-touch of the
+    scratch buffers. Runs at least `min_steps` steps and at least `min_seconds` of wall time."""
+    t0 = time.perf_counter(); n = 0
+    while n < min_steps or time.perf_counter() - t0 < min_seconds:
+        step(); n += 1
+        if n % 4 == 0:
+            torch.cuda.synchronize()
+    torch.cuda.synchronize()
+
+
 def time_steps(step, K, W, world, sampler=None):
-    """W warm-ups, then exactly K steps between barrier+synchronize, CUDA events, max over ranks (ms)."""
+    """W warm-ups, then exactly K steps between barrier+synchronize, CUDA events, max over ranks (ms).
+    Also returns the per-step durations (an event after every step) so host-side jitter is visible."""
+    if sampler:
+        sampler.start()        # nvidia-smi start-up (NVML init) lands in the warm-up, sampling covers the timed region
     for _ in range(W):
         step()
     torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
-    if sampler:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(K):
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    ev[0].record()
+    for k in range(K):
         step()
-    e1.record()
+        ev[k + 1].record()
     torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
-    ms = torch.tensor([e0.elapsed_time(e1)], device="cuda", dtype=torch.float64)
+    ms = torch.tensor([ev[0].elapsed_time(ev[K])], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    per = sorted(ev[k].elapsed_time(ev[k + 1]) for k in range(K))
     clocks = sampler.stop() if sampler else None
-    return float(ms.item()), clocks
+    return float(ms.item()), clocks, {"median": per[K // 2], "min": per[0], "max": per[-1]}
 
 
 def stage_bytes(P, M, Pvis, N, W, H, surfel=False):
@@ -363,11 +376,12 @@ def run(arm, args, rank, world, local):
 
     n, radii, _ = step_resident()
     Pvis = int((radii > 0).sum())
+    prime(step_resident)
     sampler = ClockSampler(local) if rank == 0 else None
     stages = None
     if arm.name == "ours":
         arm.lib.gsr_profile_enable(1)
-    ms_total, clocks = time_steps(step_resident, args.steps, args.warmup, world, sampler)
+    ms_total, clocks, per = time_steps(step_resident, args.steps, args.warmup, world, sampler)
     if arm.name == "ours":
         st = (C.c_float * 5)()
         arm.lib.gsr_profile_read(st)
@@ -404,14 +418,13 @@ def run(arm, args, rank, world, local):
         h_out.copy_(acc, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)
 
-    for _ in range(PRIME):          # setup, not warm-up: caching-allocator growth for the autograd path
-        step_e2e()
-    ms_e2e_total, _ = time_steps(step_e2e, args.steps, args.warmup, world)
+    prime(step_e2e)                 # setup, not warm-up: caching-allocator growth for the autograd path
+    ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
     launches = 0
     if arm.name == "ours":
         launches = (4 if fwd_only else 7) * len(cams) * args.steps      # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd)
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
-                clocks=clocks, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
+                clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
                 d2h=4, launches=launches)
 
@@ -443,7 +456,7 @@ def main():
     line = {
         "metric": METRIC if not r["fwd_only"] else "3dgs_rasterizer_fwd_throughput", "value": value, "unit": UNIT,
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": r["ms_step"], "ms_per_view": r["ms_step"] / r["vpr"], "higher_is_better": True, "scaling": "weak",
+        "ms_per_step": r["ms_step"], "ms_per_view": r["ms_step"] / r["vpr"], "ms_per_step_spread": r["per"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32",
         "data": "synthetic (seeded scene, scorp_b200/synth.py; no dataset ships with the reference)",
         "config": {"workload": synth.CONFIGS[args.config]["desc"], "id": args.config, "mode": mode, "P": r["P"],
@@ -452,7 +465,7 @@ def main():
                    "parallelism": f"view-sharded dp{world}, one allreduce over the parameter-gradient arena" if world > 1 else "single GPU",
                    "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"
                          if r["P"] * (44 + 12 * r["M"]) > 126e6 else "working set below the 126 MB L2: numbers are L2-warm, as in the reference's own loop"},
-        "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "h2d_bytes_per_step": r["h2d"],
+        "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "ms_per_step_spread": r["per_e2e"], "h2d_bytes_per_step": r["h2d"],
                 "d2h_bytes_per_step": r["d2h"],
                 "note": "public API + autograd; per view the camera and the upstream-gradient maps are copied from pinned host memory (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],

@@ -48,28 +48,50 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
 }
 
 // ---- 3. scatter instances into tile segments ----------------------------------------------
-// tile_count is consumed as a cursor (atomicSub), leaving it zero.
+// tile_count is consumed as a cursor (atomicSub), leaving it zero. One lane per Gaussian computes the
+// tile rectangle; rectangles of up to SMALL_RECT tiles are written by their own lane, larger ones are
+// spread over the whole warp (32 tiles per round), so one screen-filling splat does not serialise
+// hundreds of returning atomics behind a single thread.
+constexpr uint32_t SMALL_RECT = 4;
+
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
                const int32_t* __restrict__ radii,
                uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= P) return;
-    const int rad = radii[idx];
-    if (rad <= 0) return;
-    // every record type starts with the pixel-space centre (x, y); the depth sits at depth_off bytes
-    const char* rp = recs + (size_t)idx * rec_stride;
-    const float2 a = __ldg(reinterpret_cast<const float2*>(rp));
-    const float depth = __ldg(reinterpret_cast<const float*>(rp + depth_off));
-    uint32_t x0, y0, x1, y1;
-    tile_rect(a.x, a.y, rad, gx, gy, x0, y0, x1, y1);
-    const uint64_t key = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
-    for (uint32_t y = y0; y < y1; ++y)
-        for (uint32_t x = x0; x < x1; ++x) {
-            const uint32_t t = y * gx + x;
-            const uint32_t slot = atomicSub(tile_count + t, 1u) - 1u;
-            keys[ranges[t].x + slot] = key;
+    const int lane = threadIdx.x & 31;
+    uint32_t x0 = 0, y0 = 0, w = 0, cnt = 0;
+    uint64_t key = 0;
+    if (idx < P) {
+        const int rad = radii[idx];
+        if (rad > 0) {
+            // every record type starts with the pixel-space centre (x, y); the depth sits at depth_off bytes
+            const char* rp = recs + (size_t)idx * rec_stride;
+            const float2 a = __ldg(reinterpret_cast<const float2*>(rp));
+            const float depth = __ldg(reinterpret_cast<const float*>(rp + depth_off));
+            uint32_t x1, y1;
+            tile_rect(a.x, a.y, rad, gx, gy, x0, y0, x1, y1);
+            w = x1 - x0;
+            cnt = w * (y1 - y0);
+            key = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
         }
+    }
+    auto put = [&](uint32_t t, uint64_t k) {
+        const uint32_t slot = atomicSub(tile_count + t, 1u) - 1u;
+        keys[ranges[t].x + slot] = k;
+    };
+    if (cnt > 0 && cnt <= SMALL_RECT) {
+        for (uint32_t i = 0; i < cnt; ++i) put((y0 + i / w) * gx + x0 + i % w, key);
+    }
+    uint32_t big = __ballot_sync(0xffffffffu, cnt > SMALL_RECT);
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
+        const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
+        const uint64_t bkey = __shfl_sync(0xffffffffu, key, src);
+        for (uint32_t i = lane; i < bcnt; i += 32) put((by0 + i / bw) * gx + bx0 + i % bw, bkey);
+    }
 }
 
 // ---- 4. per-tile sort ---------------------------------------------------------------------

@@ -10,17 +10,28 @@
 
 namespace gsr {
 
-__global__ void __launch_bounds__(256)
+template <int M3>       // 3 * SH coefficients per Gaussian (0: colours were precomputed)
+__global__ void __launch_bounds__(SH_TILE)
 preprocess_backward_kernel(BwdArgs a) {
-    const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= a.P) return;
-    const bool vis = a.radii[idx] > 0;
+    __shared__ float s_sh[M3 ? SH_TILE * ShTile<M3>::STRIDE : 1];
+    __shared__ uint8_t s_vis[SH_TILE];
+    const size_t row0 = (size_t)blockIdx.x * SH_TILE;
+    const int nrows = min(SH_TILE, a.P - (int)row0);
+    const int idx = (int)row0 + threadIdx.x;
+    const bool valid = idx < a.P;
+    const bool vis = valid && a.radii[idx] > 0;
+    if constexpr (M3 != 0) {
+        s_vis[threadIdx.x] = vis;
+        __syncthreads();
+        sh_tile_load<M3>(a.shs, row0, nrows, s_vis, s_sh);
+        __syncthreads();
+    }
 
     float dcov[6] = { 0, 0, 0, 0, 0, 0 };
     V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, dscale = { 0, 0, 0 };
     float4 drot = { 0, 0, 0, 0 };
     float dop = 0.0f;
-    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+    float* const my_sh = s_sh + threadIdx.x * ShTile<M3>::STRIDE;      // coefficients in, gradients out (in place)
 
     if (vis) {
         const float* ac = a.acc + (size_t)idx * ACC_STRIDE;
@@ -99,10 +110,10 @@ preprocess_backward_kernel(BwdArgs a) {
         dmean.z += (v[10] - v[11] * mul3) * ddepth;
 
         // ---- colour -> SH (+ mean)
-        if (a.shs) {
+        if constexpr (M3 != 0) {
             const uint8_t cl = a.clamped[idx];
             const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
-            dmean = dmean + sh_backward(a.D, a.M, a.shs + (size_t)idx * a.M * 3, m, ld3(a.campos), dRGB, dsh);
+            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
 
         // ---- cov3D -> scale, rotation (backward.cu:278-341)
@@ -132,7 +143,11 @@ preprocess_backward_kernel(BwdArgs a) {
             drot.w = 2 * r * (N0.y - N1.x) + 2 * x * (N2.x + N0.z) + 2 * y * (N1.z + N2.y) - 4 * z * (N1.y + N0.x);
         }
     }
-    if (dsh && (!vis || !a.shs)) for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.0f;
+    if constexpr (M3 != 0) {
+        __syncthreads();
+        sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);
+    }
+    if (!valid) return;
 
     st3(a.dL_dmeans3D + 3 * idx, dmean);
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
@@ -146,7 +161,15 @@ preprocess_backward_kernel(BwdArgs a) {
 }
 
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st) {
-    preprocess_backward_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    switch (a.shs ? 3 * a.M : 0) {
+    case 0:  preprocess_backward_kernel<0><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 3:  preprocess_backward_kernel<3><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 12: preprocess_backward_kernel<12><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 27: preprocess_backward_kernel<27><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 48: preprocess_backward_kernel<48><<<blocks, SH_TILE, 0, st>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 

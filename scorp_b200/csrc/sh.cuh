@@ -71,12 +71,13 @@ __device__ __forceinline__ V3 operator*(float s, V3 a) { return { s * a.x, s * a
 __device__ __forceinline__ float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 
 __device__ __forceinline__ V3 ld3(const float* p) { return { __ldg(p), __ldg(p + 1), __ldg(p + 2) }; }
+__device__ __forceinline__ V3 ld3p(const float* p) { return { p[0], p[1], p[2] }; }      // generic (shared or global)
 __device__ __forceinline__ void st3(float* p, V3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
 
 // SH backward (backward.cu:20-139). Writes dL_dsh[0..M) (zeros beyond the active degree) and
 // returns the colour-induced part of dL_dmean.
-__device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict__ sh, V3 pos, V3 campos,
-                                          V3 dRGB, float* __restrict__ dsh) {
+__device__ __forceinline__ V3 sh_backward(int D, int M, const float* sh, V3 pos, V3 campos,
+                                          V3 dRGB, float* dsh) {
     const V3 dir_orig = { pos.x - campos.x, pos.y - campos.y, pos.z - campos.z };
     const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
     const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
@@ -90,13 +91,13 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict_
     int used = 1;
     if (D > 0) {
         basis[1] = -C1 * y; basis[2] = C1 * z; basis[3] = -C1 * x;
-        gx = -C1 * ld3(sh + 9); gy = -C1 * ld3(sh + 3); gz = C1 * ld3(sh + 6);
+        gx = -C1 * ld3p(sh + 9); gy = -C1 * ld3p(sh + 3); gz = C1 * ld3p(sh + 6);
         used = 4;
         if (D > 1) {
             const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
             basis[4] = C2[0] * xy; basis[5] = C2[1] * yz; basis[6] = C2[2] * (2.f * zz - xx - yy);
             basis[7] = C2[3] * xz; basis[8] = C2[4] * (xx - yy);
-            const V3 s4 = ld3(sh + 12), s5 = ld3(sh + 15), s6 = ld3(sh + 18), s7 = ld3(sh + 21), s8 = ld3(sh + 24);
+            const V3 s4 = ld3p(sh + 12), s5 = ld3p(sh + 15), s6 = ld3p(sh + 18), s7 = ld3p(sh + 21), s8 = ld3p(sh + 24);
             gx = gx + (C2[0] * y) * s4 + (C2[2] * 2.f * -x) * s6 + (C2[3] * z) * s7 + (C2[4] * 2.f * x) * s8;
             gy = gy + (C2[0] * x) * s4 + (C2[1] * z) * s5 + (C2[2] * 2.f * -y) * s6 + (C2[4] * 2.f * -y) * s8;
             gz = gz + (C2[1] * y) * s5 + (C2[2] * 2.f * 2.f * z) * s6 + (C2[3] * x) * s7;
@@ -106,8 +107,8 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict_
                 basis[11] = C3[2] * y * (4.f * zz - xx - yy); basis[12] = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
                 basis[13] = C3[4] * x * (4.f * zz - xx - yy); basis[14] = C3[5] * z * (xx - yy);
                 basis[15] = C3[6] * x * (xx - 3.f * yy);
-                const V3 s9 = ld3(sh + 27), s10 = ld3(sh + 30), s11 = ld3(sh + 33), s12 = ld3(sh + 36),
-                         s13 = ld3(sh + 39), s14 = ld3(sh + 42), s15 = ld3(sh + 45);
+                const V3 s9 = ld3p(sh + 27), s10 = ld3p(sh + 30), s11 = ld3p(sh + 33), s12 = ld3p(sh + 36),
+                         s13 = ld3p(sh + 39), s14 = ld3p(sh + 42), s15 = ld3p(sh + 45);
                 gx = gx + (C3[0] * 3.f * 2.f * xy) * s9 + (C3[1] * yz) * s10 + (C3[2] * -2.f * xy) * s11
                         + (C3[3] * -3.f * 2.f * xz) * s12 + (C3[4] * (-3.f * xx + 4.f * zz - yy)) * s13
                         + (C3[5] * 2.f * xz) * s14 + (C3[6] * 3.f * (xx - yy)) * s15;
@@ -120,9 +121,12 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict_
             }
         }
     }
-    for (int k = 0; k < M; ++k) {
-        const float bk = (k < used) ? basis[k < 16 ? k : 15] : 0.0f;
-        st3(dsh + 3 * k, bk * dRGB);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {       // M <= 16; constant indices keep basis[] in registers
+        if (k < M) {
+            const float bk = (k < used) ? basis[k] : 0.0f;
+            st3(dsh + 3 * k, bk * dRGB);
+        }
     }
     // through the normalisation of the view direction (dnormvdv, auxiliary.h:107-117)
     const V3 ddir = { dot(gx, dRGB), dot(gy, dRGB), dot(gz, dRGB) };
@@ -134,6 +138,35 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* __restrict_
     dmean.y = (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32;
     dmean.z = (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32;
     return dmean;
+}
+
+
+// ---- shared-memory staging of one CTA's SH rows (backward kernels) ------------------------------
+// The SH coefficients and their gradients are 3M contiguous floats per Gaussian: a thread-per-Gaussian
+// access touches 32 different sectors per instruction. The CTA instead moves its SH_TILE rows with
+// unit-stride accesses (one 128-byte line per warp instruction) into a padded shared tile, computes
+// in place, and writes the gradient rows back the same way. Rows of invisible Gaussians are neither
+// read (their sectors are never requested) nor computed; they are written as zeros.
+constexpr int SH_TILE = 128;
+template <int M3> struct ShTile { static constexpr int STRIDE = M3 | 1; };     // odd stride: conflict-free rows
+
+template <int M3>
+__device__ __forceinline__ void sh_tile_load(const float* __restrict__ shs, size_t row0, int nrows,
+                                             const uint8_t* s_vis, float* s_sh) {
+    const float* src = shs + row0 * M3;
+    for (int e = threadIdx.x; e < nrows * M3; e += SH_TILE) {
+        const int g = e / M3, c = e - g * M3;
+        if (s_vis[g]) s_sh[g * ShTile<M3>::STRIDE + c] = __ldg(src + e);
+    }
+}
+template <int M3>
+__device__ __forceinline__ void sh_tile_store(float* __restrict__ dsh, size_t row0, int nrows,
+                                              const uint8_t* s_vis, const float* s_sh) {
+    float* dst = dsh + row0 * M3;
+    for (int e = threadIdx.x; e < nrows * M3; e += SH_TILE) {
+        const int g = e / M3, c = e - g * M3;
+        dst[e] = s_vis[g] ? s_sh[g * ShTile<M3>::STRIDE + c] : 0.0f;
+    }
 }
 
 }  // namespace gsr

@@ -11,17 +11,28 @@
 
 namespace gsr {
 
-__global__ void __launch_bounds__(256)
+template <int M3>       // 3 * SH coefficients per Gaussian (0: colours were precomputed)
+__global__ void __launch_bounds__(SH_TILE)
 surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
-    const int idx = blockIdx.x * 256 + threadIdx.x;
-    if (idx >= a.P) return;
-    const bool vis = a.radii[idx] > 0;
+    __shared__ float s_sh[M3 ? SH_TILE * ShTile<M3>::STRIDE : 1];
+    __shared__ uint8_t s_vis[SH_TILE];
+    const size_t row0 = (size_t)blockIdx.x * SH_TILE;
+    const int nrows = min(SH_TILE, a.P - (int)row0);
+    const int idx = (int)row0 + threadIdx.x;
+    const bool valid = idx < a.P;
+    const bool vis = valid && a.radii[idx] > 0;
+    if constexpr (M3 != 0) {
+        s_vis[threadIdx.x] = vis;
+        __syncthreads();
+        sh_tile_load<M3>(a.shs, row0, nrows, s_vis, s_sh);
+        __syncthreads();
+    }
 
     float dT[3][3] = { { 0, 0, 0 }, { 0, 0, 0 }, { 0, 0, 0 } };   // column-major like glm: dT[j] = gradient of row j of transMat
     V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 };
     float dscale0 = 0.f, dscale1 = 0.f, dop = 0.f;
     float4 drot = { 0, 0, 0, 0 };
-    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+    float* const my_sh = s_sh + threadIdx.x * ShTile<M3>::STRIDE;      // coefficients in, gradients out (in place)
 
     if (vis) {
         const float* ac = a.acc + (size_t)idx * SACC_STRIDE;
@@ -154,10 +165,10 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             dmean = { dM[2][0], dM[2][1], dM[2][2] };
         }
 
-        if (a.shs) {
+        if constexpr (M3 != 0) {
             const uint8_t cl = a.clamped[idx];
             const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
-            dmean = dmean + sh_backward(a.D, a.M, a.shs + (size_t)idx * a.M * 3, m, ld3(a.campos), dRGB, dsh);
+            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
 
         // densification hack (backward.cu:632-635)
@@ -167,11 +178,15 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         dm2d.z = 0.0f;
 #pragma unroll
         for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = dT_out[k];
-    } else {
+    } else if (valid) {
 #pragma unroll
         for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = 0.0f;
     }
-    if (dsh && (!vis || !a.shs)) for (int k = 0; k < a.M * 3; ++k) dsh[k] = 0.0f;
+    if constexpr (M3 != 0) {
+        __syncthreads();
+        sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);
+    }
+    if (!valid) return;
 
     st3(a.dL_dmeans3D + 3 * idx, dmean);
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
@@ -183,7 +198,15 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
 }
 
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st) {
-    surfel_preprocess_backward_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    switch (a.shs ? 3 * a.M : 0) {
+    case 0:  surfel_preprocess_backward_kernel<0><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 3:  surfel_preprocess_backward_kernel<3><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 12: surfel_preprocess_backward_kernel<12><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 27: surfel_preprocess_backward_kernel<27><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 48: surfel_preprocess_backward_kernel<48><<<blocks, SH_TILE, 0, st>>>(a); break;
+    default: return cudaErrorInvalidValue;
+    }
     return cudaGetLastError();
 }
 
