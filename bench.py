@@ -62,6 +62,7 @@ def setup_dist(args):
         torch.cuda.set_device(local)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep NCCL's version banner off stdout: ONE JSON line
         dist.init_process_group("nccl" if torch.cuda.is_available() else "gloo",
                                 device_id=torch.device("cuda", local) if torch.cuda.is_available() else None)
     return rank, world, local
@@ -129,14 +130,20 @@ def barrier(world):
         dist.barrier()
 
 
-def prime(step, min_seconds=1.0, min_steps=PRIME):
+def prime(step, world=1, min_seconds=1.0, min_steps=PRIME):
     """Untimed set-up before the W warm-ups: caching-allocator growth, lazy module loading, first-touch of the
-    scratch buffers. Runs at least `min_steps` steps and at least `min_seconds` of wall time."""
-    t0 = time.perf_counter(); n = 0
-    while n < min_steps or time.perf_counter() - t0 < min_seconds:
-        step(); n += 1
-        if n % 4 == 0:
-            torch.cuda.synchronize()
+    scratch buffers. Runs `min_steps` steps, then as many more as fill `min_seconds`; the extra count is agreed
+    across ranks (MAX) because a step may contain a collective."""
+    t0 = time.perf_counter()
+    for _ in range(min_steps):
+        step()
+    torch.cuda.synchronize()
+    per = max((time.perf_counter() - t0) / min_steps, 1e-5)
+    extra = torch.tensor([min(int(max(0.0, min_seconds - (time.perf_counter() - t0)) / per), 2000)], device="cuda")
+    if world > 1:
+        dist.all_reduce(extra, op=dist.ReduceOp.MAX)
+    for _ in range(int(extra.item())):
+        step()
     torch.cuda.synchronize()
 
 
@@ -288,9 +295,7 @@ class Ours:
         else:
             torch.autograd.backward([outs[0], outs[2], outs[3]],
                                     [gr[:3 * hw].view(3, H, W), gr[3 * hw:4 * hw].view(1, H, W), gr[4 * hw:].view(1, H, W)])
-        if world > 1:
-            self.reduce(params[0].grad, sc.P, sc.shs.shape[1])
-        return outs[0]
+        return outs[0]      # world > 1: the exchange runs inside backward (multiview.install_backward_allreduce)
 
 
 class Reference:
@@ -376,7 +381,7 @@ def run(arm, args, rank, world, local):
 
     n, radii, _ = step_resident()
     Pvis = int((radii > 0).sum())
-    prime(step_resident)
+    prime(step_resident, world)
     sampler = ClockSampler(local) if rank == 0 else None
     stages = None
     if arm.name == "ours":
@@ -389,6 +394,8 @@ def run(arm, args, rank, world, local):
         stages = list(st)
     ms_step = ms_total / args.steps
 
+    if arm.name == "ours" and world > 1:
+        mv.install_backward_allreduce()
     # ---- end to end: public API (ours: GaussianRasterizer + autograd), per-view host inputs from pinned memory
     params = [t.clone().requires_grad_(not fwd_only) for t in (sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)]
     h_cams = [torch.cat([c.viewmatrix.flatten(), c.projmatrix.flatten(), c.campos, sc.bg]).cpu().pin_memory() for c in cams]
@@ -418,7 +425,7 @@ def run(arm, args, rank, world, local):
         h_out.copy_(acc, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)
 
-    prime(step_e2e)                 # setup, not warm-up: caching-allocator growth for the autograd path
+    prime(step_e2e, world)                 # setup, not warm-up: caching-allocator growth for the autograd path
     ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
     launches = 0
     if arm.name == "ours":

@@ -16,6 +16,9 @@ from .. import _lib
 from .._lib import GsrSettings, ptr
 
 
+_backward_hook = [None]      # optional callable(head): runs on the parameter-gradient head of every backward
+
+
 def _f32c(t: torch.Tensor, device) -> torch.Tensor:
     """contiguous fp32 on `device`; 0-element sentinels (CPU or CUDA) pass through."""
     if t is None or t.numel() == 0:
@@ -141,6 +144,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_cov), ptr(g_sh), ptr(g_sc), ptr(g_rot),
                 ws.data_ptr(), ws_bytes, _stream(dev))
         _lib.check(rc, "gsr_rasterize_backward")
+        if _backward_hook[0] is not None:       # e.g. multiview.install_backward_allreduce: reduce before autograd copies
+            _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),
             g_sh.view(P, M, 3), g_sc.view(P, 3), g_rot.view(P, 4))
 

@@ -14,6 +14,7 @@ from .._lib import ptr
 from ..diff_gaussian_rasterization._C import _Arena, _f32c, _settings, _stream, mark_visible  # noqa: F401
 
 NUM_OTHERS = 7
+_backward_hook = [None]      # optional callable(head): runs on the parameter-gradient head of every backward
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
@@ -87,6 +88,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_tm), ptr(g_sh), ptr(g_sc), ptr(g_rot),
                 ws.data_ptr(), ws_bytes, _stream(dev))
         _lib.check(rc, "gsr_surfel_backward")
+        if _backward_hook[0] is not None:       # e.g. multiview.install_backward_allreduce: reduce before autograd copies
+            _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_tm.view(P, 9),
             g_sh.view(P, M, 3), g_sc.view(P, 2), g_rot.view(P, 4))
 

@@ -82,6 +82,18 @@ def reduce_densification_stats(xyz_gradient_accum: torch.Tensor, denom: torch.Te
     dist.all_reduce(max_radii2D, op=dist.ReduceOp.MAX, group=group)
 
 
+def install_backward_allreduce(group=None, enable: bool = True) -> None:
+    """Autograd users (`loss.backward()` through GaussianRasterizer) cannot reach the arena: autograd copies the
+    returned views into `.grad`. With this hook installed, every backward of both rasterizer packages all-reduces
+    its parameter-gradient head right after the kernels, i.e. BEFORE autograd sees the gradients, so `.grad` holds
+    the sum over ranks (one collective per backward call, on the current stream)."""
+    from .diff_gaussian_rasterization import _C as c3
+    from .diff_surfel_rasterization import _C as c2
+    hook = (lambda head: allreduce_param_grads(head, group=group)) if enable else None
+    c3._backward_hook[0] = hook
+    c2._backward_hook[0] = hook
+
+
 def render_views_sharded(render_one, view_ids: Sequence[int], P: int, M: int, surfel: bool = False, group=None):
     """Runs `render_one(view_id) -> grad_means3D` (one forward+backward of this library, returning the
     means3D gradient, which identifies the arena) for this rank's views, sums locally, reduces once.
