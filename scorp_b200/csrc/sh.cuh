@@ -154,6 +154,7 @@ template <int M3>
 __device__ __forceinline__ void sh_tile_load(const float* __restrict__ shs, size_t row0, int nrows,
                                              const uint8_t* s_vis, float* s_sh) {
     const float* src = shs + row0 * M3;
+#pragma unroll 8       // eight independent loads in flight per thread
     for (int e = threadIdx.x; e < nrows * M3; e += SH_TILE) {
         const int g = e / M3, c = e - g * M3;
         if (s_vis[g]) s_sh[g * ShTile<M3>::STRIDE + c] = __ldg(src + e);
@@ -163,6 +164,7 @@ template <int M3>
 __device__ __forceinline__ void sh_tile_store(float* __restrict__ dsh, size_t row0, int nrows,
                                               const uint8_t* s_vis, const float* s_sh) {
     float* dst = dsh + row0 * M3;
+#pragma unroll 8
     for (int e = threadIdx.x; e < nrows * M3; e += SH_TILE) {
         const int g = e / M3, c = e - g * M3;
         dst[e] = s_vis[g] ? s_sh[g * ShTile<M3>::STRIDE + c] : 0.0f;

@@ -10,6 +10,7 @@
 
 namespace gsr {
 
+int blend_direct_max(int dflt);     // render_bwd.cu
 constexpr float kNearB = 0.2f, kFarB = 100.0f;
 constexpr int SURFEL_SMEM_B = 2 * BATCH * (int)sizeof(SurfelRec) + 8 * 8 * 4 + 8 * 4;
 
@@ -49,7 +50,7 @@ surfel_render_backward_kernel(int W, int H, int gx,
                               const float* __restrict__ final_Ts, const float* __restrict__ in_M1,
                               const float* __restrict__ in_M2,
                               const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dothers,
-                              float* __restrict__ acc) {
+                              float* __restrict__ acc, int direct_max) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SurfelRec (*s_rec)[BATCH] = reinterpret_cast<SurfelRec (*)[BATCH]>(smem_raw);
     uint32_t (*s_bal)[8] = reinterpret_cast<uint32_t (*)[8]>(smem_raw + 2 * BATCH * sizeof(SurfelRec));
@@ -182,7 +183,8 @@ surfel_render_backward_kernel(int W, int H, int gx,
                         act = !(alpha < 1.0f / 255.0f);
                     }
                 }
-                if (!__any_sync(0xffffffffu, act)) continue;
+                const uint32_t act_mask = __ballot_sync(0xffffffffu, act);
+                if (act_mask == 0) continue;
 
                 float val[18];
 #pragma unroll
@@ -191,7 +193,8 @@ surfel_render_backward_kernel(int W, int H, int gx,
                     const float4 q4 = q[4];
                     const float nrm0 = q2.w, nrm1 = q3.x, nrm2 = q3.y, opa = q3.z;
                     const float col0 = q3.w, col1 = q4.x, col2 = q4.y;
-                    T = T / (1.f - alpha);
+                    const float inv_1ma = __frcp_rn(1.f - alpha);     // shared by the two divisions below (gradients: rtol 1e-4)
+                    T = T * inv_1ma;
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;
                     ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = col0; dL_dalpha += (col0 - ar0) * dpix0;
@@ -227,7 +230,7 @@ surfel_render_backward_kernel(int W, int H, int gx,
 
                     dL_dalpha *= T;
                     last_alpha = alpha;
-                    dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                    dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
 
                     const float dL_dG = opa * dL_dalpha;
                     dL_dz += alpha * T * dL_ddepth;
@@ -260,6 +263,14 @@ surfel_render_backward_kernel(int W, int H, int gx,
                     }
                     val[SACC_OP] = G * dL_dalpha;
                 }
+                if (__popc(act_mask) <= direct_max) {       // splat edges: direct predicated REDs, no warp reduction
+                    if (act) {
+                        float* a = acc + (size_t)__ldg(point_list + range.x + pos) * SACC_STRIDE;
+#pragma unroll
+                        for (int i = 0; i < 18; ++i) if (val[i] != 0.0f) atomicAdd(a + i, val[i]);
+                    }
+                    continue;
+                }
                 float s1[9], s2[5], s3[3], s4[2], s5[1];
                 bfly_stage<18>(val, s1, 16, h16);
                 bfly_stage<9>(s1, s2, 8, h8);
@@ -282,7 +293,7 @@ cudaError_t launch_surfel_render_backward(int W, int H, int gx, int gy, const Su
     if (e != cudaSuccess) return e;
     surfel_render_backward_kernel<<<gx * gy, 256, SURFEL_SMEM_B, st>>>(W, H, gx, img.ranges, bin.point_list, g.rec, bg,
                                                                       img.n_contrib, img.median_contrib, img.final_T,
-                                                                      img.M1, img.M2, dL_dpix, dL_dothers, acc);
+                                                                      img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(0));
     return cudaGetLastError();
 }
 
