@@ -72,7 +72,7 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
     uint32_t tiles = 0;

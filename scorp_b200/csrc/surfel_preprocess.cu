@@ -126,7 +126,7 @@ __device__ __forceinline__ float4 surfel_cull_box(const M3& T, float cx, float c
 }
 
 template <bool VEC>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
     uint32_t tiles = 0;

@@ -12,7 +12,7 @@
 namespace gsr {
 
 template <int M3>       // 3 * SH coefficients per Gaussian (0: colours were precomputed)
-__global__ void __launch_bounds__(SH_TILE)
+__global__ void __launch_bounds__(SH_TILE, 8)
 surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
     __shared__ float s_sh[M3 ? SH_TILE * ShTile<M3>::STRIDE : 1];
     __shared__ uint8_t s_vis[SH_TILE];
