@@ -5,10 +5,11 @@
 // N keys (tile<<32 | depth bits) with a stable LSD radix sort whose input is in Gaussian-index
 // order, so the result within a tile is ordered by (depth bits, Gaussian index). Here:
 //   1. preprocess already counted instances per tile (atomic histogram);
-//   2. tile_scan: exclusive scan of the counts -> ranges[tile] (empty tiles stay (0,0));
+//   2. tile_scan: exclusive scan of the counts -> ranges[tile] (empty tiles stay (0,0)), and the longest
+//      segment, read back together with N so the host launches only the sort kernels that have work;
 //   3. scatter: every instance goes straight to its tile's segment as (depth bits<<32 | index);
-//   4. tile_sort: one CTA sorts each segment on that unique 64-bit key (bitonic in shared
-//      memory; global-memory merge steps for segments longer than the shared buffer).
+//   4. tile_sort: one CTA sorts each segment on that unique 64-bit key (register-blocked bitonic in
+//      shared memory, two size classes; global-memory merge steps for segments longer than 8192).
 // The output lists are bit-identical to the reference's and cost ~20 B/instance of traffic
 // instead of ~150 B/instance for a 6-pass radix sort.
 #include "common.cuh"
@@ -17,15 +18,17 @@ namespace gsr {
 
 // ---- 2. exclusive scan over tiles (single CTA, tiles <= a few 10^4) ------------------------
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges) {
+tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ max_len) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
+    uint32_t longest = 0;
     for (int base = 0; base < tiles; base += 1024) {
         const int t = base + threadIdx.x;
         const uint32_t c = (t < tiles) ? count[t] : 0u;
+        longest = max(longest, c);
         uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
@@ -45,6 +48,8 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         if (threadIdx.x == 1023) carry_s = incl;
         __syncthreads();
     }
+    longest = __reduce_max_sync(0xffffffffu, longest);      // the host picks the sort kernels by the longest segment
+    if (lane == 0 && longest) atomicMax(max_len, longest);
 }
 
 // ---- 3. scatter instances into tile segments ----------------------------------------------
@@ -98,18 +103,137 @@ scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_str
 // Bitonic network in its all-ascending form (first step of every merge pairs i with its mirror
 // image, the remaining steps are half-cleaners). Every comparator puts the smaller key at the
 // lower index, so a length L that is not a power of two is handled by treating indices >= L
-// as +inf: comparators that touch them are no-ops and are skipped.
-constexpr int SORT_CAP = 4096;        // u64 elements held in shared memory (32 KB)
-constexpr int SORT_THREADS = 256;
+// as +inf: such keys never move down, comparators that touch only them are skipped.
+//
+// Register blocking: a thread owns the 2^C elements that interact during C consecutive steps of
+// the network (C <= 3), so the m steps of the merge of size 2^m cost ceil(m/3) passes over shared
+// memory instead of m, and the merges of size 2, 4, 8 happen entirely in registers on the way in
+// from global memory. The last pass of the last merge writes the two output lists directly.
+constexpr uint64_t KEY_INF = ~0ull;
+__device__ __forceinline__ int sphys(int i) { return i + (i >> 3); }      // 8 B pad per 8 keys: stride-8 owners hit distinct banks
+constexpr size_t sphys_host(size_t n) { return n + (n >> 3); }
+__device__ __forceinline__ void cx(uint64_t& a, uint64_t& b) {
+    const uint64_t lo = a < b ? a : b, hi = a < b ? b : a;
+    a = lo; b = hi;
+}
+// C steps on E = 2^C registers held in ascending address order: [mirror,] then half-cleaners.
+template <int C, bool MIRROR>
+__device__ __forceinline__ void net_group(uint64_t (&r)[1 << C]) {
+    constexpr int E = 1 << C;
+    if constexpr (MIRROR) {
+#pragma unroll
+        for (int e = 0; e < E / 2; ++e) cx(r[e], r[E - 1 - e]);
+    }
+#pragma unroll
+    for (int j = MIRROR ? E / 4 : E / 2; j > 0; j >>= 1) {
+#pragma unroll
+        for (int e = 0; e < E; ++e)
+            if (!(e & j)) cx(r[e], r[e | j]);
+    }
+}
+__device__ __forceinline__ void net_sort8(uint64_t (&r)[8]) {
+    cx(r[0], r[1]); cx(r[2], r[3]); cx(r[4], r[5]); cx(r[6], r[7]);                      // merges of 2
+    cx(r[0], r[3]); cx(r[1], r[2]); cx(r[4], r[7]); cx(r[5], r[6]);                      // merges of 4
+    cx(r[0], r[1]); cx(r[2], r[3]); cx(r[4], r[5]); cx(r[6], r[7]);
+    net_group<3, true>(r);                                                               // merge of 8
+}
 
+struct SortOut { uint32_t* list; uint64_t* keys; uint64_t tile_hi; };
+
+// One pass = C network steps of the merge of size k over the n-element (padded) segment.
+// MIRROR: the group starts with the mirror step of that merge; otherwise `stride` is the distance
+// between a thread's elements (top comparator distance = stride << (C-1)). EMIT: results go to the output lists.
+template <int C, bool MIRROR, bool EMIT, int THREADS>
+__device__ __forceinline__ void sort_pass(uint64_t* s, int L, int n, int k, int stride, const SortOut& o) {
+    constexpr int E = 1 << C;
+    for (int i = threadIdx.x; i < (n >> C); i += THREADS) {
+        int addr[E];
+        if constexpr (MIRROR) {
+            const int st = k >> C;                      // stride inside each half
+            const int blk = i / st, t = i - blk * st;
+#pragma unroll
+            for (int e = 0; e < E / 2; ++e) {
+                addr[e] = blk * k + t + e * st;
+                addr[E - 1 - e] = blk * k + k - 1 - t - e * st;
+            }
+        } else {
+            const int low = i & (stride - 1);
+            const int base = low | ((i - low) << C);
+#pragma unroll
+            for (int e = 0; e < E; ++e) addr[e] = base + e * stride;
+        }
+        if (addr[0] >= L) continue;                     // nothing but padding
+        uint64_t r[E];
+#pragma unroll
+        for (int e = 0; e < E; ++e) r[e] = addr[e] < L ? s[sphys(addr[e])] : KEY_INF;
+        net_group<C, MIRROR>(r);
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            if (addr[e] < L) {
+                if constexpr (EMIT) { o.list[addr[e]] = (uint32_t)r[e]; o.keys[addr[e]] = o.tile_hi | (r[e] >> 32); }
+                else s[sphys(addr[e])] = r[e];
+            }
+        }
+    }
+}
+
+// Segments with lo_len < L <= CAP. Dynamic shared memory: sphys(CAP) keys.
+template <int THREADS, int CAP>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                 uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    extern __shared__ uint64_t s[];
+    const int tile = blockIdx.x;
+    const uint2 rg = ranges[tile];
+    const int L = (int)(rg.y - rg.x);
+    if (L <= lo_len || L > CAP) return;
+    const uint64_t* seg = keys + rg.x;
+    const SortOut o{point_list + rg.x, point_list_keys + rg.x, (uint64_t)tile << 32};
+    int n = 8; while (n < L) n <<= 1;
+    for (int i = threadIdx.x; i < (n >> 3); i += THREADS) {
+        const int base = i << 3;
+        if (base >= L) continue;
+        uint64_t r[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) r[e] = base + e < L ? seg[base + e] : KEY_INF;
+        net_sort8(r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+            if (base + e < L) {
+                if (n == 8) { o.list[base + e] = (uint32_t)r[e]; o.keys[base + e] = o.tile_hi | (r[e] >> 32); }
+                else s[sphys(base + e)] = r[e];
+            }
+        }
+    }
+    if (n == 8) return;
+    __syncthreads();
+    int m = 4;
+    for (int k = 16; k <= n; k <<= 1, ++m) {
+        const int c0 = (m % 3) ? (m % 3) : 3;            // steps in the leading (mirror) group; the rest are triples
+        if (c0 == 1)      sort_pass<1, true, false, THREADS>(s, L, n, k, 0, o);
+        else if (c0 == 2) sort_pass<2, true, false, THREADS>(s, L, n, k, 0, o);
+        else              sort_pass<3, true, false, THREADS>(s, L, n, k, 0, o);
+        __syncthreads();
+        for (int d = k >> (c0 + 1); d >= 4; d >>= 3) {   // d = top comparator distance of the triple
+            const int stride = d >> 2;
+            if (stride == 1 && k == n) { sort_pass<3, false, true, THREADS>(s, L, n, k, 1, o); return; }
+            sort_pass<3, false, false, THREADS>(s, L, n, k, stride, o);
+            __syncthreads();
+        }
+    }
+}
+
+// Segments longer than LONG_MIN (rare: > 8192 splats on one tile): chunks sorted in shared memory, merge
+// steps with stride >= LONG_CAP in global (L2-resident) memory, the tail of every merge per chunk in shared memory.
+constexpr int LONG_CAP = 4096;
+constexpr int LONG_THREADS = 1024;
 __device__ __forceinline__ void cmpx(uint64_t* a, int lo, int hi) {
     const uint64_t x = a[lo], y = a[hi];
     if (x > y) { a[lo] = y; a[hi] = x; }
 }
-// merge step 1 for blocks of size k over n/2 comparators
 __device__ __forceinline__ void mirror_step(uint64_t* a, int L, int n, int k) {
     const int h = k >> 1;
-    for (int i = threadIdx.x; i < (n >> 1); i += SORT_THREADS) {
+    for (int i = threadIdx.x; i < (n >> 1); i += LONG_THREADS) {
         const int blk = i / h, t = i - blk * h;
         const int lo = blk * k + t, hi = blk * k + k - 1 - t;
         if (hi < L) cmpx(a, lo, hi);
@@ -117,82 +241,81 @@ __device__ __forceinline__ void mirror_step(uint64_t* a, int L, int n, int k) {
     __syncthreads();
 }
 __device__ __forceinline__ void half_step(uint64_t* a, int L, int n, int j) {
-    for (int i = threadIdx.x; i < (n >> 1); i += SORT_THREADS) {
+    for (int i = threadIdx.x; i < (n >> 1); i += LONG_THREADS) {
         const int lo = ((i & ~(j - 1)) << 1) | (i & (j - 1));
         const int hi = lo | j;
         if (hi < L) cmpx(a, lo, hi);
     }
     __syncthreads();
 }
-__device__ void sort_smem(uint64_t* s, int L) {
-    int n = 1; while (n < L) n <<= 1;
-    for (int k = 2; k <= n; k <<= 1) {
-        mirror_step(s, L, n, k);
-        for (int j = k >> 2; j > 0; j >>= 1) half_step(s, L, n, j);
-    }
-}
-
-__global__ void __launch_bounds__(SORT_THREADS)
-tile_sort_kernel(int tiles, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
-    __shared__ uint64_t s[SORT_CAP];
+__global__ void __launch_bounds__(LONG_THREADS)
+tile_sort_long_kernel(int lo_len, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
+                      uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    __shared__ uint64_t s[LONG_CAP];
     const int tile = blockIdx.x;
     const uint2 r = ranges[tile];
     const int L = (int)(r.y - r.x);
-    if (L <= 0) return;
+    if (L <= lo_len) return;
     uint64_t* seg = keys + r.x;
     const uint64_t tile_hi = (uint64_t)tile << 32;
-    if (L <= SORT_CAP) {
-        for (int i = threadIdx.x; i < L; i += SORT_THREADS) s[i] = seg[i];
+    int n = LONG_CAP; while (n < L) n <<= 1;
+    for (int c0 = 0; c0 < L; c0 += LONG_CAP) {
+        const int Lc = min(LONG_CAP, L - c0);
+        for (int i = threadIdx.x; i < Lc; i += LONG_THREADS) s[i] = seg[c0 + i];
         __syncthreads();
-        sort_smem(s, L);
-        for (int i = threadIdx.x; i < L; i += SORT_THREADS) {
-            const uint64_t k = s[i];
-            point_list[r.x + i] = (uint32_t)k;
-            point_list_keys[r.x + i] = tile_hi | (k >> 32);
+        for (int k = 2; k <= LONG_CAP; k <<= 1) {
+            mirror_step(s, Lc, LONG_CAP, k);
+            for (int j = k >> 2; j > 0; j >>= 1) half_step(s, Lc, LONG_CAP, j);
         }
-        return;
-    }
-    // Long segment: chunks sorted in shared memory, merge steps with stride >= SORT_CAP in
-    // global (L2-resident) memory, the tail of every merge again per chunk in shared memory.
-    int n = SORT_CAP; while (n < L) n <<= 1;
-    for (int c0 = 0; c0 < L; c0 += SORT_CAP) {
-        const int Lc = min(SORT_CAP, L - c0);
-        for (int i = threadIdx.x; i < Lc; i += SORT_THREADS) s[i] = seg[c0 + i];
-        __syncthreads();
-        sort_smem(s, Lc);
-        for (int i = threadIdx.x; i < Lc; i += SORT_THREADS) seg[c0 + i] = s[i];
+        for (int i = threadIdx.x; i < Lc; i += LONG_THREADS) seg[c0 + i] = s[i];
         __syncthreads();
     }
-    for (int k = 2 * SORT_CAP; k <= n; k <<= 1) {
+    for (int k = 2 * LONG_CAP; k <= n; k <<= 1) {
         mirror_step(seg, L, n, k);
-        for (int j = k >> 2; j >= SORT_CAP; j >>= 1) half_step(seg, L, n, j);
-        for (int c0 = 0; c0 < L; c0 += SORT_CAP) {
-            const int Lc = min(SORT_CAP, L - c0);
-            for (int i = threadIdx.x; i < Lc; i += SORT_THREADS) s[i] = seg[c0 + i];
+        for (int j = k >> 2; j >= LONG_CAP; j >>= 1) half_step(seg, L, n, j);
+        for (int c0 = 0; c0 < L; c0 += LONG_CAP) {
+            const int Lc = min(LONG_CAP, L - c0);
+            for (int i = threadIdx.x; i < Lc; i += LONG_THREADS) s[i] = seg[c0 + i];
             __syncthreads();
-            for (int j = SORT_CAP >> 1; j > 0; j >>= 1) half_step(s, Lc, SORT_CAP, j);
-            for (int i = threadIdx.x; i < Lc; i += SORT_THREADS) seg[c0 + i] = s[i];
+            for (int j = LONG_CAP >> 1; j > 0; j >>= 1) half_step(s, Lc, LONG_CAP, j);
+            for (int i = threadIdx.x; i < Lc; i += LONG_THREADS) seg[c0 + i] = s[i];
             __syncthreads();
         }
     }
-    for (int i = threadIdx.x; i < L; i += SORT_THREADS) {
+    for (int i = threadIdx.x; i < L; i += LONG_THREADS) {
         const uint64_t k = seg[i];
         point_list[r.x + i] = (uint32_t)k;
         point_list_keys[r.x + i] = tile_hi | (k >> 32);
     }
 }
 
-cudaError_t launch_binning(int P, int gx, int gy, int N, const void* recs, int rec_stride, int depth_off,
-                           uint32_t* tile_count, const int32_t* radii, uint2* ranges, const BinningState& bin,
+constexpr int SORT_S_CAP = 1024, SORT_S_THREADS = 128;       // most tiles
+constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // crowded tiles (one CTA of 32 warps each)
+
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, cudaStream_t st) {
+    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, max_len);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
+                           uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
                            cudaStream_t st) {
     const int tiles = gx * gy;
-    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges);
-    if (N > 0) {
-        scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
-                                                        tile_count, ranges, bin.scratch);
-        tile_sort_kernel<<<tiles, SORT_THREADS, 0, st>>>(tiles, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+    if (N <= 0) return cudaSuccess;
+    scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
+                                                    tile_count, ranges, bin.scratch);
+    tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
+        0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+    if (max_len > SORT_S_CAP) {
+        // per device and cheap; only scenes with crowded tiles come here
+        cudaError_t e = cudaFuncSetAttribute(tile_sort_kernel<SORT_M_THREADS, SORT_M_CAP>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sphys_host(SORT_M_CAP) * 8));
+        if (e != cudaSuccess) return e;
+        tile_sort_kernel<SORT_M_THREADS, SORT_M_CAP><<<tiles, SORT_M_THREADS, sphys_host(SORT_M_CAP) * 8, st>>>(
+            SORT_S_CAP, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
     }
+    if (max_len > SORT_M_CAP)
+        tile_sort_long_kernel<<<tiles, LONG_THREADS, 0, st>>>(SORT_M_CAP, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
     return cudaGetLastError();
 }
 

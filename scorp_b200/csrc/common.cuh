@@ -128,6 +128,25 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx
     y1 = min((uint32_t)gy, (uint32_t)max(0, (int)mulr(addr(addr(addr(py, rf), 16.0f), -1.0f), 0.0625f)));
 }
 
+// Warp-wide: every lane brings one tile rectangle (origin x0,y0, width w, cnt = w*h tiles, cnt = 0 for none) and
+// one is added to tile_count for every tile of every rectangle. Rectangles of up to HIST_SMALL tiles are done by
+// their own lane; larger ones are spread over the 32 lanes. Must be called by all 32 lanes.
+constexpr uint32_t HIST_SMALL = 4;
+__device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uint32_t x0, uint32_t y0, uint32_t w, uint32_t cnt) {
+    if (cnt > 0 && cnt <= HIST_SMALL) {
+        for (uint32_t i = 0; i < cnt; ++i) atomicAdd(tile_count + (y0 + i / w) * gx + x0 + i % w, 1u);
+    }
+    uint32_t big = __ballot_sync(0xffffffffu, cnt > HIST_SMALL);
+    const uint32_t lane = threadIdx.x & 31;
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
+        const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
+        for (uint32_t i = lane; i < bcnt; i += 32) atomicAdd(tile_count + (by0 + i / bw) * gx + bx0 + i % bw, 1u);
+    }
+}
+
 // cp.async 16-byte global->shared (LDGSTS), L2-only caching: the records are read once per CTA.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -147,8 +166,9 @@ struct FwdArgs {
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
-cudaError_t launch_binning(int P, int gx, int gy, int N, const void* recs, int rec_stride, int depth_off,
-                           uint32_t* tile_count, const int32_t* radii, uint2* ranges, const BinningState& bin,
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, cudaStream_t st);
+cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
+                           uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
                            cudaStream_t st);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,

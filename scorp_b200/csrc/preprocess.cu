@@ -75,7 +75,7 @@ template <bool VEC>
 __global__ void __launch_bounds__(256, 4)
 preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
-    uint32_t tiles = 0;
+    uint32_t tiles = 0, rx0 = 0, ry0 = 0, rw = 0;
     if (idx < a.P) {
         int my_radius = 0;
         do {
@@ -151,15 +151,15 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
             dst[1] = make_float4(rec.cc, rec.opacity, rec.depth, rec.thr);
             dst[2] = make_float4(rec.r, rec.g, rec.b, 0.0f);
 
-            for (uint32_t ty_ = y0; ty_ < y1; ++ty_)
-                for (uint32_t tx_ = x0; tx_ < x1; ++tx_)
-                    atomicAdd(g.tile_count + ty_ * a.gx + tx_, 1u);
             my_radius = rad;
-            tiles = cnt;
+            tiles = cnt; rx0 = x0; ry0 = y0; rw = x1 - x0;
         } while (false);
         radii[idx] = my_radius;
         g.tiles_touched[idx] = tiles;
     }
+    // per-tile instance histogram (replaces the reference's scan over tiles_touched + duplicateWithKeys counting):
+    // small rectangles by their own lane, large ones spread over the warp so one big splat does not serialise it
+    tile_histogram(g.tile_count, a.gx, rx0, ry0, rw, tiles);
     // total instance count: one atomic per warp
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);

@@ -66,16 +66,19 @@ int gsr_surfel_forward(
     if ((rc = stage_check(s, st, "surfel preprocess"))) return rc;
     prof_mark(1, st);
 
-    uint32_t n_host = 0;
-    if ((rc = check_cuda(cudaMemcpyAsync(&n_host, g.counters, 4, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
+    // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
+    // tile segment (counters[1]) to it
+    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, st), "tile scan launch"))) return rc;
+    uint32_t n_host[2] = {0, 0};
+    if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
-    const int N = (int)n_host;
+    const int N = (int)n_host[0], max_len = (int)n_host[1];
     *num_rendered = N;
 
     char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
     carve_binning(bbase, N, &bin);
-    if ((rc = check_cuda(launch_binning(P, gx, gy, N, g.rec, (int)sizeof(SurfelRec), SURFEL_DEPTH_OFF, g.tile_count, radii,
+    if ((rc = check_cuda(launch_binning(P, gx, gy, N, max_len, g.rec, (int)sizeof(SurfelRec), SURFEL_DEPTH_OFF, g.tile_count, radii,
                                         img.ranges, bin, st), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);

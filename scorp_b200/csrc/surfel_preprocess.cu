@@ -129,7 +129,7 @@ template <bool VEC>
 __global__ void __launch_bounds__(256, 4)
 surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
-    uint32_t tiles = 0;
+    uint32_t tiles = 0, rx0 = 0, ry0 = 0, rw = 0;
     if (idx < a.P) {
         int my_radius = 0;
         do {
@@ -195,15 +195,13 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
             dst[4] = make_float4(cg, cb, depth, 0.0f);
             dst[5] = box;
 
-            for (uint32_t ty_ = y0; ty_ < y1; ++ty_)
-                for (uint32_t tx_ = x0; tx_ < x1; ++tx_)
-                    atomicAdd(g.tile_count + ty_ * a.gx + tx_, 1u);
             my_radius = rad;
-            tiles = cnt;
+            tiles = cnt; rx0 = x0; ry0 = y0; rw = x1 - x0;
         } while (false);
         radii[idx] = my_radius;
         g.tiles_touched[idx] = tiles;
     }
+    tile_histogram(g.tile_count, a.gx, rx0, ry0, rw, tiles);      // per-tile instance counts, warp-cooperative
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);
 }
