@@ -52,8 +52,8 @@ CASES = [
     ("C2_100k", "C2", dict(P=100_000)),
     ("sh1", "C2", dict(P=20_000, W=320, H=200, sh_degree=1)),
     ("sh2_bg", "C2", dict(P=20_000, W=320, H=200, sh_degree=2, random_bg=True)),
-    ("dense_long_lists", "C1", dict(P=60_000, W=96, H=64)),
-    ("dense_mid_lists", "C1", dict(P=8_000, W=96, H=64)),
+    ("dense_long_lists", "C1", dict(P=200_000, W=96, H=64)),
+    ("dense_mid_lists", "C1", dict(P=60_000, W=96, H=64)),
 ]
 
 
@@ -61,7 +61,7 @@ def test_sort_size_classes_are_covered():
     """binning.cu sorts tile segments with three kernels chosen by length (<= 1024, <= 8192, longer); the parity
     cases above must reach all three, otherwise their bit-exact list checks prove less than they seem to."""
     longest = {}
-    for name, kw in (("C1", dict()), ("mid", dict(P=8_000, W=96, H=64)), ("long", dict(P=60_000, W=96, H=64))):
+    for name, kw in (("C1", dict()), ("mid", dict(P=60_000, W=96, H=64)), ("long", dict(P=200_000, W=96, H=64))):
         sc = h.make("C1", **kw)
         rg = h.ours_intermediates(h.ours_forward(sc, sc.cameras[0]))["ranges"].long()
         longest[name] = int((rg[:, 1] - rg[:, 0]).max())
