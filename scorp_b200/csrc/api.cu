@@ -145,7 +145,7 @@ int gsr_rasterize_forward(
     // number of instances -> host (the one blocking point, as rasterizer_impl.cu:282)
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
-    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, st), "tile scan launch"))) return rc;
+    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
     uint32_t n_host[2] = {0, 0};
     if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;

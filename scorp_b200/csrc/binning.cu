@@ -17,10 +17,15 @@
 namespace gsr {
 
 // ---- 2. exclusive scan over tiles (single CTA, tiles <= a few 10^4) ------------------------
+constexpr int ORDER_BINS = 1024;      // == threads of the scan CTA
+__device__ __forceinline__ int order_bin(uint32_t len) { return (int)min(len >> 3, (uint32_t)(ORDER_BINS - 1)); }
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ max_len) {
+tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ max_len,
+                 uint32_t* __restrict__ order) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
+    __shared__ uint32_t bins[ORDER_BINS];
+    bins[threadIdx.x] = 0;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
@@ -29,6 +34,7 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         const int t = base + threadIdx.x;
         const uint32_t c = (t < tiles) ? count[t] : 0u;
         longest = max(longest, c);
+        if (t < tiles) atomicAdd(&bins[order_bin(c)], 1u);
         uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
@@ -50,6 +56,28 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
     }
     longest = __reduce_max_sync(0xffffffffu, longest);      // the host picks the sort kernels by the longest segment
     if (lane == 0 && longest) atomicMax(max_len, longest);
+
+    // Launch order for the blend kernels: longest segments first (counting sort on the quantised length), so
+    // the crowded tiles of an object-centred view start at once instead of landing in the last wave.
+    {
+        const uint32_t c = bins[ORDER_BINS - 1 - threadIdx.x];          // thread i owns the i-th longest class
+        uint32_t v = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
+        __syncthreads();
+        if (lane == 31) warp_sums[wid] = v;
+        __syncthreads();
+        if (wid == 0) {
+            uint32_t w = warp_sums[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, w, o); if (lane >= o) w += n; }
+            warp_sums[lane] = w;
+        }
+        __syncthreads();
+        bins[ORDER_BINS - 1 - threadIdx.x] = v - c + (wid ? warp_sums[wid - 1] : 0u);   // first slot of the class
+        __syncthreads();
+        for (int t = threadIdx.x; t < tiles; t += 1024) order[atomicAdd(&bins[order_bin(count[t])], 1u)] = (uint32_t)t;
+    }
 }
 
 // ---- 3. scatter instances into tile segments ----------------------------------------------
@@ -292,8 +320,9 @@ tile_sort_long_kernel(int lo_len, const uint2* __restrict__ ranges, uint64_t* __
 constexpr int SORT_S_CAP = 1024, SORT_S_THREADS = 128;       // most tiles
 constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // crowded tiles (one CTA of 32 warps each)
 
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, cudaStream_t st) {
-    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, max_len);
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, uint32_t* order,
+                             cudaStream_t st) {
+    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, max_len, order);
     return cudaGetLastError();
 }
 

@@ -42,6 +42,7 @@ struct GeomState {
 struct ImageState {
     uint2*    ranges;
     uint32_t* n_contrib;
+    uint32_t* tile_order;     // tiles by decreasing list length: CTA b of a blend kernel takes tile_order[b]
 };
 struct BinningState {
     uint32_t* point_list;
@@ -72,8 +73,9 @@ inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off =
     size_t o = 0;
     size_t a0 = o; o = align_up(o + (size_t)tiles * sizeof(uint2));
     size_t a1 = o; o = align_up(o + (size_t)W * H * 4);
+    size_t a2 = o; o = align_up(o + (size_t)tiles * 4);
     if (off) { off[0] = a0; off[1] = a1; }
-    if (s) { s->ranges = (uint2*)(base + a0); s->n_contrib = (uint32_t*)(base + a1); }
+    if (s) { s->ranges = (uint2*)(base + a0); s->n_contrib = (uint32_t*)(base + a1); s->tile_order = (uint32_t*)(base + a2); }
     return o;
 }
 inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nullptr) {
@@ -166,7 +168,8 @@ struct FwdArgs {
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, cudaStream_t st);
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, uint32_t* order,
+                             cudaStream_t st);
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
                            cudaStream_t st);

@@ -43,7 +43,7 @@ __device__ __forceinline__ float bfly_one(float p, int m) { return p + __shfl_xo
 
 __global__ void __launch_bounds__(256, 4)      // 64 registers: 4 CTAs/SM; measured 1.19 -> 1.06 ms at C2 (5 CTAs/SM: 1.09)
 render_backward_kernel(int W, int H, int gx,
-                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                        const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                        const float* __restrict__ alphas, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
@@ -52,7 +52,7 @@ render_backward_kernel(int W, int H, int gx,
     __shared__ uint32_t s_bal[8][8];
     __shared__ uint32_t s_max[8];
 
-    const int tile = blockIdx.x;
+    const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
@@ -232,7 +232,7 @@ cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState
                                    const BinningState& bin, const float* bg, const float* out_alpha,
                                    const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
                                    float* acc, cudaStream_t st) {
-    render_backward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, bin.point_list, g.rec, bg, out_alpha,
+    render_backward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,
                                                     img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(8));
     return cudaGetLastError();
 }

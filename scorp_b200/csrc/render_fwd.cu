@@ -37,14 +37,14 @@ __device__ __forceinline__ bool block_may_contribute(float x, float y, float a, 
 
 __global__ void __launch_bounds__(256)
 render_forward_kernel(int W, int H, int gx,
-                      const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                       const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                       uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                       float* __restrict__ out_depth, float* __restrict__ out_alpha) {
     __shared__ __align__(16) GaussRec s_rec[2][BATCH];
     __shared__ uint32_t s_bal[8][8];          // [consumer warp block][producer warp]
 
-    const int tile = blockIdx.x;
+    const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
@@ -153,7 +153,7 @@ render_forward_kernel(int W, int H, int gx,
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st) {
-    render_forward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, bin.point_list, g.rec, bg,
+    render_forward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                    img.n_contrib, out_color, out_depth, out_alpha);
     return cudaGetLastError();
 }

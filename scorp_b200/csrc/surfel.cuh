@@ -39,6 +39,7 @@ struct SurfelImage {
     float*    final_T;          // (:427)
     float*    M1;               // sum m*w  (:433)
     float*    M2;               // sum m^2*w (:434)
+    uint32_t* tile_order;       // tiles by decreasing list length (binning.cu)
 };
 
 inline size_t carve_surfel_geom(char* base, int P, int tiles, SurfelGeom* g, size_t* off = nullptr) {
@@ -64,11 +65,13 @@ inline size_t carve_surfel_image(char* base, int W, int H, SurfelImage* s, size_
     size_t a[6];
     a[0] = o; o = align_up(o + (size_t)tiles * sizeof(uint2));
     for (int k = 1; k < 6; ++k) { a[k] = o; o = align_up(o + hw * 4); }
+    const size_t a_order = o; o = align_up(o + (size_t)tiles * 4);
     if (off) { off[0] = a[0]; off[1] = a[1]; off[2] = a[2]; off[3] = a[3]; }   // ranges, n_contrib, median, final_T (M1, M2 follow at equal stride)
     if (s) {
         s->ranges = (uint2*)(base + a[0]); s->n_contrib = (uint32_t*)(base + a[1]);
         s->median_contrib = (uint32_t*)(base + a[2]); s->final_T = (float*)(base + a[3]);
         s->M1 = (float*)(base + a[4]); s->M2 = (float*)(base + a[5]);
+        s->tile_order = (uint32_t*)(base + a_order);
     }
     return o;
 }

@@ -44,7 +44,7 @@ __device__ __forceinline__ void bfly_owner18(int lane, int& slot, bool& writer) 
 
 __global__ void __launch_bounds__(256, 3)      // 80 registers: 3 CTAs/SM; measured 2.29 -> 1.97 ms at C4 (4 CTAs/SM spills: 2.60)
 surfel_render_backward_kernel(int W, int H, int gx,
-                              const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                              const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                               const SurfelRec* __restrict__ recs, const float* __restrict__ bg,
                               const uint32_t* __restrict__ n_contrib, const uint32_t* __restrict__ median_contrib,
                               const float* __restrict__ final_Ts, const float* __restrict__ in_M1,
@@ -56,7 +56,7 @@ surfel_render_backward_kernel(int W, int H, int gx,
     uint32_t (*s_bal)[8] = reinterpret_cast<uint32_t (*)[8]>(smem_raw + 2 * BATCH * sizeof(SurfelRec));
     uint32_t* s_max = reinterpret_cast<uint32_t*>(smem_raw + 2 * BATCH * sizeof(SurfelRec) + 8 * 8 * 4);
 
-    const int tile = blockIdx.x;
+    const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
@@ -291,7 +291,7 @@ cudaError_t launch_surfel_render_backward(int W, int H, int gx, int gy, const Su
                                           const float* dL_dothers, float* acc, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(surfel_render_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SURFEL_SMEM_B);
     if (e != cudaSuccess) return e;
-    surfel_render_backward_kernel<<<gx * gy, 256, SURFEL_SMEM_B, st>>>(W, H, gx, img.ranges, bin.point_list, g.rec, bg,
+    surfel_render_backward_kernel<<<gx * gy, 256, SURFEL_SMEM_B, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                                       img.n_contrib, img.median_contrib, img.final_T,
                                                                       img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(0));
     return cudaGetLastError();

@@ -14,7 +14,7 @@ constexpr int SURFEL_SMEM = 2 * BATCH * (int)sizeof(SurfelRec) + 8 * 8 * 4;
 
 __global__ void __launch_bounds__(256)
 surfel_render_forward_kernel(int W, int H, int gx,
-                             const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                             const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                              const SurfelRec* __restrict__ recs, const float* __restrict__ bg,
                              uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ median_contrib,
                              float* __restrict__ final_T, float* __restrict__ out_M1, float* __restrict__ out_M2,
@@ -23,7 +23,7 @@ surfel_render_forward_kernel(int W, int H, int gx,
     SurfelRec (*s_rec)[BATCH] = reinterpret_cast<SurfelRec (*)[BATCH]>(smem_raw);
     uint32_t (*s_bal)[8] = reinterpret_cast<uint32_t (*)[8]>(smem_raw + 2 * BATCH * sizeof(SurfelRec));
 
-    const int tile = blockIdx.x;
+    const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
@@ -160,7 +160,7 @@ cudaError_t launch_surfel_render_forward(int W, int H, int gx, int gy, const Sur
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    surfel_render_forward_kernel<<<gx * gy, 256, SURFEL_SMEM, st>>>(W, H, gx, img.ranges, bin.point_list, g.rec, bg,
+    surfel_render_forward_kernel<<<gx * gy, 256, SURFEL_SMEM, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                                     img.n_contrib, img.median_contrib, img.final_T, img.M1,
                                                                     img.M2, out_color, out_others);
     return cudaGetLastError();
