@@ -1,7 +1,9 @@
 // render_fwd.cu -- per-tile front-to-back alpha blend (3DGS forward).
 //
 // Replaces renderCUDA (reference diff-gaussian-rasterization/cuda_rasterizer/forward.cu:263-381).
-// One CTA per 16x16 tile; each of the 8 warps owns an 8x4 pixel block. Per round of 256 list
+// One CTA of 4 warps per 16x16 tile; each warp owns an 8x8 pixel block and every thread two vertically
+// adjacent pixels, so the list walk, the record loads and the x-dependent terms are shared by the pair and
+// the rest runs as packed FFMA2/FMUL2/FADD2 with the record fields as scalar operands. Per round of 256 list
 // entries: (1) 48-byte records are gathered into shared memory with cp.async, double-buffered
 // against the blend of the previous round; (2) every thread tests ITS record against the 8 warp
 // blocks (exact minimum of the conic form over the block rectangle vs. the record's power
@@ -14,146 +16,187 @@ namespace gsr {
 
 // Lower bound test: can record (x,y,a,b,c,thr) reach power >= thr anywhere in the pixel
 // rectangle [px0,px1]x[py0,py1]?  q(d) = 0.5(a dx^2 + c dy^2) + b dx dy, power = -q.
-__device__ __forceinline__ bool block_may_contribute(float x, float y, float a, float b, float c, float thr,
-                                                     float inv_a_b, float inv_c_b, bool convex,
-                                                     float px0, float px1, float py0, float py1) {
-    if (!convex) return true;
+// cull_prepare does the per-record part once (two approximate reciprocals; the minimiser only has to be
+// accurate to first order because q is stationary there, and the slack below covers the rest).
+struct CullRec { float x, y, a, b, c, thr, b_over_a, b_over_c; bool convex; };
+__device__ __forceinline__ float rcp_approx(float v) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
+__device__ __forceinline__ CullRec cull_prepare(float x, float y, float a, float b, float c, float thr) {
+    CullRec r{x, y, a, b, c, thr, 0.0f, 0.0f, false};
+    // strictly convex and well scaled; anything else is never culled
+    r.convex = (a > 1e-30f) && (c > 1e-30f) && (a < 1e30f) && (c < 1e30f) && (a * c - b * b > 0.0f);
+    if (r.convex) { r.b_over_a = b * rcp_approx(a); r.b_over_c = b * rcp_approx(c); }
+    return r;
+}
+__device__ __forceinline__ bool block_may_contribute(const CullRec& g, float px0, float px1, float py0, float py1) {
+    if (!g.convex) return true;
     // d = mean - pixel; pixel in [p0,p1]  =>  d in [m - p1, m - p0]
-    const float lx = x - px1, hx = x - px0, ly = y - py1, hy = y - py0;
+    const float lx = g.x - px1, hx = g.x - px0, ly = g.y - py1, hy = g.y - py0;
     const float cx = fminf(fmaxf(0.0f, lx), hx), cy = fminf(fmaxf(0.0f, ly), hy);
     if (cx == 0.0f && cy == 0.0f) return true;
     float qmin = 3.0e38f;
     if (cx != 0.0f) {   // facing vertical edge dx = cx
-        const float dy = fminf(fmaxf(-inv_c_b * cx, ly), hy);
-        qmin = 0.5f * (a * cx * cx + c * dy * dy) + b * cx * dy;
+        const float dy = fminf(fmaxf(-g.b_over_c * cx, ly), hy);
+        qmin = 0.5f * (g.a * cx * cx + g.c * dy * dy) + g.b * cx * dy;
     }
     if (cy != 0.0f) {   // facing horizontal edge dy = cy
-        const float dx = fminf(fmaxf(-inv_a_b * cy, lx), hx);
-        qmin = fminf(qmin, 0.5f * (a * dx * dx + c * cy * cy) + b * dx * cy);
+        const float dx = fminf(fmaxf(-g.b_over_a * cy, lx), hx);
+        qmin = fminf(qmin, 0.5f * (g.a * dx * dx + g.c * cy * cy) + g.b * dx * cy);
     }
     // keep unless provably below threshold (slack covers rounding of this test; NaN keeps)
-    return !(-qmin < thr - 1e-3f - 1e-5f * fabsf(qmin));
+    return !(-qmin < g.thr - 1e-3f - 1e-5f * fabsf(qmin));
 }
 
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ float2 bc(float v) { return make_float2(v, v); }    // scalar operand of a packed op (SASS: Rn.F32)
+
+constexpr int FWD_THREADS = 128;    // 4 warps x (8x8 pixel block, two vertically adjacent pixels per thread)
+
+__global__ void __launch_bounds__(FWD_THREADS, 8)
 render_forward_kernel(int W, int H, int gx,
                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                       const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                       uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
                       float* __restrict__ out_depth, float* __restrict__ out_alpha) {
     __shared__ __align__(16) GaussRec s_rec[2][BATCH];
-    __shared__ uint32_t s_bal[8][8];          // [consumer warp block][producer warp]
+    __shared__ uint32_t s_bal[4][8];          // [consumer warp block][32-record word of the round]
 
     const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
-    const int pxi = tile_x + bx + (lane & 7), pyi = tile_y + by + (lane >> 3);
-    const bool inside = pxi < W && pyi < H;
-    const float pxf = (float)pxi, pyf = (float)pyi;
+    const int bx = (wid & 1) * 8, by = (wid >> 1) * 8;
+    const int pxi = tile_x + bx + (lane & 7), pyi = tile_y + by + 2 * (lane >> 3);     // pixels (pxi, pyi) and (pxi, pyi+1)
+    const bool in0 = pxi < W && pyi < H, in1 = pxi < W && pyi + 1 < H;
+    const float pxf = (float)pxi;
+    const float2 npy = make_float2(-(float)pyi, -(float)(pyi + 1));
     const uint32_t pix_id = (uint32_t)pyi * W + pxi;
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const int rounds = (total + BATCH - 1) / BATCH;
 
-    float T = 1.0f, C0 = 0.0f, C1 = 0.0f, C2 = 0.0f, Dacc = 0.0f, Wacc = 0.0f;
-    uint32_t last_contributor = 0;
-    bool done = !inside;
+    // per-pixel state, .x = upper pixel, .y = lower pixel
+    float2 T = bc(1.0f), C0 = bc(0.0f), C1 = bc(0.0f), C2 = bc(0.0f), Dacc = bc(0.0f), Wacc = bc(0.0f);
+    uint32_t last0 = 0, last1 = 0;
+    bool done0 = !in0, done1 = !in1;
 
     auto issue = [&](int r) {
-        const int p = r * BATCH + tid;
-        if (p < total) {
-            const uint32_t id = __ldg(point_list + range.x + p);
-            const char* src = reinterpret_cast<const char*>(recs + id);
-            char* dst = reinterpret_cast<char*>(&s_rec[r & 1][tid]);
-            cp_async16(dst, src); cp_async16(dst + 16, src + 16); cp_async16(dst + 32, src + 32);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int slot = tid + k * FWD_THREADS;
+            const int p = r * BATCH + slot;
+            if (p < total) {
+                const uint32_t id = __ldg(point_list + range.x + p);
+                const char* src = reinterpret_cast<const char*>(recs + id);
+                char* dst = reinterpret_cast<char*>(&s_rec[r & 1][slot]);
+                cp_async16(dst, src); cp_async16(dst + 16, src + 16); cp_async16(dst + 32, src + 32);
+            }
         }
         cp_async_commit();
     };
 
     if (rounds > 0) issue(0);
     for (int r = 0; r < rounds; ++r) {
-        // all warps finished? (also orders the previous round's reads before buffer reuse)
-        if (__syncthreads_and(done)) break;
+        // all pixels finished? (also orders the previous round's reads before buffer reuse)
+        if (__syncthreads_and(done0 && done1)) break;
         if (r + 1 < rounds) { issue(r + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
         __syncthreads();
 
         const int n_here = min(BATCH, total - r * BATCH);
         const GaussRec* buf = s_rec[r & 1];
-        // per-record cull masks -> ballots
-        {
-            uint32_t mask = 0;
-            if (tid < n_here) {
-                const float4 g0 = *reinterpret_cast<const float4*>(&buf[tid]);
-                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[tid]) + 1);
-                const float x = g0.x, y = g0.y, a = g0.z, b = g0.w, c = g1.x, thr = g1.w;
-                const bool convex = (a > 0.0f) && (c > 0.0f) && (a * c - b * b > 0.0f);
-                const float inv_a_b = convex ? b / a : 0.0f, inv_c_b = convex ? b / c : 0.0f;
+        // per-record cull masks against the four 8x8 warp blocks -> ballots
 #pragma unroll
-                for (int w = 0; w < 8; ++w) {
-                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 4);
-                    if (block_may_contribute(x, y, a, b, c, thr, inv_a_b, inv_c_b, convex, x0, x0 + 7.0f, y0, y0 + 3.0f))
-                        mask |= 1u << w;
+        for (int k = 0; k < 2; ++k) {
+            const int slot = tid + k * FWD_THREADS;
+            uint32_t mask = 0;
+            if (slot < n_here) {
+                const float4 g0 = *reinterpret_cast<const float4*>(&buf[slot]);
+                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[slot]) + 1);
+                const CullRec c = cull_prepare(g0.x, g0.y, g0.z, g0.w, g1.x, g1.w);
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 8);
+                    if (block_may_contribute(c, x0, x0 + 7.0f, y0, y0 + 7.0f)) mask |= 1u << w;
                 }
             }
 #pragma unroll
-            for (int w = 0; w < 8; ++w) {
+            for (int w = 0; w < 4; ++w) {
                 const uint32_t bal = __ballot_sync(0xffffffffu, (mask >> w) & 1u);
-                if (lane == 0) s_bal[w][wid] = bal;
+                if (lane == 0) s_bal[w][wid + 4 * k] = bal;
             }
         }
         __syncthreads();
 
-        if (!__all_sync(0xffffffffu, done)) {
+        if (!__all_sync(0xffffffffu, done0 && done1)) {
+            const uint32_t pos_base = (uint32_t)(r * BATCH) + 1u;
             for (int v = 0; v < 8; ++v) {
                 uint32_t bits = s_bal[wid][v];
                 while (bits) {
                     const int j = v * 32 + __ffs(bits) - 1;
                     bits &= bits - 1;
-                    if (done) continue;
+                    if (done0 && done1) continue;
                     const float4 g0 = *reinterpret_cast<const float4*>(&buf[j]);
                     const float4 g1 = *(reinterpret_cast<const float4*>(&buf[j]) + 1);
-                    const float dx = subr(g0.x, pxf), dy = subr(g0.y, pyf);
-                    // forward.cu:334 with the reference build's contraction
-                    const float power = fmar(fmar(dx, mulr(dx, g0.z), mulr(dy, mulr(dy, g1.x))), -0.5f,
-                                             -mulr(dy, mulr(dx, g0.w)));
-                    if (power > 0.0f) continue;
-                    if (power < g1.w) continue;                  // implies alpha < 1/255
-                    const float alpha = fminf(0.99f, mulr(g1.y, expf(power)));
-                    if (alpha < 1.0f / 255.0f) continue;
-                    const float test_T = mulr(T, subr(1.0f, alpha));
-                    if (test_T < 0.0001f) { done = true; continue; }
+                    // forward.cu:334 with the reference build's contraction; the two pixels share dx
+                    const float dx = subr(g0.x, pxf);
+                    const float A = mulr(dx, g0.z), Bn = -mulr(dx, g0.w);
+                    const float2 dy = __fadd2_rn(bc(g0.y), npy);
+                    const float2 q = __ffma2_rn(bc(dx), bc(A), __fmul2_rn(dy, __fmul2_rn(dy, bc(g1.x))));
+                    const float2 power = __ffma2_rn(q, bc(-0.5f), __fmul2_rn(dy, bc(Bn)));
+                    // skip: power > 0, or power < thr (implies alpha < 1/255), or the pixel is finished
+                    const bool s0 = done0 || (power.x > 0.0f) || (power.x < g1.w);
+                    const bool s1 = done1 || (power.y > 0.0f) || (power.y < g1.w);
+                    if (s0 && s1) continue;
+                    float2 alpha = bc(0.0f);
+                    if (!s0) alpha.x = fminf(0.99f, mulr(g1.y, expf(power.x)));
+                    if (!s1) alpha.y = fminf(0.99f, mulr(g1.y, expf(power.y)));
+                    bool c0 = !s0 && !(alpha.x < 1.0f / 255.0f), c1 = !s1 && !(alpha.y < 1.0f / 255.0f);
+                    if (!c0) alpha.x = 0.0f;
+                    if (!c1) alpha.y = 0.0f;
+                    // test_T = T * (1 - alpha); halves with alpha == 0 keep T exactly
+                    const float2 test_T = __fmul2_rn(T, __ffma2_rn(alpha, bc(-1.0f), bc(1.0f)));
+                    if (c0 && test_T.x < 0.0001f) { done0 = true; c0 = false; alpha.x = 0.0f; }
+                    if (c1 && test_T.y < 0.0001f) { done1 = true; c1 = false; alpha.y = 0.0f; }
+                    if (!(c0 || c1)) continue;
                     const float4 g2 = *(reinterpret_cast<const float4*>(&buf[j]) + 2);
-                    C0 = fmar(T, mulr(alpha, g2.x), C0);
-                    C1 = fmar(T, mulr(alpha, g2.y), C1);
-                    C2 = fmar(T, mulr(alpha, g2.z), C2);
-                    Wacc = fmar(T, alpha, Wacc);
-                    Dacc = fmar(T, mulr(alpha, g1.z), Dacc);
-                    T = test_T;
-                    last_contributor = (uint32_t)(r * BATCH + j + 1);
+                    // a half with alpha == 0 adds T*0 (finite colours and depth assumed)
+                    C0 = __ffma2_rn(T, __fmul2_rn(alpha, bc(g2.x)), C0);
+                    C1 = __ffma2_rn(T, __fmul2_rn(alpha, bc(g2.y)), C1);
+                    C2 = __ffma2_rn(T, __fmul2_rn(alpha, bc(g2.z)), C2);
+                    Wacc = __ffma2_rn(T, alpha, Wacc);
+                    Dacc = __ffma2_rn(T, __fmul2_rn(alpha, bc(g1.z)), Dacc);
+                    if (c0) { T.x = test_T.x; last0 = pos_base + (uint32_t)j; }
+                    if (c1) { T.y = test_T.y; last1 = pos_base + (uint32_t)j; }
                 }
-                if (__all_sync(0xffffffffu, done)) break;
+                if (__all_sync(0xffffffffu, done0 && done1)) break;
             }
         }
     }
     cp_async_wait<0>();
 
-    if (inside) {
-        const size_t hw = (size_t)H * W;
-        n_contrib[pix_id] = last_contributor;
-        out_color[pix_id] = fmar(T, __ldg(bg), C0);
-        out_color[hw + pix_id] = fmar(T, __ldg(bg + 1), C1);
-        out_color[2 * hw + pix_id] = fmar(T, __ldg(bg + 2), C2);
-        out_alpha[pix_id] = Wacc;
-        out_depth[pix_id] = Dacc;
+    const size_t hw = (size_t)H * W;
+    const float b0 = __ldg(bg), b1 = __ldg(bg + 1), b2 = __ldg(bg + 2);
+    if (in0) {
+        n_contrib[pix_id] = last0;
+        out_color[pix_id] = fmar(T.x, b0, C0.x);
+        out_color[hw + pix_id] = fmar(T.x, b1, C1.x);
+        out_color[2 * hw + pix_id] = fmar(T.x, b2, C2.x);
+        out_alpha[pix_id] = Wacc.x;
+        out_depth[pix_id] = Dacc.x;
+    }
+    if (in1) {
+        const uint32_t p1 = pix_id + (uint32_t)W;
+        n_contrib[p1] = last1;
+        out_color[p1] = fmar(T.y, b0, C0.y);
+        out_color[hw + p1] = fmar(T.y, b1, C1.y);
+        out_color[2 * hw + p1] = fmar(T.y, b2, C2.y);
+        out_alpha[p1] = Wacc.y;
+        out_depth[p1] = Dacc.y;
     }
 }
 
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st) {
-    render_forward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
+    render_forward_kernel<<<gx * gy, FWD_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                    img.n_contrib, out_color, out_depth, out_alpha);
     return cudaGetLastError();
 }
