@@ -9,29 +9,10 @@
 //    of ten atomics per (pixel, Gaussian) pair;
 //  * accumulators live in one 48-byte slot per Gaussian (ACC_* in common.cuh) that the fused
 //    preprocess-backward kernel consumes.
-#include "common.cuh"
+#include "blend.cuh"
 #include <cstdlib>
 
 namespace gsr {
-
-__device__ __forceinline__ bool block_may_contribute_b(float x, float y, float a, float b, float c, float thr,
-                                                       float inv_a_b, float inv_c_b, bool convex,
-                                                       float px0, float px1, float py0, float py1) {
-    if (!convex) return true;
-    const float lx = x - px1, hx = x - px0, ly = y - py1, hy = y - py0;
-    const float cx = fminf(fmaxf(0.0f, lx), hx), cy = fminf(fmaxf(0.0f, ly), hy);
-    if (cx == 0.0f && cy == 0.0f) return true;
-    float qmin = 3.0e38f;
-    if (cx != 0.0f) {
-        const float dy = fminf(fmaxf(-inv_c_b * cx, ly), hy);
-        qmin = 0.5f * (a * cx * cx + c * dy * dy) + b * cx * dy;
-    }
-    if (cy != 0.0f) {
-        const float dx = fminf(fmaxf(-inv_a_b * cy, lx), hx);
-        qmin = fminf(qmin, 0.5f * (a * dx * dx + c * cy * cy) + b * dx * cy);
-    }
-    return !(-qmin < thr - 1e-3f - 1e-5f * fabsf(qmin));
-}
 
 // pair step of the multi-value butterfly: lanes with (lane & m) == 0 end up with p summed over
 // {lane, lane^m}, the others with q.
@@ -41,7 +22,9 @@ __device__ __forceinline__ float bfly_pair(float p, float q, int m, bool hi) {
 }
 __device__ __forceinline__ float bfly_one(float p, int m) { return p + __shfl_xor_sync(0xffffffffu, p, m); }
 
-__global__ void __launch_bounds__(256, 4)      // 64 registers: 4 CTAs/SM; measured 1.19 -> 1.06 ms at C2 (5 CTAs/SM: 1.09)
+__device__ __forceinline__ float hsum(float2 v) { return v.x + v.y; }
+
+__global__ void __launch_bounds__(BLEND_THREADS, 5)
 render_backward_kernel(int W, int H, int gx,
                        const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                        const GaussRec* __restrict__ recs, const float* __restrict__ bg,
@@ -49,47 +32,50 @@ render_backward_kernel(int W, int H, int gx,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
                        const float* __restrict__ dL_dalpha_pix, float* __restrict__ acc, int direct_max) {
     __shared__ __align__(16) GaussRec s_rec[2][BATCH];
-    __shared__ uint32_t s_bal[8][8];
-    __shared__ uint32_t s_max[8];
+    __shared__ uint32_t s_bal[4][8];          // [consumer warp block][32-record word of the round]
+    __shared__ uint32_t s_max[4];
 
     const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
     const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-    const int bx = (wid & 1) * 8, by = (wid >> 1) * 4;
-    const int pxi = tile_x + bx + (lane & 7), pyi = tile_y + by + (lane >> 3);
-    const bool inside = pxi < W && pyi < H;
-    const float pxf = (float)pxi, pyf = (float)pyi;
-    const uint32_t pix_id = (uint32_t)pyi * W + pxi;
+    const int bx = (wid & 1) * 8, by = (wid >> 1) * 8;
+    const int pxi = tile_x + bx + (lane & 7), pyi = tile_y + by + 2 * (lane >> 3);     // pixels (pxi, pyi) and (pxi, pyi+1)
+    const bool in0 = pxi < W && pyi < H, in1 = pxi < W && pyi + 1 < H;
+    const float pxf = (float)pxi;
+    const float2 npy = make_float2(-(float)pyi, -(float)(pyi + 1));
+    const uint32_t p0 = (uint32_t)pyi * W + pxi, p1 = p0 + (uint32_t)W;
     const size_t hw = (size_t)H * W;
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
 
-    const uint32_t last_contributor = inside ? n_contrib[pix_id] : 0u;
-    const float T_final = inside ? (1.0f - alphas[pix_id]) : 0.0f;
-    float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f, ddepth = 0.f, dalpha = 0.f;
-    if (inside) {
-        dpix0 = dL_dpix[pix_id]; dpix1 = dL_dpix[hw + pix_id]; dpix2 = dL_dpix[2 * hw + pix_id];
-        ddepth = dL_ddepth_pix[pix_id]; dalpha = dL_dalpha_pix[pix_id];
-    }
-    const float bg_dot_dpixel = __ldg(bg) * dpix0 + __ldg(bg + 1) * dpix1 + __ldg(bg + 2) * dpix2;
+    // per-pixel constants, .x = upper pixel, .y = lower pixel (zeros outside the image)
+    const uint32_t last0 = in0 ? n_contrib[p0] : 0u, last1 = in1 ? n_contrib[p1] : 0u;
+    const float2 T_final = make_float2(in0 ? 1.0f - alphas[p0] : 0.0f, in1 ? 1.0f - alphas[p1] : 0.0f);
+    auto ld2 = [&](const float* base) { return make_float2(in0 ? base[p0] : 0.0f, in1 ? base[p1] : 0.0f); };
+    const float2 dpix0 = ld2(dL_dpix), dpix1 = ld2(dL_dpix + hw), dpix2 = ld2(dL_dpix + 2 * hw);
+    const float2 ddepth = ld2(dL_ddepth_pix), dalpha = ld2(dL_dalpha_pix);
+    const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
+    // -T_final * (bg . dL_dpixel): the background term of dL/dalpha is this times 1/(1-alpha)  (backward.cu:545-549)
+    const float2 nTf_bgdot = make_float2(-T_final.x * (bg0 * dpix0.x + bg1 * dpix1.x + bg2 * dpix2.x),
+                                         -T_final.y * (bg0 * dpix0.y + bg1 * dpix1.y + bg2 * dpix2.y));
 
     // tile-wide maximum of n_contrib
     {
-        const uint32_t wm = __reduce_max_sync(0xffffffffu, last_contributor);
+        const uint32_t wm = __reduce_max_sync(0xffffffffu, max(last0, last1));
         if (lane == 0) s_max[wid] = wm;
     }
     __syncthreads();
-    uint32_t max_contrib = 0;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) max_contrib = max(max_contrib, s_max[w]);
+    const uint32_t max_contrib = max(max(s_max[0], s_max[1]), max(s_max[2], s_max[3]));
     if (max_contrib == 0 || total == 0) return;
     const uint32_t warp_max = s_max[wid];
 
-    float T = T_final;
-    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-    float adr = 0.f, ldp = 0.f, aar = 0.f, last_alpha = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+    // Running state per pixel. The reference carries (last_alpha, last_color, accum_rec) and forms
+    // accum_rec = last_alpha*last_color + (1-last_alpha)*accum_rec at the next contributor (backward.cu:512-528);
+    // B below is that value formed one step earlier, B <- B + alpha*(c - B), which is the identity for a
+    // non-contributing pixel (alpha = 0), so the pair needs no per-pixel selects.
+    float2 T = T_final, B0 = bc(0.f), B1 = bc(0.f), B2 = bc(0.f), Bd = bc(0.f), Ba = bc(0.f);
+    const float nddelx = -0.5f * W, nddely = -0.5f * H;
 
     // which reduced value this lane commits (see bfly order below)
     const bool b1 = lane & 2, b2 = lane & 4, b3 = lane & 8, b4 = lane & 16;
@@ -97,12 +83,16 @@ render_backward_kernel(int W, int H, int gx,
     const int slot = b1 ? (8 + (b4 ? 1 : 0)) : ((b2 ? 4 : 0) + (b3 ? 2 : 0) + (b4 ? 1 : 0));
 
     auto issue = [&](int r) {
-        const int p = r * BATCH + tid;
-        if (p < total) {
-            const uint32_t id = __ldg(point_list + range.x + p);
-            const char* src = reinterpret_cast<const char*>(recs + id);
-            char* dst = reinterpret_cast<char*>(&s_rec[r & 1][tid]);
-            cp_async16(dst, src); cp_async16(dst + 16, src + 16); cp_async16(dst + 32, src + 32);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int sl = tid + k * BLEND_THREADS;
+            const int p = r * BATCH + sl;
+            if (p < total) {
+                const uint32_t id = __ldg(point_list + range.x + p);
+                const char* src = reinterpret_cast<const char*>(recs + id);
+                char* dst = reinterpret_cast<char*>(&s_rec[r & 1][sl]);
+                cp_async16(dst, src); cp_async16(dst + 16, src + 16); cp_async16(dst + 32, src + 32);
+            }
         }
         cp_async_commit();
     };
@@ -116,25 +106,24 @@ render_backward_kernel(int W, int H, int gx,
 
         const int n_here = min(BATCH, total - r * BATCH);
         const GaussRec* buf = s_rec[r & 1];
-        {
-            uint32_t mask = 0;
-            if (tid < n_here) {
-                const float4 g0 = *reinterpret_cast<const float4*>(&buf[tid]);
-                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[tid]) + 1);
-                const float x = g0.x, y = g0.y, a = g0.z, b = g0.w, c = g1.x, thr = g1.w;
-                const bool convex = (a > 0.0f) && (c > 0.0f) && (a * c - b * b > 0.0f);
-                const float inv_a_b = convex ? b / a : 0.0f, inv_c_b = convex ? b / c : 0.0f;
 #pragma unroll
-                for (int w = 0; w < 8; ++w) {
-                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 4);
-                    if (block_may_contribute_b(x, y, a, b, c, thr, inv_a_b, inv_c_b, convex, x0, x0 + 7.0f, y0, y0 + 3.0f))
-                        mask |= 1u << w;
+        for (int k = 0; k < 2; ++k) {
+            const int sl = tid + k * BLEND_THREADS;
+            uint32_t mask = 0;
+            if (sl < n_here) {
+                const float4 g0 = *reinterpret_cast<const float4*>(&buf[sl]);
+                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[sl]) + 1);
+                const CullRec c = cull_prepare(g0.x, g0.y, g0.z, g0.w, g1.x, g1.w);
+#pragma unroll
+                for (int w = 0; w < 4; ++w) {
+                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 8);
+                    if (block_may_contribute(c, x0, x0 + 7.0f, y0, y0 + 7.0f)) mask |= 1u << w;
                 }
             }
 #pragma unroll
-            for (int w = 0; w < 8; ++w) {
+            for (int w = 0; w < 4; ++w) {
                 const uint32_t bal = __ballot_sync(0xffffffffu, (mask >> w) & 1u);
-                if (lane == 0) s_bal[w][wid] = bal;
+                if (lane == 0) s_bal[w][wid + 4 * k] = bal;
             }
         }
         __syncthreads();
@@ -151,51 +140,59 @@ render_backward_kernel(int W, int H, int gx,
 
                 const float4 g0 = *reinterpret_cast<const float4*>(&buf[j]);
                 const float4 g1 = *(reinterpret_cast<const float4*>(&buf[j]) + 1);
-                const float dx = subr(g0.x, pxf), dy = subr(g0.y, pyf);
-                const float power = fmar(fmar(dx, mulr(dx, g0.z), mulr(dy, mulr(dy, g1.x))), -0.5f,
-                                         -mulr(dy, mulr(dx, g0.w)));
-                bool act = (pos < last_contributor) && !(power > 0.0f) && !(power < g1.w);
-                float G = 0.f, alpha = 0.f;
-                if (act) {
-                    G = expf(power);
-                    alpha = fminf(0.99f, mulr(g1.y, G));
-                    act = !(alpha < 1.0f / 255.0f);
+                float dx; float2 dy;
+                const float2 power = pair_power(g0.x, g0.y, g0.z, g0.w, g1.x, pxf, npy, dx, dy);
+                bool a0 = (pos < last0) && !(power.x > 0.0f) && !(power.x < g1.w);
+                bool a1 = (pos < last1) && !(power.y > 0.0f) && !(power.y < g1.w);
+                float2 G = bc(0.f), alpha = bc(0.f);
+                if (a0 || a1) {
+                    G = expf2_nonpos(power);                          // the forward's expf, bit for bit
+                    const float2 ga = __fmul2_rn(bc(g1.y), G);
+                    alpha = make_float2(fminf(0.99f, ga.x), fminf(0.99f, ga.y));
+                    a0 = a0 && !(alpha.x < 1.0f / 255.0f);
+                    a1 = a1 && !(alpha.y < 1.0f / 255.0f);
                 }
+                const bool act = a0 || a1;
                 const uint32_t act_mask = __ballot_sync(0xffffffffu, act);
                 if (act_mask == 0) continue;
 
                 float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f, v8 = 0.f, v9 = 0.f;
                 if (act) {
+                    // a pixel that does not take this Gaussian runs with G = alpha = 0, 1/(1-alpha) = 1: every term
+                    // below is then zero and its state unchanged (finite colours and depth assumed)
+                    if (!a0) { G.x = 0.f; alpha.x = 0.f; }
+                    if (!a1) { G.y = 0.f; alpha.y = 0.f; }
                     const float4 g2 = *(reinterpret_cast<const float4*>(&buf[j]) + 2);
-                    const float inv_1ma = __frcp_rn(1.f - alpha);     // shared by the two divisions below (gradients: rtol 1e-4)
-                    T = T * inv_1ma;
-                    const float w = alpha * T;                       // dchannel_dcolor
-                    float dL_dopa = 0.0f;
-                    ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = g2.x; dL_dopa += (g2.x - ar0) * dpix0;
-                    ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = g2.y; dL_dopa += (g2.y - ar1) * dpix1;
-                    ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = g2.z; dL_dopa += (g2.z - ar2) * dpix2;
-                    v6 = w * dpix0; v7 = w * dpix1; v8 = w * dpix2;
-                    adr = last_alpha * ldp + (1.f - last_alpha) * adr; ldp = g1.z;
-                    dL_dopa += (g1.z - adr) * ddepth;
-                    v9 = w * ddepth;
-                    aar = last_alpha + (1.f - last_alpha) * aar;
-                    dL_dopa += (1.f - aar) * dalpha;
-                    dL_dopa *= T;
-                    last_alpha = alpha;
-                    dL_dopa += (-T_final * inv_1ma) * bg_dot_dpixel;
-                    const float dL_dG = g1.y * dL_dopa;
-                    const float gdx = G * dx, gdy = G * dy;
-                    const float dG_ddelx = -gdx * g0.z - gdy * g0.w;
-                    const float dG_ddely = -gdy * g1.x - gdx * g0.w;
-                    v0 = dL_dG * dG_ddelx * ddelx_dx;
-                    v1 = dL_dG * dG_ddely * ddely_dy;
-                    v2 = -0.5f * gdx * dx * dL_dG;
-                    v3 = -0.5f * gdx * dy * dL_dG;
-                    v4 = -0.5f * gdy * dy * dL_dG;
-                    v5 = G * dL_dopa;
+                    const float2 oma = __ffma2_rn(alpha, bc(-1.0f), bc(1.0f));
+                    const float2 inv = make_float2(a0 ? rcp_approx(oma.x) : 1.0f, a1 ? rcp_approx(oma.y) : 1.0f);
+                    T = __fmul2_rn(T, inv);
+                    const float2 w = __fmul2_rn(alpha, T);                  // dchannel_dcolor
+                    const float2 d0 = __ffma2_rn(B0, bc(-1.0f), bc(g2.x)), d1 = __ffma2_rn(B1, bc(-1.0f), bc(g2.y));
+                    const float2 d2 = __ffma2_rn(B2, bc(-1.0f), bc(g2.z)), dd = __ffma2_rn(Bd, bc(-1.0f), bc(g1.z));
+                    const float2 da = __ffma2_rn(Ba, bc(-1.0f), bc(1.0f));
+                    float2 dL = __fmul2_rn(d0, dpix0);
+                    dL = __ffma2_rn(d1, dpix1, dL); dL = __ffma2_rn(d2, dpix2, dL);
+                    dL = __ffma2_rn(dd, ddepth, dL); dL = __ffma2_rn(da, dalpha, dL);
+                    B0 = __ffma2_rn(alpha, d0, B0); B1 = __ffma2_rn(alpha, d1, B1); B2 = __ffma2_rn(alpha, d2, B2);
+                    Bd = __ffma2_rn(alpha, dd, Bd); Ba = __ffma2_rn(alpha, da, Ba);
+                    v6 = hsum(__fmul2_rn(w, dpix0)); v7 = hsum(__fmul2_rn(w, dpix1)); v8 = hsum(__fmul2_rn(w, dpix2));
+                    v9 = hsum(__fmul2_rn(w, ddepth));
+                    dL = __ffma2_rn(dL, T, __fmul2_rn(nTf_bgdot, inv));     // dL/dalpha
+                    const float2 dLdG = __fmul2_rn(bc(g1.y), dL);
+                    const float2 gdx = __fmul2_rn(G, bc(dx)), gdy = __fmul2_rn(G, dy);
+                    const float2 dGx = __ffma2_rn(gdx, bc(g0.z), __fmul2_rn(gdy, bc(g0.w)));      // -dG/ddelx
+                    const float2 dGy = __ffma2_rn(gdy, bc(g1.x), __fmul2_rn(gdx, bc(g0.w)));      // -dG/ddely
+                    v0 = hsum(__fmul2_rn(__fmul2_rn(dLdG, dGx), bc(nddelx)));
+                    v1 = hsum(__fmul2_rn(__fmul2_rn(dLdG, dGy), bc(nddely)));
+                    const float2 hg = __fmul2_rn(dLdG, bc(-0.5f));
+                    const float2 X = __fmul2_rn(hg, gdx);
+                    v2 = hsum(__fmul2_rn(X, bc(dx)));
+                    v3 = hsum(__fmul2_rn(X, dy));
+                    v4 = hsum(__fmul2_rn(__fmul2_rn(hg, gdy), dy));
+                    v5 = hsum(__fmul2_rn(G, dL));
                 }
-                // Few contributing pixels (splat edges): the active lanes commit their terms directly, 10 predicated
-                // RED instructions instead of the ~45-instruction butterfly below.
+                // Few contributing threads (splat edges): they commit their terms directly, 10 predicated RED
+                // instructions instead of the ~45-instruction butterfly below.
                 if (__popc(act_mask) <= direct_max) {
                     if (act) {
                         float* a = acc + (size_t)__ldg(point_list + range.x + pos) * ACC_STRIDE;
@@ -205,11 +202,10 @@ render_backward_kernel(int W, int H, int gx,
                     continue;
                 }
                 // 10 values -> 12 shuffles; final owner lanes given by (writer, slot)
-                const float a0 = bfly_pair(v0, v1, 16, b4), a1 = bfly_pair(v2, v3, 16, b4), a2 = bfly_pair(v4, v5, 16, b4);
-                const float a3 = bfly_pair(v6, v7, 16, b4), a4 = bfly_pair(v8, v9, 16, b4);
-                const float c0 = bfly_pair(a0, a1, 8, b3), c1 = bfly_pair(a2, a3, 8, b3), c2 = bfly_one(a4, 8);
-                const float d0 = bfly_pair(c0, c1, 4, b2), d1 = bfly_one(c2, 4);
-                const float e0 = bfly_pair(d0, d1, 2, b1);
+                const float a0_ = bfly_pair(v0, v1, 16, b4), a1_ = bfly_pair(v2, v3, 16, b4), a2_ = bfly_pair(v4, v5, 16, b4);
+                const float a3_ = bfly_pair(v6, v7, 16, b4), a4_ = bfly_pair(v8, v9, 16, b4);
+                const float c0 = bfly_pair(a0_, a1_, 8, b3), c1 = bfly_pair(a2_, a3_, 8, b3), c2 = bfly_one(a4_, 8);
+                const float e0 = bfly_pair(bfly_pair(c0, c1, 4, b2), bfly_one(c2, 4), 2, b1);
                 const float f0 = bfly_one(e0, 1);
                 if (writer && f0 != 0.0f) {
                     const uint32_t id = __ldg(point_list + range.x + pos);
@@ -232,7 +228,7 @@ cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState
                                    const BinningState& bin, const float* bg, const float* out_alpha,
                                    const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
                                    float* acc, cudaStream_t st) {
-    render_backward_kernel<<<gx * gy, 256, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,
+    render_backward_kernel<<<gx * gy, BLEND_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,
                                                     img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(8));
     return cudaGetLastError();
 }

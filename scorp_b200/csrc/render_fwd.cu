@@ -10,45 +10,11 @@
 // threshold) and the warps exchange 8 ballots; (3) each warp blends only the entries whose bit
 // is set. Skipped (pixel, Gaussian) pairs are exactly pairs the reference also skips
 // (power > 0 or alpha < 1/255), so the image, alpha, depth and n_contrib are bit-identical.
-#include "common.cuh"
+#include "blend.cuh"
 
 namespace gsr {
 
-// Lower bound test: can record (x,y,a,b,c,thr) reach power >= thr anywhere in the pixel
-// rectangle [px0,px1]x[py0,py1]?  q(d) = 0.5(a dx^2 + c dy^2) + b dx dy, power = -q.
-// cull_prepare does the per-record part once (two approximate reciprocals; the minimiser only has to be
-// accurate to first order because q is stationary there, and the slack below covers the rest).
-struct CullRec { float x, y, a, b, c, thr, b_over_a, b_over_c; bool convex; };
-__device__ __forceinline__ float rcp_approx(float v) { float r; asm("rcp.approx.f32 %0, %1;" : "=f"(r) : "f"(v)); return r; }
-__device__ __forceinline__ CullRec cull_prepare(float x, float y, float a, float b, float c, float thr) {
-    CullRec r{x, y, a, b, c, thr, 0.0f, 0.0f, false};
-    // strictly convex and well scaled; anything else is never culled
-    r.convex = (a > 1e-30f) && (c > 1e-30f) && (a < 1e30f) && (c < 1e30f) && (a * c - b * b > 0.0f);
-    if (r.convex) { r.b_over_a = b * rcp_approx(a); r.b_over_c = b * rcp_approx(c); }
-    return r;
-}
-__device__ __forceinline__ bool block_may_contribute(const CullRec& g, float px0, float px1, float py0, float py1) {
-    if (!g.convex) return true;
-    // d = mean - pixel; pixel in [p0,p1]  =>  d in [m - p1, m - p0]
-    const float lx = g.x - px1, hx = g.x - px0, ly = g.y - py1, hy = g.y - py0;
-    const float cx = fminf(fmaxf(0.0f, lx), hx), cy = fminf(fmaxf(0.0f, ly), hy);
-    if (cx == 0.0f && cy == 0.0f) return true;
-    float qmin = 3.0e38f;
-    if (cx != 0.0f) {   // facing vertical edge dx = cx
-        const float dy = fminf(fmaxf(-g.b_over_c * cx, ly), hy);
-        qmin = 0.5f * (g.a * cx * cx + g.c * dy * dy) + g.b * cx * dy;
-    }
-    if (cy != 0.0f) {   // facing horizontal edge dy = cy
-        const float dx = fminf(fmaxf(-g.b_over_a * cy, lx), hx);
-        qmin = fminf(qmin, 0.5f * (g.a * dx * dx + g.c * cy * cy) + g.b * dx * cy);
-    }
-    // keep unless provably below threshold (slack covers rounding of this test; NaN keeps)
-    return !(-qmin < g.thr - 1e-3f - 1e-5f * fabsf(qmin));
-}
-
-__device__ __forceinline__ float2 bc(float v) { return make_float2(v, v); }    // scalar operand of a packed op (SASS: Rn.F32)
-
-constexpr int FWD_THREADS = 128;    // 4 warps x (8x8 pixel block, two vertically adjacent pixels per thread)
+constexpr int FWD_THREADS = BLEND_THREADS;
 
 __global__ void __launch_bounds__(FWD_THREADS, 8)
 render_forward_kernel(int W, int H, int gx,
@@ -76,7 +42,7 @@ render_forward_kernel(int W, int H, int gx,
     // per-pixel state, .x = upper pixel, .y = lower pixel
     float2 T = bc(1.0f), C0 = bc(0.0f), C1 = bc(0.0f), C2 = bc(0.0f), Dacc = bc(0.0f), Wacc = bc(0.0f);
     uint32_t last0 = 0, last1 = 0;
-    bool done0 = !in0, done1 = !in1;
+    uint32_t live = (in0 ? 1u : 0u) | (in1 ? 2u : 0u);      // bit h: pixel h still blending
 
     auto issue = [&](int r) {
 #pragma unroll
@@ -96,7 +62,7 @@ render_forward_kernel(int W, int H, int gx,
     if (rounds > 0) issue(0);
     for (int r = 0; r < rounds; ++r) {
         // all pixels finished? (also orders the previous round's reads before buffer reuse)
-        if (__syncthreads_and(done0 && done1)) break;
+        if (__syncthreads_and(live == 0u)) break;
         if (r + 1 < rounds) { issue(r + 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
         __syncthreads();
 
@@ -125,36 +91,32 @@ render_forward_kernel(int W, int H, int gx,
         }
         __syncthreads();
 
-        if (!__all_sync(0xffffffffu, done0 && done1)) {
+        if (__any_sync(0xffffffffu, live != 0u)) {
             const uint32_t pos_base = (uint32_t)(r * BATCH) + 1u;
             for (int v = 0; v < 8; ++v) {
                 uint32_t bits = s_bal[wid][v];
                 while (bits) {
                     const int j = v * 32 + __ffs(bits) - 1;
                     bits &= bits - 1;
-                    if (done0 && done1) continue;
+                    if (live == 0u) continue;
                     const float4 g0 = *reinterpret_cast<const float4*>(&buf[j]);
                     const float4 g1 = *(reinterpret_cast<const float4*>(&buf[j]) + 1);
-                    // forward.cu:334 with the reference build's contraction; the two pixels share dx
-                    const float dx = subr(g0.x, pxf);
-                    const float A = mulr(dx, g0.z), Bn = -mulr(dx, g0.w);
-                    const float2 dy = __fadd2_rn(bc(g0.y), npy);
-                    const float2 q = __ffma2_rn(bc(dx), bc(A), __fmul2_rn(dy, __fmul2_rn(dy, bc(g1.x))));
-                    const float2 power = __ffma2_rn(q, bc(-0.5f), __fmul2_rn(dy, bc(Bn)));
-                    // skip: power > 0, or power < thr (implies alpha < 1/255), or the pixel is finished
-                    const bool s0 = done0 || (power.x > 0.0f) || (power.x < g1.w);
-                    const bool s1 = done1 || (power.y > 0.0f) || (power.y < g1.w);
-                    if (s0 && s1) continue;
-                    float2 alpha = bc(0.0f);
-                    if (!s0) alpha.x = fminf(0.99f, mulr(g1.y, expf(power.x)));
-                    if (!s1) alpha.y = fminf(0.99f, mulr(g1.y, expf(power.y)));
-                    bool c0 = !s0 && !(alpha.x < 1.0f / 255.0f), c1 = !s1 && !(alpha.y < 1.0f / 255.0f);
-                    if (!c0) alpha.x = 0.0f;
-                    if (!c1) alpha.y = 0.0f;
-                    // test_T = T * (1 - alpha); halves with alpha == 0 keep T exactly
+                    float dx; float2 dy;
+                    const float2 power = pair_power(g0.x, g0.y, g0.z, g0.w, g1.x, pxf, npy, dx, dy);
+                    // candidate: still blending, power <= 0 and power >= thr (below thr implies alpha < 1/255)
+                    bool c0 = (live & 1u) && !(power.x > 0.0f) && !(power.x < g1.w);
+                    bool c1 = (live & 2u) && !(power.y > 0.0f) && !(power.y < g1.w);
+                    if (!(c0 || c1)) continue;
+                    const float2 ga = __fmul2_rn(bc(g1.y), expf2_nonpos(power));
+                    float2 alpha = make_float2(fminf(0.99f, ga.x), fminf(0.99f, ga.y));
+                    c0 = c0 && !(alpha.x < 1.0f / 255.0f);
+                    c1 = c1 && !(alpha.y < 1.0f / 255.0f);
+                    alpha.x = c0 ? alpha.x : 0.0f;
+                    alpha.y = c1 ? alpha.y : 0.0f;
+                    // test_T = T * (1 - alpha); a half with alpha == 0 keeps T exactly
                     const float2 test_T = __fmul2_rn(T, __ffma2_rn(alpha, bc(-1.0f), bc(1.0f)));
-                    if (c0 && test_T.x < 0.0001f) { done0 = true; c0 = false; alpha.x = 0.0f; }
-                    if (c1 && test_T.y < 0.0001f) { done1 = true; c1 = false; alpha.y = 0.0f; }
+                    if (test_T.x < 0.0001f) { live &= ~1u; c0 = false; alpha.x = 0.0f; }     // T >= 1e-4 always, so only a
+                    if (test_T.y < 0.0001f) { live &= ~2u; c1 = false; alpha.y = 0.0f; }     // contributing half can trip this
                     if (!(c0 || c1)) continue;
                     const float4 g2 = *(reinterpret_cast<const float4*>(&buf[j]) + 2);
                     // a half with alpha == 0 adds T*0 (finite colours and depth assumed)
@@ -166,7 +128,7 @@ render_forward_kernel(int W, int H, int gx,
                     if (c0) { T.x = test_T.x; last0 = pos_base + (uint32_t)j; }
                     if (c1) { T.y = test_T.y; last1 = pos_base + (uint32_t)j; }
                 }
-                if (__all_sync(0xffffffffu, done0 && done1)) break;
+                if (!__any_sync(0xffffffffu, live != 0u)) break;
             }
         }
     }
