@@ -24,7 +24,7 @@ __device__ __forceinline__ float bfly_one(float p, int m) { return p + __shfl_xo
 
 __device__ __forceinline__ float hsum(float2 v) { return v.x + v.y; }
 
-__global__ void __launch_bounds__(BLEND_THREADS, 5)
+__global__ void __launch_bounds__(BLEND_THREADS, 8)
 render_backward_kernel(int W, int H, int gx,
                        const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                        const GaussRec* __restrict__ recs, const float* __restrict__ bg,
