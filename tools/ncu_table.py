@@ -40,8 +40,12 @@ def main():
     lines = [f"# ncu --set full, config {cfg} ({Path(rep).name}); one launch per kernel from the 3rd resident step\n",
              "| kernel | " + " | ".join(c[1] for c in COLS) + " |", "|---|" + "---|" * len(COLS)]
     traffic = {}
+    seen = set()
     for r in data:
         name = r[ix["Kernel Name"]].split("(")[0].replace("void ", "").replace("gsr::", "")
+        if name in seen:            # the capture window may wrap into the next step: first launch of each kernel only
+            continue
+        seen.add(name)
         base = name.split("<")[0]
         cells = []
         for key, _ in COLS:
