@@ -152,13 +152,14 @@ int gsr_rasterize_forward(
     const int N = (int)n_host[0], max_len = (int)n_host[1];
     *num_rendered = N;
 
-    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr));
+    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, gx * gy));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
-    carve_binning(bbase, N, &bin);
+    carve_binning(bbase, N, &bin, nullptr, gx * gy);
 
     if ((rc = check_cuda(launch_binning(P, gx, gy, N, max_len, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
+    if ((rc = check_cuda(cudaMemsetAsync(bin.contrib, 0, contrib_slots(N, gx * gy) * sizeof(uint4), st), "memset contribution masks"))) return rc;
     if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st),
                          "render forward launch"))) return rc;
     prof_mark(3, st);
@@ -191,7 +192,7 @@ int gsr_rasterize_backward(
     GeomState g; ImageState img; BinningState bin;
     carve_geom((char*)geom, P, tiles, &g);
     carve_image((char*)image, W, H, &img);
-    carve_binning((char*)binning, R, &bin);
+    carve_binning((char*)binning, R, &bin, nullptr, gx * gy);
 
     float* acc = (float*)workspace;
     int rc;

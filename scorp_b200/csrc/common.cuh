@@ -48,7 +48,12 @@ struct BinningState {
     uint32_t* point_list;
     uint64_t* point_list_keys;
     uint64_t* scratch;
+    uint4*    contrib;        // forward -> backward: per 32 list entries of a tile, one word per warp block with a bit
+                              // for every entry that contributed to some pixel of that block (3DGS blends)
 };
+// first contrib slot of a tile whose list starts at `first`: slots of different tiles never overlap because
+// floor((x+len)/32) + 1 >= floor(x/32) + ceil(len/32)
+__host__ __device__ inline size_t contrib_base(uint32_t first, int tile) { return (size_t)(first >> 5) + (size_t)tile; }
 
 inline size_t align_up(size_t v, size_t a = 256) { return (v + a - 1) / a * a; }
 
@@ -78,15 +83,17 @@ inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off =
     if (s) { s->ranges = (uint2*)(base + a0); s->n_contrib = (uint32_t*)(base + a1); s->tile_order = (uint32_t*)(base + a2); }
     return o;
 }
-inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nullptr) {
+inline size_t contrib_slots(int N, int tiles) { return (size_t)(N > 0 ? N : 0) / 32 + (size_t)tiles + 2; }
+inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nullptr, int tiles = 0) {
     size_t n = (size_t)(N > 0 ? N : 1);
     size_t o = 0;
     size_t a0 = o; o = align_up(o + n * 4);
     size_t a1 = o; o = align_up(o + n * 8);
     size_t a2 = o; o = align_up(o + n * 8);
+    size_t a3 = o; o = align_up(o + contrib_slots(N, tiles) * sizeof(uint4));     // last: the public offsets do not move
     if (off) { off[0] = a0; off[1] = a1; off[2] = a2; }
     if (b) { b->point_list = (uint32_t*)(base + a0); b->point_list_keys = (uint64_t*)(base + a1);
-             b->scratch = (uint64_t*)(base + a2); }
+             b->scratch = (uint64_t*)(base + a2); b->contrib = (uint4*)(base + a3); }
     return o;
 }
 

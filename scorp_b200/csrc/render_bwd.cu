@@ -30,7 +30,8 @@ render_backward_kernel(int W, int H, int gx,
                        const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                        const float* __restrict__ alphas, const uint32_t* __restrict__ n_contrib,
                        const float* __restrict__ dL_dpix, const float* __restrict__ dL_ddepth_pix,
-                       const float* __restrict__ dL_dalpha_pix, float* __restrict__ acc, int direct_max) {
+                       const float* __restrict__ dL_dalpha_pix, float* __restrict__ acc, int direct_max,
+                       const uint32_t* __restrict__ contrib) {
     __shared__ __align__(16) GaussRec s_rec[2][BATCH];
     __shared__ uint32_t s_bal[4][8];          // [consumer warp block][32-record word of the round]
     __shared__ uint32_t s_max[4];
@@ -48,6 +49,7 @@ render_backward_kernel(int W, int H, int gx,
 
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
+    const uint32_t* my_contrib = contrib + contrib_base(range.x, tile) * 4;
 
     // per-pixel constants, .x = upper pixel, .y = lower pixel (zeros outside the image)
     const uint32_t last0 = in0 ? n_contrib[p0] : 0u, last1 = in1 ? n_contrib[p1] : 0u;
@@ -104,27 +106,12 @@ render_backward_kernel(int W, int H, int gx,
         if (r > 0) { issue(r - 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
         __syncthreads();
 
-        const int n_here = min(BATCH, total - r * BATCH);
         const GaussRec* buf = s_rec[r & 1];
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const int sl = tid + k * BLEND_THREADS;
-            uint32_t mask = 0;
-            if (sl < n_here) {
-                const float4 g0 = *reinterpret_cast<const float4*>(&buf[sl]);
-                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[sl]) + 1);
-                const CullRec c = cull_prepare(g0.x, g0.y, g0.z, g0.w, g1.x, g1.w);
-#pragma unroll
-                for (int w = 0; w < 4; ++w) {
-                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 8);
-                    if (block_may_contribute(c, x0, x0 + 7.0f, y0, y0 + 7.0f)) mask |= 1u << w;
-                }
-            }
-#pragma unroll
-            for (int w = 0; w < 4; ++w) {
-                const uint32_t bal = __ballot_sync(0xffffffffu, (mask >> w) & 1u);
-                if (lane == 0) s_bal[w][wid + 4 * k] = bal;
-            }
+        // which entries to visit: the forward recorded, per warp block, the entries that blended into some pixel
+        // of the block (render_fwd.cu); everything else contributes nothing here either
+        if (tid < 32) {
+            const int w = tid >> 3, v = tid & 7;
+            s_bal[w][v] = (r * BATCH + v * 32 < total) ? __ldg(my_contrib + (size_t)(r * 8 + v) * 4 + w) : 0u;
         }
         __syncthreads();
 
@@ -229,7 +216,8 @@ cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState
                                    const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,
                                    float* acc, cudaStream_t st) {
     render_backward_kernel<<<gx * gy, BLEND_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,
-                                                    img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(8));
+                                                    img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(8),
+                                                              reinterpret_cast<const uint32_t*>(bin.contrib));
     return cudaGetLastError();
 }
 

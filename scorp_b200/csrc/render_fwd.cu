@@ -21,7 +21,7 @@ render_forward_kernel(int W, int H, int gx,
                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                       const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                       uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
-                      float* __restrict__ out_depth, float* __restrict__ out_alpha) {
+                      float* __restrict__ out_depth, float* __restrict__ out_alpha, uint32_t* __restrict__ contrib) {
     __shared__ __align__(16) GaussRec s_rec[2][BATCH];
     __shared__ uint32_t s_bal[4][8];          // [consumer warp block][32-record word of the round]
 
@@ -38,6 +38,8 @@ render_forward_kernel(int W, int H, int gx,
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const int rounds = (total + BATCH - 1) / BATCH;
+    // contribution words of this warp block for the backward (zero-initialised by the caller): bit = list entry
+    uint32_t* my_contrib = contrib + contrib_base(range.x, tile) * 4 + wid;
 
     // per-pixel state, .x = upper pixel, .y = lower pixel
     float2 T = bc(1.0f), C0 = bc(0.0f), C1 = bc(0.0f), C2 = bc(0.0f), Dacc = bc(0.0f), Wacc = bc(0.0f);
@@ -95,9 +97,12 @@ render_forward_kernel(int W, int H, int gx,
             const uint32_t pos_base = (uint32_t)(r * BATCH) + 1u;
             for (int v = 0; v < 8; ++v) {
                 uint32_t bits = s_bal[wid][v];
+                uint32_t took_bits = 0;           // per lane; OR-reduced over the warp after the word
                 while (bits) {
                     const int j = v * 32 + __ffs(bits) - 1;
-                    bits &= bits - 1;
+                    const uint32_t rest = bits & (bits - 1);
+                    const uint32_t bit = bits ^ rest;
+                    bits = rest;
                     if (live == 0u) continue;
                     const float4 g0 = *reinterpret_cast<const float4*>(&buf[j]);
                     const float4 g1 = *(reinterpret_cast<const float4*>(&buf[j]) + 1);
@@ -127,7 +132,11 @@ render_forward_kernel(int W, int H, int gx,
                     Dacc = __ffma2_rn(T, __fmul2_rn(alpha, bc(g1.z)), Dacc);
                     if (c0) { T.x = test_T.x; last0 = pos_base + (uint32_t)j; }
                     if (c1) { T.y = test_T.y; last1 = pos_base + (uint32_t)j; }
+                    took_bits |= bit;
                 }
+                // the backward walks exactly the (warp block, entry) visits that blended something here
+                took_bits = __reduce_or_sync(0xffffffffu, took_bits);
+                if (lane == 0 && took_bits) my_contrib[(size_t)(r * 8 + v) * 4] = took_bits;
                 if (!__any_sync(0xffffffffu, live != 0u)) break;
             }
         }
@@ -159,7 +168,8 @@ cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState&
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st) {
     render_forward_kernel<<<gx * gy, FWD_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
-                                                   img.n_contrib, out_color, out_depth, out_alpha);
+                                                   img.n_contrib, out_color, out_depth, out_alpha,
+                                                           reinterpret_cast<uint32_t*>(bin.contrib));
     return cudaGetLastError();
 }
 

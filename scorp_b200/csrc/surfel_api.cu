@@ -75,9 +75,9 @@ int gsr_surfel_forward(
     const int N = (int)n_host[0], max_len = (int)n_host[1];
     *num_rendered = N;
 
-    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr));
+    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, gx * gy));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
-    carve_binning(bbase, N, &bin);
+    carve_binning(bbase, N, &bin, nullptr, gx * gy);
     if ((rc = check_cuda(launch_binning(P, gx, gy, N, max_len, g.rec, (int)sizeof(SurfelRec), SURFEL_DEPTH_OFF, g.tile_count, radii,
                                         img.ranges, bin, st), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
@@ -114,7 +114,7 @@ int gsr_surfel_backward(
     SurfelGeom g; SurfelImage img; BinningState bin;
     carve_surfel_geom((char*)geom, P, tiles, &g);
     carve_surfel_image((char*)image, W, H, &img);
-    carve_binning((char*)binning, R, &bin);
+    carve_binning((char*)binning, R, &bin, nullptr, gx * gy);
 
     float* acc = (float*)workspace;
     int rc;
