@@ -23,12 +23,13 @@ preprocess_backward_kernel(BwdArgs a) {
     if constexpr (M3 != 0) {
         s_vis[threadIdx.x] = vis;
         __syncthreads();
-        sh_tile_load<M3>(a.shs, row0, nrows, s_vis, s_sh);
-        __syncthreads();
+        // asynchronous (LDGSTS): the whole tile is in flight while the per-Gaussian inputs below are fetched and
+        // the covariance part is computed; waited for just before the SH backward
+        sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
     }
 
     float dcov[6] = { 0, 0, 0, 0, 0, 0 };
-    V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, dscale = { 0, 0, 0 };
+    V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, dscale = { 0, 0, 0 }, m = { 0, 0, 0 };
     float4 drot = { 0, 0, 0, 0 };
     float dop = 0.0f;
     float* const my_sh = s_sh + threadIdx.x * ShTile<M3>::STRIDE;      // coefficients in, gradients out (in place)
@@ -44,7 +45,7 @@ preprocess_backward_kernel(BwdArgs a) {
         dcol = { q1.z, q1.w, q2.x };
         const float ddepth = q2.y;
 
-        const V3 m = ld3(a.means3D + 3 * idx);
+        m = ld3(a.means3D + 3 * idx);
         const float* v = a.view;
         const float* p = a.proj;
         const float* c = a.cov3D + 6 * (size_t)idx;
@@ -109,13 +110,6 @@ preprocess_backward_kernel(BwdArgs a) {
         dmean.y += (v[6] - v[7] * mul3) * ddepth;
         dmean.z += (v[10] - v[11] * mul3) * ddepth;
 
-        // ---- colour -> SH (+ mean)
-        if constexpr (M3 != 0) {
-            const uint8_t cl = a.clamped[idx];
-            const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
-            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
-        }
-
         // ---- cov3D -> scale, rotation (backward.cu:278-341)
         if (!a.cov_precomp) {
             const float* qp = a.rotations + 4 * (size_t)idx;
@@ -144,6 +138,14 @@ preprocess_backward_kernel(BwdArgs a) {
         }
     }
     if constexpr (M3 != 0) {
+        // ---- colour -> SH (+ mean)
+        const uint8_t cl = vis ? a.clamped[idx] : 0;
+        cp_async_wait<0>();
+        __syncthreads();
+        if (vis) {
+            const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
+            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
+        }
         __syncthreads();
         sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);
     }

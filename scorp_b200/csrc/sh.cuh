@@ -160,6 +160,23 @@ __device__ __forceinline__ void sh_tile_load(const float* __restrict__ shs, size
         if (s_vis[g]) s_sh[g * ShTile<M3>::STRIDE + c] = __ldg(src + e);
     }
 }
+// same tile, fetched with 4-byte cp.async (the odd row stride rules out wider ones): every element of the tile is
+// in flight at once; the caller waits (cp_async_wait<0> + barrier) before reading s_sh
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" :: "r"(d), "l"(gsrc));
+}
+template <int M3>
+__device__ __forceinline__ void sh_tile_load_async(const float* __restrict__ shs, size_t row0, int nrows,
+                                                   const uint8_t* s_vis, float* s_sh) {
+    const float* src = shs + row0 * M3;
+#pragma unroll 8
+    for (int e = threadIdx.x; e < nrows * M3; e += SH_TILE) {
+        const int g = e / M3, c = e - g * M3;
+        if (s_vis[g]) cp_async4(s_sh + g * ShTile<M3>::STRIDE + c, src + e);
+    }
+    cp_async_commit();
+}
 template <int M3>
 __device__ __forceinline__ void sh_tile_store(float* __restrict__ dsh, size_t row0, int nrows,
                                               const uint8_t* s_vis, const float* s_sh) {

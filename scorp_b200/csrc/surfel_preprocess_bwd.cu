@@ -24,12 +24,12 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
     if constexpr (M3 != 0) {
         s_vis[threadIdx.x] = vis;
         __syncthreads();
-        sh_tile_load<M3>(a.shs, row0, nrows, s_vis, s_sh);
-        __syncthreads();
+        // asynchronous (LDGSTS): in flight while the per-surfel inputs are fetched and the transMat part is computed
+        sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
     }
 
     float dT[3][3] = { { 0, 0, 0 }, { 0, 0, 0 }, { 0, 0, 0 } };   // column-major like glm: dT[j] = gradient of row j of transMat
-    V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 };
+    V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, m = { 0, 0, 0 };
     float dscale0 = 0.f, dscale1 = 0.f, dop = 0.f;
     float4 drot = { 0, 0, 0, 0 };
     float* const my_sh = s_sh + threadIdx.x * ShTile<M3>::STRIDE;      // coefficients in, gradients out (in place)
@@ -56,7 +56,7 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         const float4* rq = reinterpret_cast<const float4*>(a.rec + idx);
         const float4 r0 = __ldg(rq), r1 = __ldg(rq + 1), r2 = __ldg(rq + 2);
         const float Tfwd[9] = { r0.z, r0.w, r1.x, r1.y, r1.z, r1.w, r2.x, r2.y, r2.z };   // forward transMat
-        const V3 m = ld3(a.means3D + 3 * idx);
+        m = ld3(a.means3D + 3 * idx);
         const float* v = a.view;
         const float* pr = a.proj;
 
@@ -165,12 +165,6 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             dmean = { dM[2][0], dM[2][1], dM[2][2] };
         }
 
-        if constexpr (M3 != 0) {
-            const uint8_t cl = a.clamped[idx];
-            const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
-            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
-        }
-
         // densification hack (backward.cu:632-635)
         const float depth = Tfwd[8];
         dm2d.x = (float)(dT_out[2] * depth * 0.5 * float(W));
@@ -183,6 +177,14 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = 0.0f;
     }
     if constexpr (M3 != 0) {
+        // ---- colour -> SH (+ mean), once the tile has landed
+        const uint8_t cl = vis ? a.clamped[idx] : 0;
+        cp_async_wait<0>();
+        __syncthreads();
+        if (vis) {
+            const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
+            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
+        }
         __syncthreads();
         sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);
     }
