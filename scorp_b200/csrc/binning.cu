@@ -114,7 +114,18 @@ scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_str
         keys[ranges[t].x + slot] = k;
     };
     if (cnt > 0 && cnt <= SMALL_RECT) {
-        for (uint32_t i = 0; i < cnt; ++i) put((y0 + i / w) * gx + x0 + i % w, key);
+        // all cursor atomics first, then the dependent stores: one round trip instead of one per tile
+        uint32_t t[SMALL_RECT], at[SMALL_RECT];
+#pragma unroll
+        for (uint32_t i = 0; i < SMALL_RECT; ++i) {
+            if (i < cnt) {
+                t[i] = (y0 + i / w) * gx + x0 + i % w;
+                at[i] = __ldg(&ranges[t[i]].x) + atomicSub(tile_count + t[i], 1u) - 1u;
+            }
+        }
+#pragma unroll
+        for (uint32_t i = 0; i < SMALL_RECT; ++i)
+            if (i < cnt) keys[at[i]] = key;
     }
     uint32_t big = __ballot_sync(0xffffffffu, cnt > SMALL_RECT);
     while (big) {
