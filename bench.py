@@ -50,6 +50,8 @@ def parse():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", default="C2", choices=list(synth.CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--exchange", choices=["auto", "dense", "factored"], default="auto",
+                    help="N>1, ours: dense = one all_reduce over the gradient arena; factored = multiview.FactoredExchange")
     ap.add_argument("--views-per-rank", type=int, default=0, help="views each rank renders per step (0: the config's default)")
     return ap.parse_args()
 
@@ -269,9 +271,13 @@ class Ours:
         from scorp_b200 import multiview as mv
         return mv.accumulate_param_grads(total, g_means3D, P, M, self.surfel)
 
+    factored = False        # multiview.install_factored_exchange active: the backward returns reduced gradients
+
     def reduce(self, g, P, M):
         """g: dL_dmeans3D of one backward (a view of its arena) or an already accumulated head."""
         from scorp_b200 import multiview as mv
+        if self.factored:
+            return
         n = P * mv.param_grad_floats(M, self.surfel)
         head = g if (g.dim() == 1 and g.numel() == n) else mv.arena_of(g)[:n]
         mv.allreduce_param_grads(head)
@@ -379,6 +385,17 @@ def run(arm, args, rank, world, local):
             arm.reduce(total if total is not None else last[2], P, M)
         return last
 
+    exchange = "none"
+    if world > 1 and not fwd_only:
+        exchange = "one all_reduce over the parameter-gradient arena"
+        want = args.exchange == "factored" or (args.exchange == "auto" and mv.FactoredExchange.worth_it(world, M))
+        if arm.name == "ours" and vpr == 1 and M > 0 and want:
+            # one view per rank: gather 3 floats per Gaussian per rank and rebuild the SH gradient (multiview.FactoredExchange)
+            mv.install_factored_exchange()
+            arm.factored = True
+            exchange = "factored: all_gather of dL_dRGB (12 B x world per Gaussian) + all_reduce of the 11 non-SH floats"
+        elif arm.name == "reference":
+            exchange = "five all_reduce calls (one per gradient tensor)"
     n, radii, _ = step_resident()
     Pvis = int((radii > 0).sum())
     prime(step_resident, world)
@@ -394,7 +411,7 @@ def run(arm, args, rank, world, local):
         stages = list(st)
     ms_step = ms_total / args.steps
 
-    if arm.name == "ours" and world > 1:
+    if arm.name == "ours" and world > 1 and not arm.factored:
         mv.install_backward_allreduce()
     # ---- end to end: public API (ours: GaussianRasterizer + autograd), per-view host inputs from pinned memory
     params = [t.clone().requires_grad_(not fwd_only) for t in (sc.means3D, sc.shs, sc.opacities, sc.scales, sc.rotations)]
@@ -429,11 +446,12 @@ def run(arm, args, rank, world, local):
     ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
     launches = 0
     if arm.name == "ours":
-        launches = (4 if fwd_only else 7) * len(cams) * args.steps      # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd)
+        # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd) (+ clamped colour gradient, SH rebuild)
+        launches = ((4 if fwd_only else 7) + (2 if arm.factored else 0)) * len(cams) * args.steps
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
-                d2h=4, launches=launches)
+                d2h=4, launches=launches, exchange=exchange)
 
 
 def main():
@@ -469,7 +487,7 @@ def main():
         "config": {"workload": synth.CONFIGS[args.config]["desc"], "id": args.config, "mode": mode, "P": r["P"],
                    "sh_coeffs": r["M"], "width": W, "height": H, "visible": r["Pvis"], "num_rendered": r["N"],
                    "views_per_step": r["views"], "views_per_rank": r["vpr"],
-                   "parallelism": f"view-sharded dp{world}, one allreduce over the parameter-gradient arena" if world > 1 else "single GPU",
+                   "parallelism": f"view-sharded dp{world}; exchange: {r['exchange']}" if world > 1 else "single GPU",
                    "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"
                          if r["P"] * (44 + 12 * r["M"]) > 126e6 else "working set below the 126 MB L2: numbers are L2-warm, as in the reference's own loop"},
         "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "ms_per_step_spread": r["per_e2e"], "h2d_bytes_per_step": r["h2d"],

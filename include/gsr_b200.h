@@ -165,6 +165,21 @@ void gsr_surfel_image_layout(int W, int H, size_t off[4], size_t* total);
 size_t gsr_knn_workspace_bytes(int P);
 int gsr_knn_dist2(int P, const float* xyz, float* out, void* tmp, size_t tmp_bytes, void* stream);
 
+/* ---- view-sharded multi-GPU helpers (no reference counterpart; the reference is single-GPU) ----
+ * The SH gradient of ONE view is an outer product, dL_dsh[k] = b_k(dir) * dL_dRGB with dir = normalize(mean - campos)
+ * and dL_dRGB zeroed on the channels the forward clamped (diff-gaussian-rasterization/cuda_rasterizer/backward.cu:20-141).
+ * Ranks can therefore exchange 3 floats per Gaussian per view (all-gather) instead of all-reducing 3M floats, and
+ * rebuild the sum over views locally:
+ *   gsr_clamped_color_grad : drgb[P][3] = dL_dcolors with the forward's clamp bits applied (geom_buffer of that view's
+ *                            forward; surfel != 0 for a gsr_surfel_forward buffer)
+ *   gsr_sh_grad_from_views : dL_dsh[P][M][3] = sum over v < n_views, in order, of b(normalize(means3D - campos[v])) (x)
+ *                            drgb[v][P][3]
+ * gsr_rasterize_backward / gsr_surfel_backward accept dL_dsh == NULL with shs given and then skip the SH rows. */
+int gsr_clamped_color_grad(int P, int W, int H, int surfel, const void* geom_buffer, const float* dL_dcolors,
+                           float* drgb, void* stream);
+int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
+                           const float* drgb, float* dL_dsh, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -186,7 +186,6 @@ int gsr_rasterize_backward(
         !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dmeans3D || !dL_dcov3D || !dL_dscales || !dL_drotations || !workspace) {
         set_error("null required pointer in backward"); return GSR_EINVAL;
     }
-    if (shs && !dL_dsh) { set_error("dL_dsh is NULL but shs given"); return GSR_EINVAL; }
     if (workspace_bytes < gsr_backward_workspace_bytes(P)) { set_error("workspace too small"); return GSR_EINVAL; }
     const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, tiles = gx * gy;
     GeomState g; ImageState img; BinningState bin;

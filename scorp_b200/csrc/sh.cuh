@@ -74,6 +74,28 @@ __device__ __forceinline__ V3 ld3(const float* p) { return { __ldg(p), __ldg(p +
 __device__ __forceinline__ V3 ld3p(const float* p) { return { p[0], p[1], p[2] }; }      // generic (shared or global)
 __device__ __forceinline__ void st3(float* p, V3 v) { p[0] = v.x; p[1] = v.y; p[2] = v.z; }
 
+// Real SH basis b_k(dir) up to degree D (dir normalised); returns how many entries are set. dL/dsh[k] = b_k * dL/dRGB
+// (backward.cu:20-141), which is what makes the SH gradient of ONE view a rank-1 outer product.
+__device__ __forceinline__ int sh_basis(int D, float x, float y, float z, float (&basis)[16]) {
+    const float C1 = 0.4886025119029199f;
+    const float C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
+    const float C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                          -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
+    basis[0] = 0.28209479177387814f;
+    if (D < 1) return 1;
+    basis[1] = -C1 * y; basis[2] = C1 * z; basis[3] = -C1 * x;
+    if (D < 2) return 4;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    basis[4] = C2[0] * xy; basis[5] = C2[1] * yz; basis[6] = C2[2] * (2.f * zz - xx - yy);
+    basis[7] = C2[3] * xz; basis[8] = C2[4] * (xx - yy);
+    if (D < 3) return 9;
+    basis[9] = C3[0] * y * (3.f * xx - yy); basis[10] = C3[1] * xy * z;
+    basis[11] = C3[2] * y * (4.f * zz - xx - yy); basis[12] = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
+    basis[13] = C3[4] * x * (4.f * zz - xx - yy); basis[14] = C3[5] * z * (xx - yy);
+    basis[15] = C3[6] * x * (xx - 3.f * yy);
+    return 16;
+}
+
 // SH backward (backward.cu:20-139). Writes dL_dsh[0..M) (zeros beyond the active degree) and
 // returns the colour-induced part of dL_dmean.
 __device__ __forceinline__ V3 sh_backward(int D, int M, const float* sh, V3 pos, V3 campos,
@@ -87,26 +109,16 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* sh, V3 pos,
                           -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
     V3 gx = { 0, 0, 0 }, gy = { 0, 0, 0 }, gz = { 0, 0, 0 };   // dRGB/dx, /dy, /dz
     float basis[16];
-    basis[0] = 0.28209479177387814f;
-    int used = 1;
+    const int used = sh_basis(D, x, y, z, basis);
     if (D > 0) {
-        basis[1] = -C1 * y; basis[2] = C1 * z; basis[3] = -C1 * x;
         gx = -C1 * ld3p(sh + 9); gy = -C1 * ld3p(sh + 3); gz = C1 * ld3p(sh + 6);
-        used = 4;
         if (D > 1) {
             const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
-            basis[4] = C2[0] * xy; basis[5] = C2[1] * yz; basis[6] = C2[2] * (2.f * zz - xx - yy);
-            basis[7] = C2[3] * xz; basis[8] = C2[4] * (xx - yy);
             const V3 s4 = ld3p(sh + 12), s5 = ld3p(sh + 15), s6 = ld3p(sh + 18), s7 = ld3p(sh + 21), s8 = ld3p(sh + 24);
             gx = gx + (C2[0] * y) * s4 + (C2[2] * 2.f * -x) * s6 + (C2[3] * z) * s7 + (C2[4] * 2.f * x) * s8;
             gy = gy + (C2[0] * x) * s4 + (C2[1] * z) * s5 + (C2[2] * 2.f * -y) * s6 + (C2[4] * 2.f * -y) * s8;
             gz = gz + (C2[1] * y) * s5 + (C2[2] * 2.f * 2.f * z) * s6 + (C2[3] * x) * s7;
-            used = 9;
             if (D > 2) {
-                basis[9] = C3[0] * y * (3.f * xx - yy); basis[10] = C3[1] * xy * z;
-                basis[11] = C3[2] * y * (4.f * zz - xx - yy); basis[12] = C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy);
-                basis[13] = C3[4] * x * (4.f * zz - xx - yy); basis[14] = C3[5] * z * (xx - yy);
-                basis[15] = C3[6] * x * (xx - 3.f * yy);
                 const V3 s9 = ld3p(sh + 27), s10 = ld3p(sh + 30), s11 = ld3p(sh + 33), s12 = ld3p(sh + 36),
                          s13 = ld3p(sh + 39), s14 = ld3p(sh + 42), s15 = ld3p(sh + 45);
                 gx = gx + (C3[0] * 3.f * 2.f * xy) * s9 + (C3[1] * yz) * s10 + (C3[2] * -2.f * xy) * s11
@@ -117,7 +129,6 @@ __device__ __forceinline__ V3 sh_backward(int D, int M, const float* sh, V3 pos,
                         + (C3[6] * -3.f * 2.f * xy) * s15;
                 gz = gz + (C3[1] * xy) * s10 + (C3[2] * 4.f * 2.f * yz) * s11 + (C3[3] * 3.f * (2.f * zz - xx - yy)) * s12
                         + (C3[4] * 4.f * 2.f * xz) * s13 + (C3[5] * (xx - yy)) * s14;
-                used = 16;
             }
         }
     }

@@ -1,0 +1,81 @@
+// sh_exchange.cu -- view-sharded multi-GPU helper (no reference counterpart).
+//
+// The SH gradient a view produces for a Gaussian is an outer product: dL/dsh[k] = b_k(dir) * dL/dRGB, with
+// dir = normalize(mean - campos) and dL/dRGB zeroed on the channels the forward clamped (backward.cu:20-141).
+// Summing the SH gradients of n views across ranks therefore does not need the 3M floats per Gaussian per rank
+// an all-reduce moves: every rank all-GATHERS 3 floats per Gaussian per view (plus the camera positions) and
+// rebuilds the sum locally, in view order (deterministic, unlike a ring reduction):
+//   gsr_clamped_color_grad  : dL_dcolors + the forward's clamp bits -> the 3 floats to exchange
+//   gsr_sh_grad_from_views  : sum_v b(dir_v) (x) drgb_v -> dL_dsh[P][M][3]
+// With n views in flight the exchange per Gaussian is 12 n bytes instead of 192 (M = 16): worth it up to ~8-12
+// views per step; scorp_b200/multiview.py picks. The backward is then called with dL_dsh = NULL and does not
+// write the SH rows at all.
+#include "sh.cuh"
+#include "surfel.cuh"
+
+namespace gsr {
+
+__global__ void __launch_bounds__(256)
+clamped_color_grad_kernel(int P, const uint8_t* __restrict__ clamped, const float* __restrict__ dcol, float* __restrict__ drgb) {
+    const int i = blockIdx.x * 256 + threadIdx.x;        // one float per thread: unit-stride in and out
+    if (i >= 3 * P) return;
+    const int g = i / 3, c = i - 3 * g;
+    drgb[i] = ((clamped[g] >> c) & 1) ? 0.0f : dcol[i];
+}
+
+// One thread per (Gaussian, coefficient k): reads the n_views colour gradients of its Gaussian (L1-cached across
+// the M threads of a Gaussian), writes its three floats. Rows come out as contiguous 12-byte pieces, so a warp
+// writes 384 contiguous bytes.
+__global__ void __launch_bounds__(256)
+sh_grad_from_views_kernel(int P, int M, int D, int n_views, const float* __restrict__ means3D,
+                          const float* __restrict__ campos, const float* __restrict__ drgb, float* __restrict__ dsh) {
+    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (t >= (size_t)P * M) return;
+    const int g = (int)(t / M), k = (int)(t - (size_t)g * M);
+    const V3 m = ld3(means3D + 3 * (size_t)g);
+    V3 acc = { 0.f, 0.f, 0.f };
+    for (int v = 0; v < n_views; ++v) {
+        const V3 d = ld3(drgb + ((size_t)v * P + g) * 3);
+        if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) continue;      // not visible in view v (or fully clamped)
+        const V3 dir = { m.x - __ldg(campos + 3 * v), m.y - __ldg(campos + 3 * v + 1), m.z - __ldg(campos + 3 * v + 2) };
+        const float inv_len = 1.0f / sqrtf(dot(dir, dir));
+        float basis[16];
+        const int used = sh_basis(D, dir.x * inv_len, dir.y * inv_len, dir.z * inv_len, basis);
+        float bk = 0.0f;
+#pragma unroll
+        for (int q = 0; q < 16; ++q) if (q == k && q < used) bk = basis[q];
+        acc = acc + bk * d;
+    }
+    st3(dsh + 3 * t, acc);
+}
+
+}  // namespace gsr
+
+using namespace gsr;
+
+extern "C" int gsr_clamped_color_grad(int P, int W, int H, int surfel, const void* geom_buffer, const float* dL_dcolors,
+                                      float* drgb, void* stream) {
+    if (P < 0 || W <= 0 || H <= 0) { set_error("bad sizes"); return GSR_EINVAL; }
+    if (P == 0) return GSR_OK;
+    if (!geom_buffer || !dL_dcolors || !drgb) { set_error("null pointer in gsr_clamped_color_grad"); return GSR_EINVAL; }
+    const int tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+    const uint8_t* clamped;
+    if (surfel) { SurfelGeom g; carve_surfel_geom((char*)geom_buffer, P, tiles, &g); clamped = g.clamped; }
+    else { GeomState g; carve_geom((char*)geom_buffer, P, tiles, &g); clamped = g.clamped; }
+    cudaStream_t st = (cudaStream_t)stream;
+    clamped_color_grad_kernel<<<(3 * P + 255) / 256, 256, 0, st>>>(P, clamped, dL_dcolors, drgb);
+    return check_cuda(cudaGetLastError(), "clamped colour gradient launch");
+}
+
+extern "C" int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
+                                      const float* drgb, float* dL_dsh, void* stream) {
+    if (P < 0 || M < 1 || M > 16 || D < 0 || D > 3 || (D + 1) * (D + 1) > M || n_views < 1) {
+        set_error("bad sizes in gsr_sh_grad_from_views"); return GSR_EINVAL;
+    }
+    if (P == 0) return GSR_OK;
+    if (!means3D || !campos || !drgb || !dL_dsh) { set_error("null pointer in gsr_sh_grad_from_views"); return GSR_EINVAL; }
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t n = (size_t)P * M;
+    sh_grad_from_views_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, M, D, n_views, means3D, campos, drgb, dL_dsh);
+    return check_cuda(cudaGetLastError(), "SH gradient from views launch");
+}

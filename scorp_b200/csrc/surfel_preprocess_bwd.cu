@@ -186,7 +186,7 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
         __syncthreads();
-        sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);
+        if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
     if (!valid) return;
 

@@ -17,6 +17,7 @@ from .._lib import GsrSettings, ptr
 
 
 _backward_hook = [None]      # optional callable(head): runs on the parameter-gradient head of every backward
+_factored = [None]           # multiview.install_factored_exchange
 
 
 def _f32c(t: torch.Tensor, device) -> torch.Tensor:
@@ -125,12 +126,23 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     # One arena for all gradients (fully written by the library: no zero fill needed). The five
     # parameter gradients come first and are contiguous, so a view-sharded trainer can sum them
     # across ranks with ONE allreduce over arena[:P * PARAM_GRAD_FLOATS(M)].
-    widths = (3, 3 * M, 1, 3, 4, 3, 3, 6)      # means3D, sh, opacity, scales, rotations | means2D, colors, cov3D
+    # With multiview.install_factored_exchange the SH gradient is NOT produced by the backward (dL_dsh = NULL): the
+    # arena head is [means3D, opacity, scales, rotations] (all-reduced), followed by the clamped colour gradient that
+    # is all-gathered, and dL_dsh is rebuilt from all ranks' colour gradients (csrc/sh_exchange.cu).
+    fx = _factored[0] if (M > 0 and P != 0) else None
+    if fx is not None:
+        widths = (3, 1, 3, 4, 3, 3, 3, 6)       # means3D, opacity, scales, rotations | drgb | means2D, colors, cov3D
+    else:
+        widths = (3, 3 * M, 1, 3, 4, 3, 3, 6)   # means3D, sh, opacity, scales, rotations | means2D, colors, cov3D
     flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
     outs, o = [], 0
     for w in widths:
         outs.append(flat[o:o + P * w]); o += P * w
-    g_m3d, g_sh, g_op, g_sc, g_rot, g_m2d, g_col, g_cov = outs
+    if fx is not None:
+        g_m3d, g_op, g_sc, g_rot, g_drgb, g_m2d, g_col, g_cov = outs
+        g_sh = torch.empty((P * M * 3,), dtype=torch.float32, device=dev)
+    else:
+        g_m3d, g_sh, g_op, g_sc, g_rot, g_m2d, g_col, g_cov = outs
     if P != 0:
         ws_bytes = lib.gsr_backward_workspace_bytes(P)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -141,10 +153,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),
                 ptr(cov3D_precomp), ptr(radii), ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer),
                 ptr(alpha), ptr(dL_dout_color), ptr(dL_dout_depth), ptr(dL_dout_alpha),
-                ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_cov), ptr(g_sh), ptr(g_sc), ptr(g_rot),
-                ws.data_ptr(), ws_bytes, _stream(dev))
-        _lib.check(rc, "gsr_rasterize_backward")
-        if _backward_hook[0] is not None:       # e.g. multiview.install_backward_allreduce: reduce before autograd copies
+                ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_cov), None if fx is not None else ptr(g_sh),
+                ptr(g_sc), ptr(g_rot), ws.data_ptr(), ws_bytes, _stream(dev))
+            _lib.check(rc, "gsr_rasterize_backward")
+            if fx is not None:
+                rc = lib.gsr_clamped_color_grad(P, W, H, 0, ptr(geomBuffer), ptr(g_col), ptr(g_drgb), _stream(dev))
+                _lib.check(rc, "gsr_clamped_color_grad")
+        if fx is not None:
+            fx(flat[: P * 11], g_drgb, campos, means3D, g_sh, P, M, int(degree))
+        elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),
             g_sh.view(P, M, 3), g_sc.view(P, 3), g_rot.view(P, 4))

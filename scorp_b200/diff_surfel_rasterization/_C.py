@@ -15,6 +15,7 @@ from ..diff_gaussian_rasterization._C import _Arena, _f32c, _settings, _stream, 
 
 NUM_OTHERS = 7
 _backward_hook = [None]      # optional callable(head): runs on the parameter-gradient head of every backward
+_factored = [None]           # multiview.install_factored_exchange
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
@@ -68,13 +69,23 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     background = _f32c(background, dev); viewmatrix = _f32c(viewmatrix, dev)
     projmatrix = _f32c(projmatrix, dev); campos = _f32c(campos, dev)
     dL_dout_color = _f32c(dL_dout_color, dev); dL_dout_others = _f32c(dL_dout_others, dev)
-    # parameter gradients first and contiguous (one allreduce), then the rest
-    widths = (3, 3 * M, 1, 2, 4, 3, 3, 9)      # means3D, sh, opacity, scales, rotations | means2D, colors, transMat
+    # parameter gradients first and contiguous (one allreduce), then the rest; with
+    # multiview.install_factored_exchange the SH rows are rebuilt from all ranks' colour gradients instead
+    # (see diff_gaussian_rasterization/_C.py and csrc/sh_exchange.cu)
+    fx = _factored[0] if (M > 0 and P != 0) else None
+    if fx is not None:
+        widths = (3, 1, 2, 4, 3, 3, 3, 9)       # means3D, opacity, scales, rotations | drgb | means2D, colors, transMat
+    else:
+        widths = (3, 3 * M, 1, 2, 4, 3, 3, 9)   # means3D, sh, opacity, scales, rotations | means2D, colors, transMat
     flat = torch.empty((P * sum(widths),), dtype=torch.float32, device=dev)
     outs, o = [], 0
     for w in widths:
         outs.append(flat[o:o + P * w]); o += P * w
-    g_m3d, g_sh, g_op, g_sc, g_rot, g_m2d, g_col, g_tm = outs
+    if fx is not None:
+        g_m3d, g_op, g_sc, g_rot, g_drgb, g_m2d, g_col, g_tm = outs
+        g_sh = torch.empty((P * M * 3,), dtype=torch.float32, device=dev)
+    else:
+        g_m3d, g_sh, g_op, g_sc, g_rot, g_m2d, g_col, g_tm = outs
     if P != 0:
         ws_bytes = lib.gsr_surfel_backward_workspace_bytes(P)
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
@@ -85,10 +96,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),
                 ptr(transMat_precomp), ptr(radii), ptr(geomBuffer), ptr(binningBuffer), ptr(imageBuffer),
                 ptr(dL_dout_color), ptr(dL_dout_others),
-                ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_tm), ptr(g_sh), ptr(g_sc), ptr(g_rot),
-                ws.data_ptr(), ws_bytes, _stream(dev))
-        _lib.check(rc, "gsr_surfel_backward")
-        if _backward_hook[0] is not None:       # e.g. multiview.install_backward_allreduce: reduce before autograd copies
+                ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_tm), None if fx is not None else ptr(g_sh),
+                ptr(g_sc), ptr(g_rot), ws.data_ptr(), ws_bytes, _stream(dev))
+            _lib.check(rc, "gsr_surfel_backward")
+            if fx is not None:
+                rc = lib.gsr_clamped_color_grad(P, W, H, 1, ptr(geomBuffer), ptr(g_col), ptr(g_drgb), _stream(dev))
+                _lib.check(rc, "gsr_clamped_color_grad")
+        if fx is not None:
+            fx(flat[: P * 10], g_drgb, campos, means3D, g_sh, P, M, int(degree))
+        elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_tm.view(P, 9),
             g_sh.view(P, M, 3), g_sc.view(P, 2), g_rot.view(P, 4))

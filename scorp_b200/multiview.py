@@ -94,6 +94,77 @@ def install_backward_allreduce(group=None, enable: bool = True) -> None:
     c2._backward_hook[0] = hook
 
 
+class FactoredExchange:
+    """Exchange of one backward per rank (ONE view per rank per step) that moves 3 floats per Gaussian for the SH
+    part instead of 3*M: the SH gradient of a view is the outer product basis(dir) (x) dL_dRGB
+    (csrc/sh_exchange.cu, include/gsr_b200.h), so ranks all-gather dL_dRGB (and the camera positions) and every
+    rank rebuilds sum_v basis(dir_v) (x) dL_dRGB_v itself, in rank order. The other parameter gradients
+    (means3D, opacity, scales, rotations: 11 or 10 floats) are all-reduced as before; that collective runs
+    underneath the rebuild kernel. Per Gaussian on the wire: 44 B all-reduced + 12 B x world gathered, against
+    236 B all-reduced (M = 16); `worth_it` says when this wins.
+
+    `rebuild(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out)` defaults to the CUDA entry point
+    gsr_sh_grad_from_views; the CPU (gloo) tests of the host logic pass their own."""
+
+    def __init__(self, group=None, rebuild=None):
+        self.group, self.rebuild = group, rebuild
+        self._bufs = {}
+
+    @staticmethod
+    def worth_it(world: int, M: int) -> bool:
+        """bytes received per Gaussian: gather 12*world (+ 44 reduced) vs ~2 * 4*(11+3M) for a ring all-reduce"""
+        return M > 0 and 12 * world + 2 * 44 < 2 * 4 * (11 + 3 * M)
+
+    def _buffers(self, world, P, dev):
+        key = (world, P, str(dev))
+        if key not in self._bufs:
+            self._bufs = {key: (torch.empty((world, P, 3), dtype=torch.float32, device=dev),
+                                torch.empty((world, 3), dtype=torch.float32, device=dev))}
+        return self._bufs[key]
+
+    def __call__(self, head: torch.Tensor, drgb: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor,
+                 dsh_out: torch.Tensor, P: int, M: int, D: int) -> None:
+        """head: the contiguous non-SH parameter gradients (summed in place); drgb[P,3]: this rank's clamped colour
+        gradient; dsh_out[P,M,3]: receives the SH gradient summed over ranks."""
+        world = dist.get_world_size(self.group) if (dist.is_available() and dist.is_initialized()) else 1
+        drgb_all, campos_all = self._buffers(world, P, drgb.device)
+        if world > 1:
+            w_g = dist.all_gather_into_tensor(drgb_all.view(-1), drgb.reshape(-1), group=self.group, async_op=True)
+            w_c = dist.all_gather_into_tensor(campos_all.view(-1), campos.reshape(-1).contiguous(), group=self.group, async_op=True)
+            w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+            w_g.wait(); w_c.wait()
+        else:
+            drgb_all[0].copy_(drgb.view(P, 3)); campos_all[0].copy_(campos.reshape(3))
+            w_r = None
+        (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
+        if w_r is not None:
+            w_r.wait()
+
+
+def _rebuild_cuda(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
+    from . import _lib
+    if not dsh_out.is_cuda:
+        raise _lib.GsrError("gsr_sh_grad_from_views needs CUDA tensors: there is no CPU path")
+    lib = _lib.lib()
+    with torch.cuda.device(dsh_out.device):
+        rc = lib.gsr_sh_grad_from_views(P, M, D, n_views, means3D.data_ptr(), campos_all.data_ptr(), drgb_all.data_ptr(),
+                                        dsh_out.data_ptr(), torch.cuda.current_stream(dsh_out.device).cuda_stream)
+    _lib.check(rc, "gsr_sh_grad_from_views")
+
+
+def install_factored_exchange(group=None, enable: bool = True, rebuild=None) -> None:
+    """One view per rank per step: every backward of both rasterizer packages (autograd or `_C` level) returns
+    gradients already summed over ranks, exchanged with FactoredExchange. Replaces install_backward_allreduce."""
+    from .diff_gaussian_rasterization import _C as c3
+    from .diff_surfel_rasterization import _C as c2
+    fx = FactoredExchange(group, rebuild) if enable else None
+    c3._factored[0] = fx
+    c2._factored[0] = fx
+    if enable:
+        c3._backward_hook[0] = None
+        c2._backward_hook[0] = None
+
+
 def render_views_sharded(render_one, view_ids: Sequence[int], P: int, M: int, surfel: bool = False, group=None):
     """Runs `render_one(view_id) -> grad_means3D` (one forward+backward of this library, returning the
     means3D gradient, which identifies the arena) for this rank's views, sums locally, reduces once.

@@ -189,3 +189,36 @@ def ref_surfel_backward(scene, cam, fwd, grads):
     return ref_cuda.dsr_backward(fwd, scene.bg, scene.means3D, col, sc, rot, smod, tm, cam.viewmatrix,
                                  cam.projmatrix, cam.tanfovx, cam.tanfovy, grads[0], grads[1], shs,
                                  scene.sh_degree, cam.campos)
+
+
+def sh_basis_torch(D, dirs):
+    """Real SH basis b_k(dir) for unit directions dirs[N,3] -> [N,(D+1)^2] (same constants as
+    diff-gaussian-rasterization/cuda_rasterizer/auxiliary.h:20-36); test-side restatement used to check the
+    factored multi-GPU exchange (scorp_b200/multiview.py:FactoredExchange)."""
+    x, y, z = dirs[:, 0], dirs[:, 1], dirs[:, 2]
+    C1 = 0.4886025119029199
+    C2 = (1.0925484305920792, -1.0925484305920792, 0.31539156525252005, -1.0925484305920792, 0.5462742152960396)
+    C3 = (-0.5900435899266435, 2.890611442640554, -0.4570457994644658, 0.3731763325901154, -0.4570457994644658,
+          1.445305721320277, -0.5900435899266435)
+    b = [torch.full_like(x, 0.28209479177387814)]
+    if D > 0:
+        b += [-C1 * y, C1 * z, -C1 * x]
+    if D > 1:
+        xx, yy, zz, xy, yz, xz = x * x, y * y, z * z, x * y, y * z, x * z
+        b += [C2[0] * xy, C2[1] * yz, C2[2] * (2 * zz - xx - yy), C2[3] * xz, C2[4] * (xx - yy)]
+    if D > 2:
+        b += [C3[0] * y * (3 * xx - yy), C3[1] * xy * z, C3[2] * y * (4 * zz - xx - yy),
+              C3[3] * z * (2 * zz - 3 * xx - 3 * yy), C3[4] * x * (4 * zz - xx - yy), C3[5] * z * (xx - yy),
+              C3[6] * x * (xx - 3 * yy)]
+    return torch.stack(b, dim=1)
+
+
+def sh_grad_from_views_torch(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
+    """sum_v basis(normalize(mean - campos_v)) (x) drgb_v, written into dsh_out[P*M*3] (float64 accumulation)."""
+    acc = torch.zeros((P, M, 3), dtype=torch.float64, device=means3D.device)
+    for v in range(n_views):
+        d = means3D.double() - campos_all[v].double()
+        d = d / d.norm(dim=1, keepdim=True)
+        b = sh_basis_torch(D, d)                                   # [P, used]
+        acc[:, : b.shape[1], :] += b[:, :, None] * drgb_all[v].double().view(P, 1, 3)
+    dsh_out.view(P, M, 3).copy_(acc.to(dsh_out.dtype))

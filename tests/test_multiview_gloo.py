@@ -65,6 +65,55 @@ def test_view_sharded_allreduce_gloo(world, n_views, surfel):
     assert seen == list(range(n_views))
 
 
+def _factored_worker(rank, world, port, P, M, D, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"; os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import helpers as h
+        g = torch.Generator().manual_seed(5)
+        means = torch.randn(P, 3, generator=g)                                       # replicated parameters
+        per_rank = []
+        for r in range(world):                                                       # every rank can build all inputs
+            gr = torch.Generator().manual_seed(50 + r)
+            head = torch.randn(P * 11, generator=gr)
+            drgb = torch.randn(P, 3, generator=gr); drgb[torch.rand(P, generator=gr) < 0.3] = 0.0
+            campos = torch.randn(3, generator=gr) * 5
+            per_rank.append((head, drgb, campos))
+        head, drgb, campos = (t.clone() for t in per_rank[rank])
+        dsh = torch.empty(P * M * 3)
+        fx = mv.FactoredExchange(rebuild=h.sh_grad_from_views_torch)                  # CUDA rebuild replaced for the CPU test
+        fx(head, drgb, campos, means, dsh, P, M, D)
+        want_head = sum(t[0].double() for t in per_rank)
+        want_dsh = torch.empty(P * M * 3)
+        h.sh_grad_from_views_torch(P, M, D, world, means, torch.stack([t[2] for t in per_rank]),
+                                   torch.stack([t[1] for t in per_rank]), want_dsh)
+        ok = torch.allclose(head.double(), want_head, rtol=1e-5, atol=1e-5) and torch.equal(dsh, want_dsh)
+        # and it is the sum of the per-rank outer products an all-reduce of dL_dsh would have produced
+        mine = torch.empty(P * M * 3)
+        h.sh_grad_from_views_torch(P, M, D, 1, means, campos.view(1, 3), drgb.view(1, P, 3), mine)
+        dist.all_reduce(mine)
+        ok = ok and torch.allclose(mine, dsh, rtol=1e-4, atol=1e-5)
+        q.put((rank, bool(ok)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_factored_exchange_gloo(world):
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_factored_worker, args=(r, world, port, 301, 16, 3, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(ok for _, ok in res)
+    assert mv.FactoredExchange.worth_it(8, 16) and not mv.FactoredExchange.worth_it(32, 16) and not mv.FactoredExchange.worth_it(2, 0)
+
+
 def test_views_for_rank_partition():
     for world in (1, 2, 4, 8):
         for n in (1, 8, 13, 128):
