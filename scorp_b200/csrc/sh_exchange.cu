@@ -23,30 +23,46 @@ clamped_color_grad_kernel(int P, const uint8_t* __restrict__ clamped, const floa
     drgb[i] = ((clamped[g] >> c) & 1) ? 0.0f : dcol[i];
 }
 
-// One thread per (Gaussian, coefficient k): reads the n_views colour gradients of its Gaussian (L1-cached across
-// the M threads of a Gaussian), writes its three floats. Rows come out as contiguous 12-byte pieces, so a warp
-// writes 384 contiguous bytes.
-__global__ void __launch_bounds__(256)
-sh_grad_from_views_kernel(int P, int M, int D, int n_views, const float* __restrict__ means3D,
+// One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
+// sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
+template <int M3>
+__global__ void __launch_bounds__(SH_TILE)
+sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ means3D,
                           const float* __restrict__ campos, const float* __restrict__ drgb, float* __restrict__ dsh) {
-    const size_t t = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (t >= (size_t)P * M) return;
-    const int g = (int)(t / M), k = (int)(t - (size_t)g * M);
-    const V3 m = ld3(means3D + 3 * (size_t)g);
-    V3 acc = { 0.f, 0.f, 0.f };
-    for (int v = 0; v < n_views; ++v) {
-        const V3 d = ld3(drgb + ((size_t)v * P + g) * 3);
-        if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) continue;      // not visible in view v (or fully clamped)
-        const V3 dir = { m.x - __ldg(campos + 3 * v), m.y - __ldg(campos + 3 * v + 1), m.z - __ldg(campos + 3 * v + 2) };
-        const float inv_len = 1.0f / sqrtf(dot(dir, dir));
-        float basis[16];
-        const int used = sh_basis(D, dir.x * inv_len, dir.y * inv_len, dir.z * inv_len, basis);
-        float bk = 0.0f;
+    constexpr int M = M3 / 3;
+    __shared__ float s_sh[SH_TILE * ShTile<M3>::STRIDE];
+    __shared__ uint8_t s_all[SH_TILE];
+    const size_t row0 = (size_t)blockIdx.x * SH_TILE;
+    const int nrows = min(SH_TILE, P - (int)row0);
+    const int g = (int)row0 + threadIdx.x;
+    float acc[M3];
 #pragma unroll
-        for (int q = 0; q < 16; ++q) if (q == k && q < used) bk = basis[q];
-        acc = acc + bk * d;
+    for (int i = 0; i < M3; ++i) acc[i] = 0.0f;
+    if (g < P) {
+        const V3 m = ld3(means3D + 3 * (size_t)g);
+        for (int v = 0; v < n_views; ++v) {
+            const V3 d = ld3(drgb + ((size_t)v * P + g) * 3);
+            if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) continue;      // not visible in view v (or fully clamped)
+            const V3 dir = { m.x - __ldg(campos + 3 * v), m.y - __ldg(campos + 3 * v + 1), m.z - __ldg(campos + 3 * v + 2) };
+            const float inv_len = 1.0f / sqrtf(dot(dir, dir));
+            float basis[16];
+            const int used = sh_basis(D, dir.x * inv_len, dir.y * inv_len, dir.z * inv_len, basis);
+#pragma unroll
+            for (int k = 0; k < M; ++k) {
+                if (k < used) {
+                    acc[3 * k] = fmaf(basis[k], d.x, acc[3 * k]);
+                    acc[3 * k + 1] = fmaf(basis[k], d.y, acc[3 * k + 1]);
+                    acc[3 * k + 2] = fmaf(basis[k], d.z, acc[3 * k + 2]);
+                }
+            }
+        }
     }
-    st3(dsh + 3 * t, acc);
+    s_all[threadIdx.x] = 1;
+    float* mine = s_sh + threadIdx.x * ShTile<M3>::STRIDE;
+#pragma unroll
+    for (int i = 0; i < M3; ++i) mine[i] = acc[i];
+    __syncthreads();
+    sh_tile_store<M3>(dsh, row0, nrows, s_all, s_sh);
 }
 
 }  // namespace gsr
@@ -75,7 +91,13 @@ extern "C" int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const fl
     if (P == 0) return GSR_OK;
     if (!means3D || !campos || !drgb || !dL_dsh) { set_error("null pointer in gsr_sh_grad_from_views"); return GSR_EINVAL; }
     cudaStream_t st = (cudaStream_t)stream;
-    const size_t n = (size_t)P * M;
-    sh_grad_from_views_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(P, M, D, n_views, means3D, campos, drgb, dL_dsh);
+    const int blocks = (P + SH_TILE - 1) / SH_TILE;
+    switch (3 * M) {
+    case 3:  sh_grad_from_views_kernel<3><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
+    case 12: sh_grad_from_views_kernel<12><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
+    case 27: sh_grad_from_views_kernel<27><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
+    case 48: sh_grad_from_views_kernel<48><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
+    default: set_error("gsr_sh_grad_from_views: M must be 1, 4, 9 or 16"); return GSR_EINVAL;
+    }
     return check_cuda(cudaGetLastError(), "SH gradient from views launch");
 }
