@@ -437,7 +437,7 @@ def run(arm, args, rank, world, local):
                 main.wait_stream(copy_stream)
                 return d_gr_buf
             color = arm.e2e_step(sc, cam, params, d_cam, d_gr, fwd_only, world)
-            s = color.sum().view(1)
+            s = color.detach().sum().view(1)      # the scalar that goes to the host (loss.item()); no graph hangs off it
             acc = s if acc is None else acc + s
         h_out.copy_(acc, non_blocking=True)
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)

@@ -32,22 +32,32 @@ def _f32c(t: torch.Tensor, device) -> torch.Tensor:
 
 
 class _Arena:
-    """Allocator handed to the library: one uint8 tensor per scratch buffer."""
+    """Allocator handed to the library: one uint8 tensor per scratch buffer.
+
+    The callback is a closure over the buffer dict, NOT a bound method: `self.fn = ALLOC_FN(self._alloc)` would make
+    the object reference itself, and the three scratch tensors (140 MB at 1 M Gaussians) would then stay allocated
+    until the cyclic garbage collector runs instead of being released with the autograd graph."""
 
     def __init__(self, device):
         self.device = device
         self.bufs = {}
-        self.error = None
-        self.fn = _lib.ALLOC_FN(self._alloc)
+        self._errors = []
+        bufs, errors = self.bufs, self._errors
 
-    def _alloc(self, _user, which, nbytes):
-        try:
-            t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=self.device)
-            self.bufs[which] = t
-            return t.data_ptr()
-        except Exception as ex:  # never let an exception cross the C ABI
-            self.error = ex
-            return None
+        def _alloc(_user, which, nbytes):
+            try:
+                t = torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+                bufs[which] = t
+                return t.data_ptr()
+            except Exception as ex:  # never let an exception cross the C ABI
+                errors.append(ex)
+                return None
+
+        self.fn = _lib.ALLOC_FN(_alloc)
+
+    @property
+    def error(self):
+        return self._errors[0] if self._errors else None
 
     def get(self, which):
         t = self.bufs.get(which)

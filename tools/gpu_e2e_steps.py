@@ -29,7 +29,7 @@ def step(h2d=True, slices=True, readback=True):
     color, radii, depth, alpha = dgr.GaussianRasterizer(rs)(means3D=params[0], means2D=torch.zeros_like(params[0], requires_grad=True), shs=params[1], opacities=params[2], scales=params[3], rotations=params[4])
     torch.autograd.backward([color, depth, alpha], gr)
     if readback:
-        h_out.copy_(color.sum().view(1), non_blocking=True)
+        h_out.copy_(color.detach().sum().view(1), non_blocking=True)
         torch.cuda.current_stream().synchronize()
 
 for name, kw in [("full", {}), ("no readback/sync", dict(readback=False)), ("no h2d", dict(h2d=False)), ("h2d no slices", dict(slices=False)), ("full again", {})]:
@@ -37,3 +37,19 @@ for name, kw in [("full", {}), ("no readback/sync", dict(readback=False)), ("no 
     for i in range(25):
         torch.cuda.synchronize(); t0 = time.perf_counter(); step(**kw); torch.cuda.synchronize(); ts.append((time.perf_counter() - t0) * 1e3)
     print(f"{name:20s}", " ".join(f"{x:.2f}" for x in ts))
+
+import gc, statistics
+for label, off in (("gc on", False), ("gc off", True), ("gc on again", False)):
+    if off:
+        gc.collect(); gc.disable()
+    ts = []
+    for i in range(400):
+        torch.cuda.synchronize(); t0 = time.perf_counter(); step(); torch.cuda.synchronize(); ts.append((time.perf_counter() - t0) * 1e3)
+        if torch.cuda.memory_allocated() > 20e9:
+            print("memory keeps growing:", torch.cuda.memory_allocated() / 1e9, "GB after", i, "steps"); break
+    if off:
+        gc.enable()
+    med = statistics.median(ts)
+    spikes = [(i, round(x, 2)) for i, x in enumerate(ts) if x > 1.5 * med]
+    print(f"allocated {torch.cuda.memory_allocated() / 1e9:.2f} GB")
+    print(f"{label:12s} median {med:.3f} mean {sum(ts)/len(ts):.3f} max {max(ts):.2f} spikes {len(spikes)}: {spikes[:12]}")
