@@ -177,6 +177,11 @@ int gsr_knn_dist2(int P, const float* xyz, float* out, void* tmp, size_t tmp_byt
  * gsr_rasterize_backward / gsr_surfel_backward accept dL_dsh == NULL with shs given and then skip the SH rows. */
 int gsr_clamped_color_grad(int P, int W, int H, int surfel, const void* geom_buffer, const float* dL_dcolors,
                            float* drgb, void* stream);
+/* Arms the NEXT gsr_rasterize_backward / gsr_surfel_backward call made by this thread: right after its blend kernel
+ * (i.e. before the preprocess-backward kernel is enqueued) it writes the clamped colour gradient to drgb[P][3] and
+ * calls ready(user) on the host, so the caller can start the all-gather of drgb underneath the rest of the backward.
+ * drgb == NULL disarms. Only takes effect when the backward is given SH coefficients. */
+int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
                            const float* drgb, float* dL_dsh, void* stream);
 

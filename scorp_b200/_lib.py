@@ -14,6 +14,7 @@ LIB_PATH = HERE / "libgsr_b200.so"
 
 c_void_p, c_int, c_size_t, c_float = C.c_void_p, C.c_int, C.c_size_t, C.c_float
 
+READY_FN = C.CFUNCTYPE(None, C.c_void_p)          # gsr_backward_early_rgb callback
 ALLOC_FN = C.CFUNCTYPE(c_void_p, c_void_p, c_int, c_size_t)
 
 GSR_BUF_GEOM, GSR_BUF_BINNING, GSR_BUF_IMAGE = 0, 1, 2
@@ -55,6 +56,7 @@ SIGNATURES = {
     "gsr_knn_workspace_bytes": (c_size_t, [c_int]),
     "gsr_knn_dist2": (c_int, [c_int, _P, _P, _P, c_size_t, _P]),
     "gsr_clamped_color_grad": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
+    "gsr_backward_early_rgb": (c_int, [_P, _P, _P]),
     "gsr_sh_grad_from_views": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
 }
 

@@ -47,6 +47,9 @@ void prof_mark(int i, cudaStream_t st) {
 
 static bool sh_count_ok(int M) { return M == 0 || M == 1 || M == 4 || M == 9 || M == 16; }
 
+thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false };
+EarlyRgb take_early_rgb() { const EarlyRgb e = g_early; g_early.armed = false; return e; }
+
 }  // namespace gsr
 
 using namespace gsr;
@@ -203,6 +206,14 @@ int gsr_rasterize_backward(
         if ((rc = stage_check(s, st, "render backward"))) return rc;
     }
     prof_mark(5, st);
+    {   // multi-GPU: the colour gradient is final here; hand it out so its all-gather overlaps the next kernel
+        const EarlyRgb e = take_early_rgb();
+        if (e.armed && shs) {
+            if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.drgb, st),
+                                 "early colour gradient launch"))) return rc;
+            if (e.ready) e.ready(e.user);
+        }
+    }
     BwdArgs b;
     b.P = P; b.M = shs ? M : 0; b.D = s->sh_degree; b.W = W; b.H = H;
     b.tanfovx = s->tanfovx; b.tanfovy = s->tanfovy;
@@ -218,6 +229,12 @@ int gsr_rasterize_backward(
     if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");
+}
+
+int gsr_backward_early_rgb(float* drgb, void (*ready)(void*), void* user) {
+    if (!drgb) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false}; return GSR_OK; }
+    gsr::g_early = gsr::EarlyRgb{drgb, ready, user, true};
+    return GSR_OK;
 }
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -97,6 +97,12 @@ inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nu
     return o;
 }
 
+// gsr_backward_early_rgb (api.cu): armed per thread for the next backward call
+struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; };
+EarlyRgb take_early_rgb();          // returns the armed request (armed == false if none) and disarms it
+cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
+                                        int rgb_off, float* drgb, cudaStream_t st);
+
 // error plumbing (api.cu)
 void set_error(const char* fmt, ...);
 int  check_cuda(cudaError_t e, const char* what);

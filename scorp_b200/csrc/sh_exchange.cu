@@ -23,6 +23,24 @@ clamped_color_grad_kernel(int P, const uint8_t* __restrict__ clamped, const floa
     drgb[i] = ((clamped[g] >> c) & 1) ? 0.0f : dcol[i];
 }
 
+// the same three floats, straight from the blend backward's accumulator slots (available BEFORE the
+// preprocess-backward kernel runs, so the all-gather can start underneath it; gsr_backward_early_rgb)
+__global__ void __launch_bounds__(256)
+clamped_rgb_from_acc_kernel(int P, const int32_t* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                            const float* __restrict__ acc, int stride, int rgb_off, float* __restrict__ drgb) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= 3 * P) return;
+    const int g = i / 3, c = i - 3 * g;
+    float v = 0.0f;
+    if (radii[g] > 0 && !((clamped[g] >> c) & 1)) v = acc[(size_t)g * stride + rgb_off + c];
+    drgb[i] = v;
+}
+cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
+                                        int rgb_off, float* drgb, cudaStream_t st) {
+    if (P > 0) clamped_rgb_from_acc_kernel<<<(3 * P + 255) / 256, 256, 0, st>>>(P, radii, clamped, acc, stride, rgb_off, drgb);
+    return cudaGetLastError();
+}
+
 // One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
 // sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
 template <int M3>

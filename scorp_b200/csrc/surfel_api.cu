@@ -125,6 +125,14 @@ int gsr_surfel_backward(
         if ((rc = stage_check(s, st, "surfel render backward"))) return rc;
     }
     prof_mark(5, st);
+    {   // multi-GPU: see gsr_rasterize_backward
+        const EarlyRgb e = take_early_rgb();
+        if (e.armed && shs) {
+            if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.drgb, st),
+                                 "early colour gradient launch"))) return rc;
+            if (e.ready) e.ready(e.user);
+        }
+    }
     SurfelBwdArgs b;
     b.P = P; b.M = shs ? M : 0; b.D = s->sh_degree; b.W = W; b.H = H;
     b.tanfovx = s->tanfovx; b.tanfovy = s->tanfovy;

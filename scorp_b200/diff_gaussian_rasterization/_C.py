@@ -64,6 +64,24 @@ class _Arena:
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
 
 
+def _arm_early(lib, fx, g_drgb, campos, P):
+    """Factored multi-GPU exchange: ask the next backward call to hand out the clamped colour gradient right after
+    its blend kernel and start gathering it there (gsr_backward_early_rgb). Returns (callback to keep alive until the
+    backward returned, list that receives an exception raised inside it); no reference cycle: the closure does not
+    see the callback object."""
+    errors = []
+
+    def _ready(_user):
+        try:
+            fx.begin(g_drgb, campos, P)
+        except Exception as ex:      # never let an exception cross the C ABI
+            errors.append(ex)
+
+    cb = _lib.READY_FN(_ready)
+    _lib.check(lib.gsr_backward_early_rgb(ptr(g_drgb), cb, None), "gsr_backward_early_rgb")
+    return cb, errors
+
+
 def _settings(bg, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier, degree,
               prefiltered, debug):
     s = GsrSettings()
@@ -158,6 +176,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
                       degree, False, debug)
+        early = _arm_early(lib, fx, g_drgb, campos, P) if fx is not None else None
         with torch.cuda.device(dev):
             rc = lib.gsr_rasterize_backward(
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),
@@ -166,11 +185,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_cov), None if fx is not None else ptr(g_sh),
                 ptr(g_sc), ptr(g_rot), ws.data_ptr(), ws_bytes, _stream(dev))
             _lib.check(rc, "gsr_rasterize_backward")
-            if fx is not None:
-                rc = lib.gsr_clamped_color_grad(P, W, H, 0, ptr(geomBuffer), ptr(g_col), ptr(g_drgb), _stream(dev))
-                _lib.check(rc, "gsr_clamped_color_grad")
         if fx is not None:
-            fx(flat[: P * 11], g_drgb, campos, means3D, g_sh, P, M, int(degree))
+            if early[1]:
+                raise early[1][0]
+            fx.finish(flat[: P * 11], means3D, g_sh, P, M, int(degree))
         elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),

@@ -11,7 +11,7 @@ import torch
 
 from .. import _lib
 from .._lib import ptr
-from ..diff_gaussian_rasterization._C import _Arena, _f32c, _settings, _stream, mark_visible  # noqa: F401
+from ..diff_gaussian_rasterization._C import _Arena, _arm_early, _f32c, _settings, _stream, mark_visible  # noqa: F401
 
 NUM_OTHERS = 7
 _backward_hook = [None]      # optional callable(head): runs on the parameter-gradient head of every backward
@@ -91,6 +91,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
                       degree, False, debug)
+        early = _arm_early(lib, fx, g_drgb, campos, P) if fx is not None else None
         with torch.cuda.device(dev):
             rc = lib.gsr_surfel_backward(
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),
@@ -99,11 +100,10 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 ptr(g_m2d), ptr(g_col), ptr(g_op), ptr(g_m3d), ptr(g_tm), None if fx is not None else ptr(g_sh),
                 ptr(g_sc), ptr(g_rot), ws.data_ptr(), ws_bytes, _stream(dev))
             _lib.check(rc, "gsr_surfel_backward")
-            if fx is not None:
-                rc = lib.gsr_clamped_color_grad(P, W, H, 1, ptr(geomBuffer), ptr(g_col), ptr(g_drgb), _stream(dev))
-                _lib.check(rc, "gsr_clamped_color_grad")
         if fx is not None:
-            fx(flat[: P * 10], g_drgb, campos, means3D, g_sh, P, M, int(degree))
+            if early[1]:
+                raise early[1][0]
+            fx.finish(flat[: P * 10], means3D, g_sh, P, M, int(degree))
         elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_tm.view(P, 9),

@@ -109,6 +109,7 @@ class FactoredExchange:
     def __init__(self, group=None, rebuild=None):
         self.group, self.rebuild = group, rebuild
         self._bufs = {}
+        self._pending = ()
 
     @staticmethod
     def worth_it(world: int, M: int) -> bool:
@@ -122,23 +123,43 @@ class FactoredExchange:
                                 torch.empty((world, 3), dtype=torch.float32, device=dev))}
         return self._bufs[key]
 
-    def __call__(self, head: torch.Tensor, drgb: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor,
-                 dsh_out: torch.Tensor, P: int, M: int, D: int) -> None:
-        """head: the contiguous non-SH parameter gradients (summed in place); drgb[P,3]: this rank's clamped colour
-        gradient; dsh_out[P,M,3]: receives the SH gradient summed over ranks."""
-        world = dist.get_world_size(self.group) if (dist.is_available() and dist.is_initialized()) else 1
+    def _world(self):
+        return dist.get_world_size(self.group) if (dist.is_available() and dist.is_initialized()) else 1
+
+    def begin(self, drgb: torch.Tensor, campos: torch.Tensor, P: int) -> None:
+        """Start gathering this rank's clamped colour gradient drgb[P,3] and camera position. Called as soon as drgb
+        is final (from the library's gsr_backward_early_rgb callback, i.e. while the preprocess-backward kernel is
+        still to run): NCCL orders the gather after the work already enqueued on the current stream and runs it
+        on its own stream underneath what is enqueued next."""
+        world = self._world()
         drgb_all, campos_all = self._buffers(world, P, drgb.device)
         if world > 1:
-            w_g = dist.all_gather_into_tensor(drgb_all.view(-1), drgb.reshape(-1), group=self.group, async_op=True)
-            w_c = dist.all_gather_into_tensor(campos_all.view(-1), campos.reshape(-1).contiguous(), group=self.group, async_op=True)
-            w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-            w_g.wait(); w_c.wait()
+            self._pending = (
+                dist.all_gather_into_tensor(drgb_all.view(-1), drgb.reshape(-1), group=self.group, async_op=True),
+                dist.all_gather_into_tensor(campos_all.view(-1), campos.reshape(-1).contiguous(), group=self.group, async_op=True))
         else:
             drgb_all[0].copy_(drgb.view(P, 3)); campos_all[0].copy_(campos.reshape(3))
-            w_r = None
+            self._pending = ()
+
+    def finish(self, head: torch.Tensor, means3D: torch.Tensor, dsh_out: torch.Tensor, P: int, M: int, D: int) -> None:
+        """All-reduce the non-SH head (in place), and rebuild the SH gradient summed over ranks into dsh_out[P,M,3]
+        while that collective runs."""
+        world = self._world()
+        drgb_all, campos_all = self._buffers(world, P, dsh_out.device)
+        w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True) if world > 1 else None
+        for w in self._pending:
+            w.wait()
+        self._pending = ()
         (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
         if w_r is not None:
             w_r.wait()
+
+    def __call__(self, head: torch.Tensor, drgb: torch.Tensor, campos: torch.Tensor, means3D: torch.Tensor,
+                 dsh_out: torch.Tensor, P: int, M: int, D: int) -> None:
+        """begin + finish in one go. head: the contiguous non-SH parameter gradients (summed in place); drgb[P,3]:
+        this rank's clamped colour gradient; dsh_out[P,M,3]: receives the SH gradient summed over ranks."""
+        self.begin(drgb, campos, P)
+        self.finish(head, means3D, dsh_out, P, M, D)
 
 
 def _rebuild_cuda(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
