@@ -267,6 +267,19 @@ class Ours:
                                                 sc.sh_degree, campos, geom, n, binning, img, alpha, False)
         return n, radii, color, g[3]          # g[3] = dL_dmeans3D, the head of the gradient arena
 
+    def tile_stats(self, sc, cam):
+        """mean / max tile-list length and the pair count before early exit, from the ranges of one forward"""
+        out = self.C.rasterize_gaussians(sc.bg, sc.means3D, self.E, sc.opacities, sc.scales, sc.rotations, 1.0, self.E,
+                                         cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs,
+                                         sc.sh_degree, cam.campos, False, False)
+        img = out[-1]
+        tiles = ((cam.W + 15) // 16) * ((cam.H + 15) // 16)
+        off = (C.c_size_t * 4)(); tot = C.c_size_t(0)
+        (self.lib.gsr_surfel_image_layout if self.surfel else self.lib.gsr_image_layout)(cam.W, cam.H, off, C.byref(tot))
+        rg = img[off[0]: off[0] + 8 * tiles].view(torch.int32).view(tiles, 2).long()
+        ln = rg[:, 1] - rg[:, 0]
+        return {"tiles": tiles, "mean_list": float(ln.float().mean()), "max_list": int(ln.max()), "pairs": int(ln.sum()) * 256}
+
     def accumulate(self, total, g_means3D, P, M):
         from scorp_b200 import multiview as mv
         return mv.accumulate_param_grads(total, g_means3D, P, M, self.surfel)
@@ -359,6 +372,40 @@ class Reference:
         return color
 
 
+def time_exchange(arm, P, M, surfel, world, dev, reps=10):
+    """The exchange step alone, on buffers of the real size (ms, max over ranks) and what it moves per GPU."""
+    from scorp_b200 import multiview as mv
+    nh = 10 if surfel else 11
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    if arm.name == "ours" and arm.factored:
+        fx = mv.FactoredExchange()
+        head = torch.zeros(P * nh, device=dev); drgb = torch.zeros(P, 3, device=dev); campos = torch.zeros(3, device=dev)
+        means = torch.randn(P, 3, device=dev); dsh = torch.empty(P * M * 3, device=dev)
+        fn = lambda: fx(head, drgb, campos, means, dsh, P, M, int(round(M ** 0.5)) - 1)
+        moved = 4 * P * (nh + 3 * (world - 1))          # reduced floats out + gathered floats in
+        kind = "all_gather(dL_dRGB) + all_reduce(%d floats) + SH rebuild kernel" % nh
+    elif arm.name == "ours":
+        head = torch.zeros(P * mv.param_grad_floats(M, surfel), device=dev)
+        fn = lambda: mv.allreduce_param_grads(head)
+        moved = 4 * head.numel(); kind = "one all_reduce"
+    else:
+        bufs = [torch.zeros(P * w, device=dev) for w in (3, 3 * M, 1, 2 if surfel else 3, 4)]
+        fn = lambda: [dist.all_reduce(b) for b in bufs]
+        moved = 4 * sum(b.numel() for b in bufs); kind = "five all_reduce calls"
+    for _ in range(3):
+        fn()
+    dist.barrier(); torch.cuda.synchronize()
+    ev[0].record()
+    for _ in range(reps):
+        fn()
+    ev[1].record(); torch.cuda.synchronize()
+    t = torch.tensor([ev[0].elapsed_time(ev[1]) / reps], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t)
+    return {"kind": kind, "ms": ms, "bytes_per_gpu": moved, "gbs": moved / ms / 1e6,
+            "frac_of_nvlink_900": moved / ms / 1e6 / 900.0}
+
+
 def run(arm, args, rank, world, local):
     cfg = synth.CONFIGS[args.config]
     surfel, fwd_only = cfg["surfel"], cfg.get("forward_only", False)
@@ -444,6 +491,10 @@ def run(arm, args, rank, world, local):
 
     prime(step_e2e, world)                 # setup, not warm-up: caching-allocator growth for the autograd path
     ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+    exch = None
+    if world > 1 and not fwd_only:
+        exch = time_exchange(arm, P, M, surfel, world, dev)
+    tstats = arm.tile_stats(sc, cams[0]) if arm.name == "ours" else None
     launches = 0
     if arm.name == "ours":
         # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd) (+ clamped colour gradient, SH rebuild)
@@ -451,7 +502,7 @@ def run(arm, args, rank, world, local):
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
-                d2h=4, launches=launches, exchange=exchange)
+                d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats)
 
 
 def main():
@@ -495,6 +546,10 @@ def main():
                 "note": "public API + autograd; per view the camera and the upstream-gradient maps are copied from pinned host memory (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
     }
+    if r["exch"]:
+        line["exchange"] = r["exch"]
+    if r["tstats"]:
+        line["config"]["tile_lists"] = r["tstats"]
     if args.impl == "ours":
         sb = stage_bytes(r["P"], r["M"], r["Pvis"], r["N"], W, H, r["surfel"])
         stages = []
