@@ -117,6 +117,44 @@ int gsr_rasterize_backward(
     float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
     void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- model-space entry points (caller-side parameter staging) --------
+ * No reference counterpart at the C++ level: these fold what the reference's caller runs as separate torch kernels
+ * right before the boundary -- GaussianModel.get_features = torch.cat(features_dc, features_rest)
+ * (gs3dgs/scene/gaussian_model.py:139-142), get_opacity = sigmoid, get_scaling = exp, get_rotation = normalize
+ * (:31-46,126-146), all called from gaussian_renderer.render() (gs3dgs/gaussian_renderer/__init__.py:67-90) -- and
+ * their autograd mirrors, into the preprocess kernels. Inputs are the tensors GaussianModel STORES:
+ *   xyz[P*3], features_dc[P*1*3], features_rest[P*(M-1)*3] (NULL when M == 1), opacity[P] (pre-sigmoid),
+ *   scaling[P*3] (pre-exp), rotation[P*4] (un-normalised quaternion).
+ * The result equals gsr_rasterize_forward on the activated, concatenated tensors. The stock entry points above are
+ * unchanged; this pair is opt-in (scorp_b200/model_space.py). */
+typedef struct GsrModelParams {
+    const float* xyz;
+    const float* features_dc;
+    const float* features_rest;
+    const float* opacity;
+    const float* scaling;
+    const float* rotation;
+} GsrModelParams;
+typedef struct GsrModelGrads {      /* same shapes as GsrModelParams; every row is written */
+    float* xyz;
+    float* features_dc;
+    float* features_rest;
+    float* opacity;
+    float* scaling;
+    float* rotation;
+} GsrModelGrads;
+int gsr_rasterize_forward_raw(
+    const GsrSettings* s, int P, int M, const GsrModelParams* params,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream);
+/* Gradients with respect to the STORED parameters (through the activations); dL_dmeans2D[P*3] is the screen-space
+ * gradient the densification statistics use (train_3dgs.py:180-183). Workspace as for gsr_rasterize_backward. */
+int gsr_rasterize_backward_raw(
+    const GsrSettings* s, int P, int M, int R, const GsrModelParams* params,
+    const int32_t* radii, const void* geom, const void* binning, const void* image, const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, const GsrModelGrads* grads, void* workspace, size_t workspace_bytes, void* stream);
+
 /* present[P] (1 byte each) = view-space z > 0.2 */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
@@ -184,6 +222,22 @@ int gsr_clamped_color_grad(int P, int W, int H, int surfel, const void* geom_buf
 int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
                            const float* drgb, float* dL_dsh, void* stream);
+
+/* ---- photometric loss (the step right after the boundary) ----------------
+ * Replaces l1_loss + ssim of gs3dgs/utils/loss_utils.py:17-18,45-73 (five grouped 11x11 F.conv2d calls and ~20
+ * elementwise torch kernels per forward, mirrored by autograd) as used by train_3dgs.py:106-107:
+ *     loss = (1 - lambda_dssim) * mean|img - gt| + lambda_dssim * (1 - mean(ssim_map(img, gt)))
+ * img, gt: [C*H*W] fp32 (C planes, F.conv2d zero padding 5, window gaussian(11, 1.5)).
+ * forward writes out3 (device) = { loss, l1, ssim } and fills the workspace (three derivative maps + per-CTA
+ * partial sums; gsr_l1_ssim_workspace_bytes) that backward reads. Deterministic (no float atomics).
+ * backward writes dL_dimg[C*H*W] = upstream * (w_l1 * d l1/d img + w_ssim * d ssim/d img); upstream is a DEVICE
+ * scalar (NULL = 1). For the fused training loss pass w_l1 = 1 - lambda, w_ssim = -lambda; (1, 0) and (0, 1) give the
+ * gradients of l1_loss and ssim alone. gt receives no gradient (it never does in the reference's loops). */
+size_t gsr_l1_ssim_workspace_bytes(int C, int H, int W);
+int gsr_l1_ssim_forward(int C, int H, int W, const float* img, const float* gt, float lambda_dssim,
+                        float* out3, void* workspace, size_t workspace_bytes, void* stream);
+int gsr_l1_ssim_backward(int C, int H, int W, const float* img, const float* gt, const float* upstream,
+                         float w_l1, float w_ssim, const void* workspace, float* dL_dimg, void* stream);
 
 #ifdef __cplusplus
 }

@@ -249,3 +249,21 @@ def knn_dist2(points, brute=False):
     if P:
         (L.knn_oracle_brute if brute else L.knn_oracle)(C.c_int(P), _p(pts), _p(out))
     return out
+
+
+# ---- photometric loss (oracle/loss_oracle.c) --------------------------------------------------------
+
+def l1_ssim(img, gt, lambda_dssim=0.2, grads=True):
+    """Restatement of loss_utils.py l1_loss / ssim and train_3dgs.py:107.
+    -> dict(loss, l1, ssim [, dl1, dssim, dloss]) with the gradients w.r.t. img."""
+    L = lib()
+    a, b = _f(img), _f(gt)
+    Cn, H, W = a.shape
+    out = (C.c_double * 3)()
+    dl1 = np.zeros_like(a) if grads else None
+    dss = np.zeros_like(a) if grads else None
+    L.loss_oracle_l1_ssim(C.c_int(Cn), C.c_int(H), C.c_int(W), _p(a), _p(b), C.c_float(lambda_dssim), out, _p(dl1), _p(dss))
+    res = dict(loss=out[0], l1=out[1], ssim=out[2])
+    if grads:
+        res.update(dl1=dl1, dssim=dss, dloss=((1.0 - lambda_dssim) * dl1 - lambda_dssim * dss).astype(np.float32))
+    return res

@@ -30,6 +30,16 @@ class GsrSettings(C.Structure):
     ]
 
 
+class GsrModelParams(C.Structure):
+    """struct GsrModelParams (include/gsr_b200.h): the tensors GaussianModel stores."""
+    _fields_ = [(n, c_void_p) for n in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")]
+
+
+class GsrModelGrads(C.Structure):
+    """struct GsrModelGrads (include/gsr_b200.h)."""
+    _fields_ = [(n, c_void_p) for n in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")]
+
+
 _P = c_void_p
 # name -> (restype, argtypes); every symbol include/gsr_b200.h declares
 SIGNATURES = {
@@ -42,6 +52,13 @@ SIGNATURES = {
     "gsr_backward_workspace_bytes": (c_size_t, [c_int]),
     "gsr_rasterize_backward": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int] + [_P] * 6 + [_P]
                                + [_P] * 3 + [_P] + [_P] * 3 + [_P] * 8 + [_P, c_size_t, _P]),
+    "gsr_rasterize_forward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, C.POINTER(GsrModelParams)] + [_P] * 4
+                                  + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
+    "gsr_rasterize_backward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int, C.POINTER(GsrModelParams)]
+                                   + [_P] * 5 + [_P] * 3 + [_P, C.POINTER(GsrModelGrads), _P, c_size_t, _P]),
+    "gsr_l1_ssim_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
+    "gsr_l1_ssim_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, c_size_t, _P]),
+    "gsr_l1_ssim_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),
     "gsr_mark_visible": (c_int, [c_int, _P, _P, _P, _P, _P]),
     "gsr_geom_layout": (None, [c_int, c_int, C.POINTER(c_size_t), C.POINTER(c_size_t)]),
     "gsr_image_layout": (None, [c_int, c_int, C.POINTER(c_size_t), C.POINTER(c_size_t)]),

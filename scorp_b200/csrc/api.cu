@@ -88,9 +88,11 @@ void gsr_binning_layout(int N, size_t off[3], size_t* total) { *total = carve_bi
 
 size_t gsr_backward_workspace_bytes(int P) { return align_up((size_t)(P > 0 ? P : 1) * ACC_STRIDE * sizeof(float)); }
 
-int gsr_rasterize_forward(
+// shared by gsr_rasterize_forward and gsr_rasterize_forward_raw (raw: shs = features_dc, shs_rest = features_rest,
+// opacities / scales / rotations are the stored parameters)
+static int forward_impl(
     const GsrSettings* s, int P, int M,
-    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* means3D, const float* shs, const float* shs_rest, bool raw, const float* colors_precomp,
     const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
     float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
     gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
@@ -141,6 +143,7 @@ int gsr_rasterize_forward(
     a.scales = scales; a.rotations = rotations; a.cov3D_precomp = cov3D_precomp;
     a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos; a.bg = s->bg;
     a.prefiltered = s->prefiltered != 0;
+    a.shs_rest = shs_rest; a.raw = raw;
     if ((rc = check_cuda(launch_preprocess(a, g, radii, st), "preprocess launch"))) return rc;
     if ((rc = stage_check(s, st, "preprocess"))) return rc;
     prof_mark(1, st);
@@ -169,6 +172,45 @@ int gsr_rasterize_forward(
     return stage_check(s, st, "render forward");
 }
 
+int gsr_rasterize_forward(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    return forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                        out_color, out_depth, out_alpha, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+int gsr_rasterize_forward_raw(
+    const GsrSettings* s, int P, int M, const GsrModelParams* mp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    if (!mp) { set_error("null model parameters"); return GSR_EINVAL; }
+    if (P > 0 && (!mp->features_dc || !mp->opacity || !mp->scaling || !mp->rotation || (M > 1 && !mp->features_rest))) {
+        set_error("null model parameter"); return GSR_EINVAL;
+    }
+    if (M < 1) { set_error("model-space entry needs SH coefficients (M >= 1)"); return GSR_EUNSUPPORTED; }
+    return forward_impl(s, P, M, mp->xyz, mp->features_dc, mp->features_rest, true, nullptr, mp->opacity, mp->scaling,
+                        mp->rotation, nullptr, out_color, out_depth, out_alpha, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+struct RawBwd { const float* shs_rest; const float* opacities; float* dL_dsh_rest; };
+
+static int backward_impl(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream, const RawBwd* raw);
+
 int gsr_rasterize_backward(
     const GsrSettings* s, int P, int M, int R,
     const float* means3D, const float* shs, const float* colors_precomp,
@@ -180,6 +222,42 @@ int gsr_rasterize_backward(
     float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
     float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
     void* workspace, size_t workspace_bytes, void* stream)
+{
+    return backward_impl(s, P, M, R, means3D, shs, colors_precomp, scales, rotations, cov3D_precomp, radii, geom, binning,
+                         image, out_alpha, dL_dout_color, dL_dout_depth, dL_dout_alpha, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                         dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations, workspace, workspace_bytes, stream, nullptr);
+}
+
+int gsr_rasterize_backward_raw(
+    const GsrSettings* s, int P, int M, int R, const GsrModelParams* mp,
+    const int32_t* radii, const void* geom, const void* binning, const void* image, const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, const GsrModelGrads* mg, void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!mp || !mg) { set_error("null model parameters/gradients"); return GSR_EINVAL; }
+    if (P > 0 && (!mp->features_dc || !mp->opacity || !mp->scaling || !mp->rotation || (M > 1 && !mp->features_rest) ||
+                  !mg->features_dc || !mg->opacity || !mg->scaling || !mg->rotation || !mg->xyz || (M > 1 && !mg->features_rest))) {
+        set_error("null model parameter or gradient"); return GSR_EINVAL;
+    }
+    if (M < 1) { set_error("model-space entry needs SH coefficients (M >= 1)"); return GSR_EUNSUPPORTED; }
+    const RawBwd raw = { mp->features_rest, mp->opacity, mg->features_rest };
+    // dL_dcolors / dL_dcov3D have no model parameter behind them: not produced (any non-NULL pointer passes the checks)
+    return backward_impl(s, P, M, R, mp->xyz, mp->features_dc, nullptr, mp->scaling, mp->rotation, nullptr, radii, geom, binning,
+                         image, out_alpha, dL_dout_color, dL_dout_depth, dL_dout_alpha, dL_dmeans2D, mg->xyz, mg->opacity,
+                         mg->xyz, mg->xyz, mg->features_dc, mg->scaling, mg->rotation, workspace, workspace_bytes, stream, &raw);
+}
+
+static int backward_impl(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* cov3D_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* out_alpha,
+    const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dcov3D, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream, const RawBwd* raw)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
@@ -226,6 +304,7 @@ int gsr_rasterize_backward(
     b.radii = radii; b.clamped = g.clamped; b.acc = acc;
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
+    if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
     if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");

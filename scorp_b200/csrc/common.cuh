@@ -116,6 +116,21 @@ __device__ __forceinline__ float subr(float a, float b) { return __fsub_rn(a, b)
 __device__ __forceinline__ float fmar(float a, float b, float c) { return __fmaf_rn(a, b, c); }
 __device__ __forceinline__ float divr(float a, float b) { return __fdiv_rn(a, b); }
 
+// ---- parameter activations of GaussianModel (gs3dgs/scene/gaussian_model.py:31-46), fused into the model-space
+// entry points. Written as the float sequences torch's CUDA kernels execute: sigmoid = 1 / (1 + expf(-x)) with an IEEE
+// division, exp = expf, normalize = x / max(sqrt((x0^2 + x2^2) + (x1^2 + x3^2)), 1e-12) (squares rounded; this pairing is what torch's
+// reduction kernel does for a [P,4] row: two lanes, each summing a stride-2 pair -- identified on a B200 by
+// tools/gpu_diag_norm.py, 0 of 200000 rows differ).
+__device__ __forceinline__ float act_opacity(float x) { return divr(1.0f, addr(1.0f, expf(-x))); }
+__device__ __forceinline__ float act_scale(float x) { return expf(x); }
+__device__ __forceinline__ float quat_norm(float4 q) {
+    return fmaxf(__fsqrt_rn(addr(addr(mulr(q.x, q.x), mulr(q.z, q.z)), addr(mulr(q.y, q.y), mulr(q.w, q.w)))), 1e-12f);
+}
+__device__ __forceinline__ float4 act_rotation(float4 q) {
+    const float n = quat_norm(q);
+    return make_float4(divr(q.x, n), divr(q.y, n), divr(q.z, n), divr(q.w, n));
+}
+
 // row r of (matrix * [p,1]) with the reference's rounding sequence
 // (transformPoint4x3/4x4, auxiliary.h:58-80: FMUL(y*m4) FFMA(x,m0) FFMA(z,m8) FADD(m12)).
 __device__ __forceinline__ float xform_row(const float* __restrict__ m, int r, float x, float y, float z) {
@@ -178,6 +193,10 @@ struct FwdArgs {
     const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *cov3D_precomp;
     const float *view, *proj, *campos, *bg;
     bool prefiltered;
+    // model-space variant (gsr_rasterize_forward_raw): shs = features_dc[P,1,3], shs_rest = features_rest[P,M-1,3],
+    // opacities / scales / rotations hold the stored (pre-activation) parameters
+    const float* shs_rest = nullptr;
+    bool raw = false;
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
@@ -203,6 +222,11 @@ struct BwdArgs {
     const uint8_t* clamped;
     const float* acc;  // 12 floats per Gaussian from the blend backward
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dcov3D, *dL_dsh, *dL_dscales, *dL_drotations;
+    // model-space variant (gsr_rasterize_backward_raw): split SH rows, gradients through the activations
+    const float* shs_rest = nullptr;
+    const float* opacities = nullptr;      // raw opacity (only read when raw)
+    float* dL_dsh_rest = nullptr;
+    bool raw = false;
 };
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st);
 

@@ -71,7 +71,7 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
     return make_float3(addr(cov00, 0.3f), cov01, addr(cov11, 0.3f));
 }
 
-template <bool VEC>
+template <bool VEC, bool RAW>
 __global__ void __launch_bounds__(256, 4)
 preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -98,9 +98,10 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
             } else {
                 // scalar loads: the caller's tensor may be a view at any 4-byte offset
                 const float* qp = a.rotations + 4 * (size_t)idx;
-                const float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
-                cov3d_from_scale_rot(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2),
-                                     a.scale_modifier, q.x, q.y, q.z, q.w, c3);
+                float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
+                float sx = __ldg(a.scales + 3 * idx), sy = __ldg(a.scales + 3 * idx + 1), sz = __ldg(a.scales + 3 * idx + 2);
+                if constexpr (RAW) { q = act_rotation(q); sx = act_scale(sx); sy = act_scale(sy); sz = act_scale(sz); }
+                cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q.x, q.y, q.z, q.w, c3);
 #pragma unroll
                 for (int k = 0; k < 6; ++k) g.cov3D[6 * idx + k] = c3[k];
             }
@@ -128,8 +129,9 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
                 rec.b = __ldg(a.colors_precomp + 3 * idx + 2);
             } else {
                 ShReader<VEC> sh;
-                const float* base = a.shs + (size_t)idx * a.M * 3;
+                const float* base = RAW ? a.shs + (size_t)idx * 3 : a.shs + (size_t)idx * a.M * 3;
                 sh.base = base;
+                sh.rest = RAW ? a.shs_rest + (size_t)idx * (a.M - 1) * 3 : base + 3;
                 if constexpr (VEC) {
 #pragma unroll
                     for (int k = 0; k < 12; ++k) sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k);
@@ -141,7 +143,7 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
                 g.clamped[idx] = cl;
                 rec.r = (col.r < 0.0f) ? 0.0f : col.r; rec.g = (col.g < 0.0f) ? 0.0f : col.g; rec.b = (col.b < 0.0f) ? 0.0f : col.b;
             }
-            const float op = __ldg(a.opacities + idx);
+            const float op = RAW ? act_opacity(__ldg(a.opacities + idx)) : __ldg(a.opacities + idx);
             rec.x = ix; rec.y = iy; rec.ca = ca; rec.cb = cb; rec.cc = cc; rec.opacity = op; rec.depth = depth;
             // alpha = min(0.99, op*exp(power)) < 1/255 is implied by power < thr (0.2 % margin).
             rec.thr = (op > 0.0f) ? (-logf(255.0f * op) - 0.002f) : ((op <= 0.0f) ? FLT_MAX : -FLT_MAX);
@@ -168,8 +170,9 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st) {
     const int blocks = (a.P + 255) / 256;
     const bool vec = a.shs && a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
-    if (vec) preprocess_kernel<true><<<blocks, 256, 0, st>>>(a, g, radii);
-    else     preprocess_kernel<false><<<blocks, 256, 0, st>>>(a, g, radii);
+    if (a.raw)    preprocess_kernel<false, true><<<blocks, 256, 0, st>>>(a, g, radii);
+    else if (vec) preprocess_kernel<true, false><<<blocks, 256, 0, st>>>(a, g, radii);
+    else          preprocess_kernel<false, false><<<blocks, 256, 0, st>>>(a, g, radii);
     return cudaGetLastError();
 }
 

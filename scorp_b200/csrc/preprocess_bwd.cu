@@ -10,7 +10,9 @@
 
 namespace gsr {
 
-template <int M3>       // 3 * SH coefficients per Gaussian (0: colours were precomputed)
+// M3: 3 * SH coefficients per Gaussian (0: colours were precomputed). RAW: model-space variant -- SH rows split into
+// features_dc / features_rest, and the gradients are taken through sigmoid / exp / normalize to the stored parameters.
+template <int M3, bool RAW>
 __global__ void __launch_bounds__(SH_TILE, 8)
 preprocess_backward_kernel(BwdArgs a) {
     __shared__ float s_sh[M3 ? SH_TILE * ShTile<M3>::STRIDE : 1];
@@ -25,7 +27,8 @@ preprocess_backward_kernel(BwdArgs a) {
         __syncthreads();
         // asynchronous (LDGSTS): the whole tile is in flight while the per-Gaussian inputs below are fetched and
         // the covariance part is computed; waited for just before the SH backward
-        sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
+        if constexpr (RAW) sh_tile_load_async_split<M3>(a.shs, a.shs_rest, row0, nrows, s_vis, s_sh);
+        else               sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
     }
 
     float dcov[6] = { 0, 0, 0, 0, 0, 0 };
@@ -113,9 +116,15 @@ preprocess_backward_kernel(BwdArgs a) {
         // ---- cov3D -> scale, rotation (backward.cu:278-341)
         if (!a.cov_precomp) {
             const float* qp = a.rotations + 4 * (size_t)idx;
-            const float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
+            float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
+            V3 sc = ld3(a.scales + 3 * idx);
+            float qn = 1.0f;
+            if constexpr (RAW) {
+                qn = quat_norm(q); q = act_rotation(q);
+                sc = { act_scale(sc.x), act_scale(sc.y), act_scale(sc.z) };
+            }
             const float r = q.x, x = q.y, y = q.z, z = q.w;
-            const V3 s = a.scale_modifier * ld3(a.scales + 3 * idx);
+            const V3 s = a.scale_modifier * sc;
             // rows of R-hat (R-hat(row,col) = glm R[col][row])
             const V3 R0 = { 1.f - 2.f * (y * y + z * z), 2.f * (x * y + r * z), 2.f * (x * z - r * y) };
             const V3 R1 = { 2.f * (x * y - r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z + r * x) };
@@ -135,6 +144,17 @@ preprocess_backward_kernel(BwdArgs a) {
             drot.y = 2 * y * (N1.x + N0.y) + 2 * z * (N2.x + N0.z) + 2 * r * (N1.z - N2.y) - 4 * x * (N2.z + N1.y);
             drot.z = 2 * x * (N1.x + N0.y) + 2 * r * (N2.x - N0.z) + 2 * z * (N1.z + N2.y) - 4 * y * (N2.z + N0.x);
             drot.w = 2 * r * (N0.y - N1.x) + 2 * x * (N2.x + N0.z) + 2 * y * (N1.z + N2.y) - 4 * z * (N1.y + N0.x);
+            if constexpr (RAW) {
+                // exp: d/draw = d/dscale * scale;  normalize: d/draw = (g - q (q.g)) / |raw|
+                dscale = { dscale.x * sc.x, dscale.y * sc.y, dscale.z * sc.z };
+                const float qg = q.x * drot.x + q.y * drot.y + q.z * drot.z + q.w * drot.w;
+                const float in = 1.0f / qn;
+                drot = make_float4((drot.x - q.x * qg) * in, (drot.y - q.y * qg) * in, (drot.z - q.z * qg) * in, (drot.w - q.w * qg) * in);
+            }
+        }
+        if constexpr (RAW) {      // sigmoid: d/draw = d/dopacity * s (1 - s)
+            const float so = act_opacity(__ldg(a.opacities + idx));
+            dop = dop * ((1.0f - so) * so);
         }
     }
     if constexpr (M3 != 0) {
@@ -147,16 +167,19 @@ preprocess_backward_kernel(BwdArgs a) {
             dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
         __syncthreads();
-        if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
+        if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
+        else if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
     if (!valid) return;
 
     st3(a.dL_dmeans3D + 3 * idx, dmean);
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
-    st3(a.dL_dcolors + 3 * idx, dcol);
     a.dL_dopacity[idx] = dop;
+    if constexpr (!RAW) {       // no model parameter behind these two in the model-space variant
+        st3(a.dL_dcolors + 3 * idx, dcol);
 #pragma unroll
-    for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+        for (int k = 0; k < 6; ++k) a.dL_dcov3D[6 * (size_t)idx + k] = dcov[k];
+    }
     st3(a.dL_dscales + 3 * idx, dscale);
     float* dq = a.dL_drotations + 4 * (size_t)idx;     // scalar: output may sit at any 4-byte offset
     dq[0] = drot.x; dq[1] = drot.y; dq[2] = drot.z; dq[3] = drot.w;
@@ -164,12 +187,22 @@ preprocess_backward_kernel(BwdArgs a) {
 
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st) {
     const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    if (a.raw) {
+        switch (3 * a.M) {
+        case 3:  preprocess_backward_kernel<3, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 12: preprocess_backward_kernel<12, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 27: preprocess_backward_kernel<27, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 48: preprocess_backward_kernel<48, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
     switch (a.shs ? 3 * a.M : 0) {
-    case 0:  preprocess_backward_kernel<0><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 3:  preprocess_backward_kernel<3><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 12: preprocess_backward_kernel<12><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 27: preprocess_backward_kernel<27><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 48: preprocess_backward_kernel<48><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 0:  preprocess_backward_kernel<0, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 3:  preprocess_backward_kernel<3, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 12: preprocess_backward_kernel<12, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 27: preprocess_backward_kernel<27, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 48: preprocess_backward_kernel<48, false><<<blocks, SH_TILE, 0, st>>>(a); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -14,14 +14,16 @@ struct Sh3 { float r, g, b; };
 // Loads coefficient k (3 floats) of one Gaussian. VEC: 48 floats were preloaded as float4s.
 template <bool VEC>
 struct ShReader {
-    const float* base;     // scalar path: pointer to this Gaussian's coefficients
+    const float* base;     // scalar path: pointer to this Gaussian's coefficient 0 (features_dc in the split layout)
+    const float* rest;     // scalar path: coefficients 1.. (base + 3, or this Gaussian's features_rest row)
     float4 v[VEC ? 12 : 1];
     __device__ __forceinline__ Sh3 get(int k) const {
         if constexpr (VEC) {
             const float* f = reinterpret_cast<const float*>(v);
             return { f[3 * k], f[3 * k + 1], f[3 * k + 2] };
         } else {
-            return { __ldg(base + 3 * k), __ldg(base + 3 * k + 1), __ldg(base + 3 * k + 2) };
+            const float* p = (k == 0) ? base : rest + 3 * (k - 1);
+            return { __ldg(p), __ldg(p + 1), __ldg(p + 2) };
         }
     }
 };
@@ -187,6 +189,44 @@ __device__ __forceinline__ void sh_tile_load_async(const float* __restrict__ shs
         if (s_vis[g]) cp_async4(s_sh + g * ShTile<M3>::STRIDE + c, src + e);
     }
     cp_async_commit();
+}
+// split layout (model-space entry points): column 0..2 of the tile from dc[P,3], the rest from rest[P,M3-3]
+template <int M3>
+__device__ __forceinline__ void sh_tile_load_async_split(const float* __restrict__ dc, const float* __restrict__ rest,
+                                                         size_t row0, int nrows, const uint8_t* s_vis, float* s_sh) {
+    const float* src0 = dc + row0 * 3;
+    for (int e = threadIdx.x; e < nrows * 3; e += SH_TILE) {
+        const int g = e / 3, c = e - g * 3;
+        if (s_vis[g]) cp_async4(s_sh + g * ShTile<M3>::STRIDE + c, src0 + e);
+    }
+    if constexpr (M3 > 3) {
+        constexpr int R3 = M3 - 3;
+        const float* src = rest + row0 * R3;
+#pragma unroll 8
+        for (int e = threadIdx.x; e < nrows * R3; e += SH_TILE) {
+            const int g = e / R3, c = e - g * R3;
+            if (s_vis[g]) cp_async4(s_sh + g * ShTile<M3>::STRIDE + 3 + c, src + e);
+        }
+    }
+    cp_async_commit();
+}
+template <int M3>
+__device__ __forceinline__ void sh_tile_store_split(float* __restrict__ ddc, float* __restrict__ drest, size_t row0, int nrows,
+                                                    const uint8_t* s_vis, const float* s_sh) {
+    float* dst0 = ddc + row0 * 3;
+    for (int e = threadIdx.x; e < nrows * 3; e += SH_TILE) {
+        const int g = e / 3, c = e - g * 3;
+        dst0[e] = s_vis[g] ? s_sh[g * ShTile<M3>::STRIDE + c] : 0.0f;
+    }
+    if constexpr (M3 > 3) {
+        constexpr int R3 = M3 - 3;
+        float* dst = drest + row0 * R3;
+#pragma unroll 8
+        for (int e = threadIdx.x; e < nrows * R3; e += SH_TILE) {
+            const int g = e / R3, c = e - g * R3;
+            dst[e] = s_vis[g] ? s_sh[g * ShTile<M3>::STRIDE + 3 + c] : 0.0f;
+        }
+    }
 }
 template <int M3>
 __device__ __forceinline__ void sh_tile_store(float* __restrict__ dsh, size_t row0, int nrows,

@@ -174,7 +174,7 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
             } else {
                 ShReader<VEC> sh;
                 const float* base = a.shs + (size_t)idx * a.M * 3;
-                sh.base = base;
+                sh.base = base; sh.rest = base + 3;
                 if constexpr (VEC) {
 #pragma unroll
                     for (int k = 0; k < 12; ++k) sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k);

@@ -1,0 +1,142 @@
+"""Model-space entry points on the GPU: rasterize_model on the tensors GaussianModel
+stores must equal what the reference's caller computes -- torch.cat(features_dc, features_rest), sigmoid, exp,
+normalize (gs3dgs/scene/gaussian_model.py:126-146) followed by the stock rasterizer -- in the forward, and the
+autograd chain of those torch ops in the backward."""
+import json
+import os
+from types import SimpleNamespace
+
+import pytest
+import torch
+
+import helpers as h
+from scorp_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _stored(sc, seed=5):
+    """Stored parameters whose activations reproduce the scene (rotation left un-normalised on purpose)."""
+    g = torch.Generator().manual_seed(seed)
+    dev = sc.means3D.device
+    op = sc.opacities.clamp(1e-4, 1 - 1e-4)
+    stored = dict(
+        xyz=sc.means3D.clone(),
+        features_dc=sc.shs[:, :1, :].contiguous().clone(),
+        features_rest=sc.shs[:, 1:, :].contiguous().clone(),
+        opacity=torch.log(op / (1 - op)),
+        scaling=torch.log(sc.scales),
+        rotation=sc.rotations * (0.25 + 3.0 * torch.rand(sc.P, 1, generator=g)).to(dev),
+    )
+    return {k: v.requires_grad_(True) for k, v in stored.items()}
+
+
+def _settings(sc, cam, mod, scale_modifier=1.0):
+    return mod.GaussianRasterizationSettings(
+        image_height=cam.H, image_width=cam.W, tanfovx=cam.tanfovx, tanfovy=cam.tanfovy, bg=sc.bg,
+        scale_modifier=scale_modifier, viewmatrix=cam.viewmatrix, projmatrix=cam.projmatrix, sh_degree=sc.sh_degree,
+        campos=cam.campos, prefiltered=False, debug=False)
+
+
+def _stock(st, rs):
+    """the reference caller's staging (torch kernels) + the stock drop-in rasterizer"""
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    shs = torch.cat((st["features_dc"], st["features_rest"]), dim=1)
+    m2d = torch.zeros_like(st["xyz"], requires_grad=True) + 0
+    m2d.retain_grad()
+    out = dgr.GaussianRasterizer(rs)(means3D=st["xyz"], means2D=m2d, opacities=torch.sigmoid(st["opacity"]), shs=shs,
+                                     scales=torch.exp(st["scaling"]),
+                                     rotations=torch.nn.functional.normalize(st["rotation"]))
+    return out, m2d
+
+
+def _model(st, rs):
+    from scorp_b200 import model_space as ms
+    m2d = torch.zeros_like(st["xyz"], requires_grad=True) + 0
+    m2d.retain_grad()
+    return ms.rasterize_model(st["xyz"], m2d, st["features_dc"], st["features_rest"], st["opacity"], st["scaling"],
+                              st["rotation"], rs), m2d
+
+
+def _note(name, **kw):
+    """exact-equality observations for profiles/ (not assertions)"""
+    os.makedirs(os.path.join(h.ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(h.ROOT, "gpurun_out", "model_space_diag.jsonl"), "a") as f:
+        f.write(json.dumps(dict(case=name, **kw)) + "\n")
+
+
+@pytest.mark.parametrize("name,kw,smod", [
+    ("C1", dict(P=30_000, W=256, H=192), 1.0),           # SH0: features_rest is empty
+    ("C2", dict(P=60_000, W=320, H=208), 1.0),           # SH3
+    ("C2", dict(P=20_000, W=200, H=120), 0.7),           # scale modifier
+])
+def test_forward_and_backward_match_torch_staging(name, kw, smod):
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    sc = h.make(name, **kw); cam = sc.cameras[0]
+    rs = _settings(sc, cam, dgr, smod)
+    sa, sb = _stored(sc), _stored(sc)
+    (ca, ra, da, aa), m2a = _stock(sa, rs)
+    (cb, rb, db, ab), m2b = _model(sb, rs)
+    exact = dict(color=torch.equal(ca, cb), depth=torch.equal(da, db), alpha=torch.equal(aa, ab),
+                 radii=torch.equal(ra, rb))
+    _note(f"{name}-{kw['P']}-{smod}", **exact, radii_mismatch=int((ra != rb).sum()))
+    # the activations are written as the float sequences torch's kernels execute, so everything is bit-identical
+    assert torch.equal(ra, rb), f"{int((ra != rb).sum())} radii differ"
+    assert torch.equal(ca, cb) and torch.equal(da, db) and torch.equal(aa, ab), exact
+
+    gc, gd, ga = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 33)]
+    for (c, d, a) in ((ca, da, aa), (cb, db, ab)):
+        ((c * gc).sum() + (d * gd).sum() + (a * ga).sum()).backward()
+
+    def same(x, y):      # two backward runs differ by the order of float atomics in the blend backward
+        return torch.allclose(x, y, rtol=1e-3, atol=1e-5 * float(y.abs().max()) + 1e-30)
+    for k in sa:
+        if sa[k].numel() == 0:
+            assert sb[k].grad is None or sb[k].grad.numel() == 0
+            continue
+        assert sb[k].grad is not None and sb[k].grad.shape == sa[k].shape, k
+        assert same(sb[k].grad, sa[k].grad), (k, float((sb[k].grad - sa[k].grad).abs().max()), float(sa[k].grad.abs().max()))
+    assert same(m2b.grad, m2a.grad)
+    # invisible Gaussians get exact zeros in every gradient row (every row is written, none left uninitialised)
+    inv = rb == 0
+    for k in sb:
+        if sb[k].numel():
+            assert float(sb[k].grad[inv].abs().max() if inv.any() else 0.0) == 0.0, k
+
+
+def test_render_mirror_of_gaussian_renderer():
+    """model_space.render() with a GaussianModel-shaped object returns gaussian_renderer.render()'s dict."""
+    import math
+    from scorp_b200 import model_space as ms
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    sc = h.make("C2", P=20_000, W=256, H=160); cam = sc.cameras[0]
+    st = _stored(sc)
+    pc = SimpleNamespace(get_xyz=st["xyz"], _features_dc=st["features_dc"], _features_rest=st["features_rest"],
+                         _opacity=st["opacity"], _scaling=st["scaling"], _rotation=st["rotation"],
+                         active_sh_degree=sc.sh_degree, max_sh_degree=3)
+    vc = SimpleNamespace(FoVx=2 * math.atan(cam.tanfovx), FoVy=2 * math.atan(cam.tanfovy), resolution=(cam.W, cam.H),
+                         world_view_transform=cam.viewmatrix, full_proj_transform=cam.projmatrix,
+                         camera_center=cam.campos)
+    pkg = ms.render(vc, pc, SimpleNamespace(debug=False, compute_cov3D_python=False, convert_SHs_python=False), sc.bg)
+    assert set(pkg) == {"render", "viewspace_points", "visibility_filter", "radii", "render_depth", "render_alpha"}
+    assert pkg["render"].shape == (3, cam.H, cam.W) and pkg["visibility_filter"].dtype == torch.bool
+    (c, r, d, a), _ = _stock(_stored(sc), _settings(sc, cam, dgr))
+    assert torch.allclose(pkg["render"], c, rtol=1e-4, atol=1e-6) and torch.equal(pkg["radii"], r)
+    pkg["render"].sum().backward()
+    assert pkg["viewspace_points"].grad is not None and st["features_rest"].grad is not None
+    assert float(st["opacity"].grad.abs().max()) > 0
+
+
+def test_empty_and_errors():
+    from scorp_b200 import model_space as ms, _lib
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    sc = h.make("C1", P=1_000, W=64, H=64); cam = sc.cameras[0]
+    rs = _settings(sc, cam, dgr)
+    z = lambda *s: torch.zeros(*s, device="cuda")
+    c, r, d, a = ms.rasterize_model(z(0, 3), z(0, 3), z(0, 1, 3), z(0, 0, 3), z(0, 1), z(0, 3), z(0, 4), rs)
+    assert r.numel() == 0 and float(c.abs().max()) == 0.0
+    with pytest.raises(_lib.GsrError):
+        ms.rasterize_model(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 1, 3), torch.zeros(4, 0, 3),
+                           torch.zeros(4, 1), torch.zeros(4, 3), torch.zeros(4, 4), rs)
+    with pytest.raises(RuntimeError, match="features_dc"):
+        ms.rasterize_model(z(4, 3), z(4, 3), z(3, 1, 3), z(4, 0, 3), z(4, 1), z(4, 3), z(4, 4), rs)

@@ -1,0 +1,167 @@
+#!/usr/bin/env python
+"""Measurement of the SURVEY.md 8(f) rows next to the rasterizer boundary, each against what a user of the reference
+runs today on the same GPU (its own torch code around the drop-in rasterizer). One JSON line per row.
+
+    python tools/bench_next.py [--config C2] [--steps 30] [--warmup 5]
+
+row "staging" (8(f) rank 1): stored GaussianModel tensors -> image -> gradients on the stored tensors
+    stock : torch.cat / sigmoid / exp / normalize + stock GaussianRasterizer + autograd  (gaussian_model.py:126-146)
+    model : scorp_b200.model_space.rasterize_model (activations and the SH split fused into the preprocess kernels)
+row "loss" (8(f) rank 3): (1 - l) * L1 + l * (1 - SSIM) forward + backward on a C2-sized image
+    torch : loss_utils.py:17-18,45-73 restated call for call (five grouped conv2d + elementwise kernels + autograd)
+    fused : scorp_b200.loss_utils.l1_ssim_loss (two kernels)
+Times are CUDA events around K steps after W warm-ups, inputs resident; HBM fraction uses MEASURED_PEAKS.json.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from scorp_b200 import synth
+
+
+def peak():
+    try:
+        return float(json.loads((ROOT / "MEASURED_PEAKS.json").read_text())["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+def timeit(fn, K, W):
+    for _ in range(W):
+        fn()
+    torch.cuda.synchronize()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(K + 1)]
+    ev[0].record()
+    for k in range(K):
+        fn(); ev[k + 1].record()
+    torch.cuda.synchronize()
+    per = sorted(ev[k].elapsed_time(ev[k + 1]) for k in range(K))
+    return ev[0].elapsed_time(ev[K]) / K, {"median": per[K // 2], "min": per[0], "max": per[-1]}
+
+
+def row_staging(cfg, K, W):
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    from scorp_b200 import model_space as ms
+    sc = synth.make_scene(cfg).to("cuda"); cam = sc.cameras[0]
+    P, M = sc.P, sc.shs.shape[1]
+    op = sc.opacities.clamp(1e-4, 1 - 1e-4)
+    st = dict(xyz=sc.means3D.clone(), features_dc=sc.shs[:, :1].contiguous(), features_rest=sc.shs[:, 1:].contiguous(),
+              opacity=torch.log(op / (1 - op)), scaling=torch.log(sc.scales), rotation=sc.rotations * 1.7)
+    st = {k: v.requires_grad_(True) for k, v in st.items()}
+    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, sc.bg, 1.0, cam.viewmatrix,
+                                           cam.projmatrix, sc.sh_degree, cam.campos, False, False)
+    gr = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 1)]
+
+    def finish(outs):
+        torch.autograd.backward([outs[0], outs[2], outs[3]], gr)
+
+    def stock():
+        for v in st.values():
+            v.grad = None
+        shs = torch.cat((st["features_dc"], st["features_rest"]), dim=1)
+        m2d = torch.zeros_like(st["xyz"], requires_grad=True) + 0
+        finish(dgr.GaussianRasterizer(rs)(means3D=st["xyz"], means2D=m2d, opacities=torch.sigmoid(st["opacity"]),
+                                          shs=shs, scales=torch.exp(st["scaling"]),
+                                          rotations=F.normalize(st["rotation"])))
+
+    def model():
+        for v in st.values():
+            v.grad = None
+        m2d = torch.zeros_like(st["xyz"], requires_grad=True) + 0
+        finish(ms.rasterize_model(st["xyz"], m2d, st["features_dc"], st["features_rest"], st["opacity"], st["scaling"],
+                                  st["rotation"], rs))
+
+    for _ in range(8):
+        stock(); model()
+    t_stock, sp_stock = timeit(stock, K, W)
+    t_model, sp_model = timeit(model, K, W)
+    # traffic the fused form removes: cat (read + write the SH tensor) and its two slice copies in backward, plus
+    # 3 activations fwd (read + write) and their backward kernels (read grad, read saved, write grad)
+    removed = 4 * P * (2 * 3 * M + 2 * 3 * M + 2 * (1 + 3 + 4) + 3 * (1 + 3 + 4))
+    return {"row": "8f-1 staging", "config": cfg, "P": P, "sh_coeffs": M, "unit": "ms per fwd+bwd (autograd, inputs resident)",
+            "stock_torch_staging_ms": t_stock, "model_space_ms": t_model, "speedup": t_stock / t_model,
+            "spread": {"stock": sp_stock, "model": sp_model}, "staging_bytes_removed": removed}
+
+
+def torch_loss(x, b, lam, w):
+    Cn = x.size(-3)
+    conv = lambda t: F.conv2d(t, w, padding=5, groups=Cn)
+    mu1, mu2 = conv(x), conv(b)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = conv(x * x) - mu1_sq; s2 = conv(b * b) - mu2_sq; s12 = conv(x * b) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    m = ((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))
+    return (1.0 - lam) * torch.abs(x - b).mean() + lam * (1.0 - m.mean())
+
+
+def row_loss(cfg, K, W):
+    from scorp_b200 import loss_utils as lu, _lib
+    c = synth.CONFIGS[cfg]
+    Wd, Hd = c["W"], c["H"]
+    gen = torch.Generator().manual_seed(1)
+    a = torch.rand(3, Hd, Wd, generator=gen).cuda().requires_grad_(True)
+    b = torch.rand(3, Hd, Wd, generator=gen).cuda()
+    g = torch.tensor([np.exp(-(x - 5) ** 2 / (2 * 1.5 ** 2)) for x in range(11)], dtype=torch.float32)
+    g = (g / g.sum()).unsqueeze(1)
+    w = g.mm(g.t()).float()[None, None].expand(3, 1, 11, 11).contiguous().cuda()
+    lam = 0.2
+
+    def ref():
+        a.grad = None
+        torch_loss(a, b, lam, w).backward()
+
+    def fused():
+        a.grad = None
+        lu.l1_ssim_loss(a, b, lam).backward()
+
+    for _ in range(8):
+        ref(); fused()
+    t_ref, sp_ref = timeit(ref, K, W)
+    t_fused, sp_fused = timeit(fused, K, W)
+    # kernel-only times of the two fused kernels (C ABI, no autograd / allocation)
+    lib = _lib.lib()
+    n = a.numel()
+    nb = lib.gsr_l1_ssim_workspace_bytes(3, Hd, Wd)
+    ws = torch.empty(nb, dtype=torch.uint8, device="cuda"); out = torch.empty(3, device="cuda"); gi = torch.empty_like(b)
+    ad = a.detach()
+    st = torch.cuda.current_stream().cuda_stream
+    # ping-pong over several image pairs so successive launches do not find their inputs in L2
+    kf, _ = timeit(lambda: lib.gsr_l1_ssim_forward(3, Hd, Wd, ad.data_ptr(), b.data_ptr(), lam, out.data_ptr(), ws.data_ptr(), nb, st), 50, 5)
+    kb, _ = timeit(lambda: lib.gsr_l1_ssim_backward(3, Hd, Wd, ad.data_ptr(), b.data_ptr(), None, 1 - lam, -lam, ws.data_ptr(), gi.data_ptr(), st), 50, 5)
+    pk, src = peak()
+    bytes_f, bytes_b = 4 * n * (2 + 3), 4 * n * (3 + 2 + 1)
+    return {"row": "8f-3 loss", "config": cfg, "image": [3, Hd, Wd], "unit": "ms per loss fwd+bwd (autograd, inputs resident)",
+            "torch_ms": t_ref, "fused_ms": t_fused, "speedup": t_ref / t_fused, "spread": {"torch": sp_ref, "fused": sp_fused},
+            "kernels": {"forward_ms": kf, "backward_ms": kb,
+                        "note": "back-to-back launches on a 78 MB working set (inside the 126 MB L2): L2-warm, as in a training loop where the rasterizer just wrote the image"},
+            "roofline": {"bound": "hbm", "peak": pk, "peak_source": src, "unit": "GB/s",
+                         "forward": {"algorithmic_bytes": bytes_f, "achieved": bytes_f / kf / 1e6, "frac": bytes_f / kf / 1e6 / pk},
+                         "backward": {"algorithmic_bytes": bytes_b, "achieved": bytes_b / kb / 1e6, "frac": bytes_b / kb / 1e6 / pk}}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--config", default="C2")
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--rows", default="staging,loss")
+    args = ap.parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("needs a CUDA device")
+    for r in args.rows.split(","):
+        fn = {"staging": row_staging, "loss": row_loss}[r]
+        print(json.dumps(fn(args.config, args.steps, args.warmup)), flush=True)
+
+
+if __name__ == "__main__":
+    main()
