@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--exchange", choices=["auto", "dense", "factored"], default="auto",
                     help="N>1, ours: dense = one all_reduce over the gradient arena; factored = multiview.FactoredExchange")
     ap.add_argument("--views-per-rank", type=int, default=0, help="views each rank renders per step (0: the config's default)")
+    ap.add_argument("--view-loop", action="store_true",
+                    help="ours, forward-only configs: one forward call per view (the reference's loop) instead of the batched gsr_rasterize_forward_views")
     return ap.parse_args()
 
 
@@ -420,7 +422,17 @@ def run(arm, args, rank, world, local):
     W, H, P, M = cams[0].W, cams[0].H, sc.P, sc.shs.shape[1]
     grads = [[g.to(dev) for g in synth.upstream_grads(W, H, 1 + v, channels=out_channels(surfel))] for v in my_views]
 
+    batched = arm.name == "ours" and fwd_only and not surfel and len(cams) > 1 and not args.view_loop
+    if batched:
+        vm = torch.stack([c.viewmatrix for c in cams]); pm = torch.stack([c.projmatrix for c in cams])
+        cp = torch.stack([c.campos for c in cams])
+
     def step_resident():
+        if batched:     # the whole pose sweep of this rank in one call
+            n, color, depth, alpha, radii = arm.C.rasterize_gaussians_views(
+                sc.bg, sc.means3D, arm.E, sc.opacities, sc.scales, sc.rotations, 1.0, arm.E, vm, pm, cams[0].tanfovx,
+                cams[0].tanfovy, H, W, sc.shs, sc.sh_degree, cp, False, False)
+            return n, radii, None
         last, total = None, None
         for cam, gr in zip(cams, grads):
             n, radii, color, g = arm.fwd_bwd(sc, cam, sc.bg, cam.viewmatrix, cam.projmatrix, cam.campos, gr, fwd_only)
@@ -444,7 +456,7 @@ def run(arm, args, rank, world, local):
         elif arm.name == "reference":
             exchange = "five all_reduce calls (one per gradient tensor)"
     n, radii, _ = step_resident()
-    Pvis = int((radii > 0).sum())
+    Pvis = int((radii > 0).sum())          # batched: radii is [V, P] and n the total, so the stage bytes cover all views
     prime(step_resident, world)
     sampler = ClockSampler(local) if rank == 0 else None
     stages = None
@@ -468,9 +480,23 @@ def run(arm, args, rank, world, local):
     copy_stream = torch.cuda.Stream(dev)
     d_gr_buf = torch.empty_like(h_grads[0], device=dev)
 
+    if batched:
+        h_all = torch.stack(h_cams).pin_memory()
+
     def step_e2e():
         main = torch.cuda.current_stream(dev)
         acc = None
+        if batched:     # one H2D of the V cameras, one forward_views call, one scalar back
+            d = h_all.to(dev, non_blocking=True)
+            rs = arm.mod.GaussianRasterizationSettings(H, W, cams[0].tanfovx, cams[0].tanfovy, d[0, 35:38], 1.0,
+                                                       d[0, 0:16].view(4, 4), d[0, 16:32].view(4, 4), sc.sh_degree,
+                                                       d[0, 32:35], False, False)
+            color, _, _, _ = arm.mod.GaussianRasterizer(rs).forward_views(
+                d[:, 0:16].reshape(-1, 4, 4), d[:, 16:32].reshape(-1, 4, 4), d[:, 32:35], params[0], params[2],
+                shs=params[1], scales=params[3], rotations=params[4])
+            h_out.copy_(color.sum().view(1), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return
         for cam, h_cam, h_gr in zip(cams, h_cams, h_grads):
             d_cam = h_cam.to(dev, non_blocking=True)
             if not fwd_only:
@@ -498,11 +524,11 @@ def run(arm, args, rank, world, local):
     launches = 0
     if arm.name == "ours":
         # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd) (+ clamped colour gradient, SH rebuild)
-        launches = ((4 if fwd_only else 7) + (2 if arm.factored else 0)) * len(cams) * args.steps
+        launches = ((4 if fwd_only else 7) + (2 if arm.factored else 0)) * (1 if batched else len(cams)) * args.steps
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
-                d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats)
+                d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched)
 
 
 def main():
@@ -551,7 +577,9 @@ def main():
     if r["tstats"]:
         line["config"]["tile_lists"] = r["tstats"]
     if args.impl == "ours":
-        sb = stage_bytes(r["P"], r["M"], r["Pvis"], r["N"], W, H, r["surfel"])
+        nv = r["vpr"] if r["batched"] else 1          # a batched call runs every stage once over all of the rank's views
+        sb = stage_bytes(r["P"] * nv, r["M"], r["Pvis"], r["N"], W, H * nv, r["surfel"])
+        line["config"]["views_per_call"] = nv
         stages = []
         for name, ms in zip(STAGES, r["stages"]):
             ms_v = ms if ms and ms > 0 else None

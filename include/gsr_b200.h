@@ -223,6 +223,25 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
                            const float* drgb, float* dL_dsh, void* stream);
 
+/* ---- batched multi-view forward ----------------------------------------
+ * One call renders the SAME Gaussians from V cameras of identical resolution and intrinsics: the pose sweep of
+ * align_3dgs_clpe_9dof.py:146-160 and utils/mask.py:120-122, which the reference runs as a Python loop of V forward
+ * calls (V host synchronisations on num_rendered, 3V allocations). Here the V views go through ONE preprocess launch
+ * (grid.y = view), ONE counting sort over V * tiles tile lists (the view index takes the place of the key's high
+ * bits) and ONE blend launch over V * tiles CTAs, with a single readback.
+ * s->viewmatrix / s->projmatrix / s->campos point to V consecutive matrices / positions ([V*16], [V*16], [V*3]);
+ * tanfov, resolution, bg, scale_modifier and sh_degree are shared. Outputs: out_color[V*3*H*W], out_depth[V*H*W],
+ * out_alpha[V*H*W], radii[V*P]; view v's slice is bit-identical to gsr_rasterize_forward with camera v.
+ * *num_rendered is the total over the views. Forward only: the scratch buffers have the batched layout and are not
+ * accepted by gsr_rasterize_backward. */
+int gsr_rasterize_forward_views(
+    const GsrSettings* s, int V, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations,
+    const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream);
+
 /* ---- photometric loss (the step right after the boundary) ----------------
  * Replaces l1_loss + ssim of gs3dgs/utils/loss_utils.py:17-18,45-73 (five grouped 11x11 F.conv2d calls and ~20
  * elementwise torch kernels per forward, mirrored by autograd) as used by train_3dgs.py:106-107:

@@ -56,6 +56,8 @@ SIGNATURES = {
                                   + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_rasterize_backward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int, C.POINTER(GsrModelParams)]
                                    + [_P] * 5 + [_P] * 3 + [_P, C.POINTER(GsrModelGrads), _P, c_size_t, _P]),
+    "gsr_rasterize_forward_views": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int] + [_P] * 7 + [_P] * 4
+                                    + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_l1_ssim_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_l1_ssim_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, c_size_t, _P]),
     "gsr_l1_ssim_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),

@@ -95,15 +95,16 @@ static int forward_impl(
     const float* means3D, const float* shs, const float* shs_rest, bool raw, const float* colors_precomp,
     const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
     float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
-    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, int views = 1)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
+    if (views < 1 || (long long)views * P > 0x7fffffffLL) { set_error("bad view count %d for P=%d", views, P); return GSR_EINVAL; }
     *num_rendered = 0;
     const int W = s->image_width, H = s->image_height;
     if (P < 0 || W <= 0 || H <= 0) { set_error("bad sizes P=%d W=%d H=%d", P, W, H); return GSR_EINVAL; }
     if (!out_color || !out_depth || !out_alpha) { set_error("null output image"); return GSR_EINVAL; }
-    const size_t hw = (size_t)W * H;
+    const size_t hw = (size_t)W * H * views;
     int rc;
     if (P == 0) {   // rasterize_points.cu:83: zero outputs, nothing else
         if ((rc = check_cuda(cudaMemsetAsync(out_color, 0, 3 * hw * 4, st), "memset color"))) return rc;
@@ -120,14 +121,15 @@ static int forward_impl(
     if (shs && (!sh_count_ok(M) || M == 0 || (s->sh_degree + 1) * (s->sh_degree + 1) > M || s->sh_degree < 0 || s->sh_degree > 3)) {
         set_error("unsupported SH layout: M=%d degree=%d", M, s->sh_degree); return GSR_EUNSUPPORTED;
     }
-    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, tiles = gx * gy;
+    const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE, tiles = gx * gy * views;
+    const int PV = P * views;          // records: view v owns [v*P, (v+1)*P)
 
     GeomState g; ImageState img; BinningState bin;
-    char* gbase = (char*)alloc(alloc_user, GSR_BUF_GEOM, carve_geom(nullptr, P, tiles, nullptr));
-    char* ibase = (char*)alloc(alloc_user, GSR_BUF_IMAGE, carve_image(nullptr, W, H, nullptr));
+    char* gbase = (char*)alloc(alloc_user, GSR_BUF_GEOM, carve_geom(nullptr, PV, tiles, nullptr));
+    char* ibase = (char*)alloc(alloc_user, GSR_BUF_IMAGE, carve_image(nullptr, W, H, nullptr, nullptr, views));
     if (!gbase || !ibase) { set_error("allocator returned NULL"); return GSR_EALLOC; }
-    carve_geom(gbase, P, tiles, &g);
-    carve_image(ibase, W, H, &img);
+    carve_geom(gbase, PV, tiles, &g);
+    carve_image(ibase, W, H, &img, nullptr, views);
 
     // tile_count and counters are adjacent at the end of the geometry buffer: one memset
     const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + 16;
@@ -144,29 +146,29 @@ static int forward_impl(
     a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos; a.bg = s->bg;
     a.prefiltered = s->prefiltered != 0;
     a.shs_rest = shs_rest; a.raw = raw;
-    if ((rc = check_cuda(launch_preprocess(a, g, radii, st), "preprocess launch"))) return rc;
+    if ((rc = check_cuda(launch_preprocess(a, g, radii, st, views), "preprocess launch"))) return rc;
     if ((rc = stage_check(s, st, "preprocess"))) return rc;
     prof_mark(1, st);
 
     // number of instances -> host (the one blocking point, as rasterizer_impl.cu:282)
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
-    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
+    if ((rc = check_cuda(launch_tile_scan(tiles, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
     uint32_t n_host[2] = {0, 0};
     if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
     const int N = (int)n_host[0], max_len = (int)n_host[1];
     *num_rendered = N;
 
-    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, gx * gy));
+    char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, tiles));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
-    carve_binning(bbase, N, &bin, nullptr, gx * gy);
+    carve_binning(bbase, N, &bin, nullptr, tiles);
 
-    if ((rc = check_cuda(launch_binning(P, gx, gy, N, max_len, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st), "binning launch"))) return rc;
+    if ((rc = check_cuda(launch_binning(PV, gx, gy, N, max_len, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st, views), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
-    if ((rc = check_cuda(cudaMemsetAsync(bin.contrib, 0, contrib_slots(N, gx * gy) * sizeof(uint4), st), "memset contribution masks"))) return rc;
-    if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st),
+    if ((rc = check_cuda(cudaMemsetAsync(bin.contrib, 0, contrib_slots(N, tiles) * sizeof(uint4), st), "memset contribution masks"))) return rc;
+    if ((rc = check_cuda(launch_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_depth, out_alpha, st, views),
                          "render forward launch"))) return rc;
     prof_mark(3, st);
     return stage_check(s, st, "render forward");
@@ -195,6 +197,17 @@ int gsr_rasterize_forward_raw(
     if (M < 1) { set_error("model-space entry needs SH coefficients (M >= 1)"); return GSR_EUNSUPPORTED; }
     return forward_impl(s, P, M, mp->xyz, mp->features_dc, mp->features_rest, true, nullptr, mp->opacity, mp->scaling,
                         mp->rotation, nullptr, out_color, out_depth, out_alpha, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+int gsr_rasterize_forward_views(
+    const GsrSettings* s, int V, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    return forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                        out_color, out_depth, out_alpha, radii, alloc, alloc_user, num_rendered, stream, V);
 }
 
 struct RawBwd { const float* shs_rest; const float* opacities; float* dL_dsh_rest; };

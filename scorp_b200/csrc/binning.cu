@@ -88,12 +88,13 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
 constexpr uint32_t SMALL_RECT = 4;
 
 __global__ void __launch_bounds__(256)
-scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
+scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
                const int32_t* __restrict__ radii,
                uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, w = 0, cnt = 0;
+    uint32_t tbase = 0;                       // first tile of this record's view (0 for a single view)
     uint64_t key = 0;
     if (idx < P) {
         const int rad = radii[idx];
@@ -107,6 +108,7 @@ scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_str
             w = x1 - x0;
             cnt = w * (y1 - y0);
             key = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
+            tbase = (uint32_t)(idx / per_view) * (uint32_t)(gx * gy);
         }
     }
     auto put = [&](uint32_t t, uint64_t k) {
@@ -119,7 +121,7 @@ scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_str
 #pragma unroll
         for (uint32_t i = 0; i < SMALL_RECT; ++i) {
             if (i < cnt) {
-                t[i] = (y0 + i / w) * gx + x0 + i % w;
+                t[i] = tbase + (y0 + i / w) * gx + x0 + i % w;
                 at[i] = __ldg(&ranges[t[i]].x) + atomicSub(tile_count + t[i], 1u) - 1u;
             }
         }
@@ -134,7 +136,8 @@ scatter_kernel(int P, int gx, int gy, const char* __restrict__ recs, int rec_str
         const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
         const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
         const uint64_t bkey = __shfl_sync(0xffffffffu, key, src);
-        for (uint32_t i = lane; i < bcnt; i += 32) put((by0 + i / bw) * gx + bx0 + i % bw, bkey);
+        const uint32_t bt = __shfl_sync(0xffffffffu, tbase, src);
+        for (uint32_t i = lane; i < bcnt; i += 32) put(bt + (by0 + i / bw) * gx + bx0 + i % bw, bkey);
     }
 }
 
@@ -339,10 +342,10 @@ cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* range
 
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
-                           cudaStream_t st) {
-    const int tiles = gx * gy;
+                           cudaStream_t st, int views) {
+    const int tiles = gx * gy * views;
     if (N <= 0) return cudaSuccess;
-    scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
+    scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
                                                     tile_count, ranges, bin.scratch);
     tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
         0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);

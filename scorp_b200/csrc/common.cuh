@@ -73,11 +73,11 @@ inline size_t carve_geom(char* base, int P, int tiles, GeomState* g, size_t* off
     }
     return o;
 }
-inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off = nullptr) {
-    int tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off = nullptr, int views = 1) {
+    int tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE) * views;
     size_t o = 0;
     size_t a0 = o; o = align_up(o + (size_t)tiles * sizeof(uint2));
-    size_t a1 = o; o = align_up(o + (size_t)W * H * 4);
+    size_t a1 = o; o = align_up(o + (size_t)W * H * 4 * views);
     size_t a2 = o; o = align_up(o + (size_t)tiles * 4);
     if (off) { off[0] = a0; off[1] = a1; }
     if (s) { s->ranges = (uint2*)(base + a0); s->n_contrib = (uint32_t*)(base + a1); s->tile_order = (uint32_t*)(base + a2); }
@@ -198,16 +198,18 @@ struct FwdArgs {
     const float* shs_rest = nullptr;
     bool raw = false;
 };
-cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st);
+cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views = 1);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, uint32_t* order,
                              cudaStream_t st);
+// views > 1: P is the TOTAL record count (views * Gaussians), record v*Pv + i belongs to view v and its tiles are
+// numbered v * gx*gy + local tile
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
-                           cudaStream_t st);
+                           cudaStream_t st, int views = 1);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
-                                  float* out_color, float* out_depth, float* out_alpha, cudaStream_t st);
+                                  float* out_color, float* out_depth, float* out_alpha, cudaStream_t st, int views = 1);
 cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                    const BinningState& bin, const float* bg, const float* out_alpha,
                                    const float* dL_dpix, const float* dL_ddepth, const float* dL_dalpha,

@@ -75,6 +75,15 @@ template <bool VEC, bool RAW>
 __global__ void __launch_bounds__(256, 4)
 preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
+    // batched views (gsr_rasterize_forward_views): blockIdx.y = view; its camera, its P records and its tile counters.
+    // A single-view launch has gridDim.y == 1 and shifts nothing.
+    const int view_id = blockIdx.y;
+    if (view_id) {
+        a.view += 16 * view_id; a.proj += 16 * view_id; a.campos += 3 * view_id;
+        g.rec += (size_t)view_id * a.P; g.clamped += (size_t)view_id * a.P; g.tiles_touched += (size_t)view_id * a.P;
+        g.tile_count += (size_t)view_id * a.gx * a.gy;
+        radii += (size_t)view_id * a.P;
+    }
     uint32_t tiles = 0, rx0 = 0, ry0 = 0, rw = 0;
     if (idx < a.P) {
         int my_radius = 0;
@@ -102,8 +111,10 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
                 float sx = __ldg(a.scales + 3 * idx), sy = __ldg(a.scales + 3 * idx + 1), sz = __ldg(a.scales + 3 * idx + 2);
                 if constexpr (RAW) { q = act_rotation(q); sx = act_scale(sx); sy = act_scale(sy); sz = act_scale(sz); }
                 cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q.x, q.y, q.z, q.w, c3);
+                if (view_id == 0) {      // the same for every view
 #pragma unroll
-                for (int k = 0; k < 6; ++k) g.cov3D[6 * idx + k] = c3[k];
+                    for (int k = 0; k < 6; ++k) g.cov3D[6 * idx + k] = c3[k];
+                }
             }
             const float tx = xform_row(a.view, 0, px, py, pz), ty = xform_row(a.view, 1, px, py, pz);
             const float3 cov = cov2d_from_cov3d(tx, ty, depth, a.focal_x, a.focal_y, a.tanfovx, a.tanfovy, c3, a.view);
@@ -167,8 +178,8 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);
 }
 
-cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st) {
-    const int blocks = (a.P + 255) / 256;
+cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views) {
+    const dim3 blocks((a.P + 255) / 256, views);
     const bool vec = a.shs && a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
     if (a.raw)    preprocess_kernel<false, true><<<blocks, 256, 0, st>>>(a, g, radii);
     else if (vec) preprocess_kernel<true, false><<<blocks, 256, 0, st>>>(a, g, radii);

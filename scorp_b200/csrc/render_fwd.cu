@@ -17,7 +17,7 @@ namespace gsr {
 constexpr int FWD_THREADS = BLEND_THREADS;
 
 __global__ void __launch_bounds__(FWD_THREADS, 8)
-render_forward_kernel(int W, int H, int gx,
+render_forward_kernel(int W, int H, int gx, int tiles_per_view,
                       const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                       const GaussRec* __restrict__ recs, const float* __restrict__ bg,
                       uint32_t* __restrict__ n_contrib, float* __restrict__ out_color,
@@ -26,7 +26,13 @@ render_forward_kernel(int W, int H, int gx,
     __shared__ uint32_t s_bal[4][8];          // [consumer warp block][32-record word of the round]
 
     const int tile = (int)tile_order[blockIdx.x];      // longest lists first (binning.cu)
-    const int tile_x = (tile % gx) * TILE, tile_y = (tile / gx) * TILE;
+    // batched views: tile = view * tiles_per_view + local tile; every per-pixel output of view v starts v images in
+    const int view_id = tile / tiles_per_view, ltile = tile - view_id * tiles_per_view;
+    const int tile_x = (ltile % gx) * TILE, tile_y = (ltile / gx) * TILE;
+    if (view_id) {
+        const size_t vo = (size_t)view_id * H * W;
+        n_contrib += vo; out_color += 3 * vo; out_depth += vo; out_alpha += vo;
+    }
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int bx = (wid & 1) * 8, by = (wid >> 1) * 8;
     const int pxi = tile_x + bx + (lane & 7), pyi = tile_y + by + 2 * (lane >> 3);     // pixels (pxi, pyi) and (pxi, pyi+1)
@@ -166,8 +172,8 @@ render_forward_kernel(int W, int H, int gx,
 
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
-                                  float* out_color, float* out_depth, float* out_alpha, cudaStream_t st) {
-    render_forward_kernel<<<gx * gy, FWD_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
+                                  float* out_color, float* out_depth, float* out_alpha, cudaStream_t st, int views) {
+    render_forward_kernel<<<gx * gy * views, FWD_THREADS, 0, st>>>(W, H, gx, gx * gy, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                    img.n_contrib, out_color, out_depth, out_alpha,
                                                            reinterpret_cast<uint32_t*>(bin.contrib));
     return cudaGetLastError();

@@ -134,6 +134,49 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             arena.get(_lib.GSR_BUF_GEOM), arena.get(_lib.GSR_BUF_BINNING), arena.get(_lib.GSR_BUF_IMAGE))
 
 
+def rasterize_gaussians_views(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                              viewmatrices, projmatrices, tan_fovx, tan_fovy, image_height, image_width, sh, degree,
+                              camposes, prefiltered, debug):
+    """Batched forward (no reference counterpart; include/gsr_b200.h gsr_rasterize_forward_views): same arguments as
+    rasterize_gaussians with viewmatrices[V,4,4], projmatrices[V,4,4], camposes[V,3].
+    -> (num_rendered, color[V,3,H,W], depth[V,1,H,W], alpha[V,1,H,W], radii[V,P]); forward only."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise _lib.GsrError("means3D must be a CUDA tensor: this rasterizer has no CPU path")
+    if viewmatrices.dim() != 3 or viewmatrices.shape[1:] != (4, 4) or projmatrices.shape != viewmatrices.shape \
+            or camposes.shape != (viewmatrices.size(0), 3):
+        raise RuntimeError("expected viewmatrices[V,4,4], projmatrices[V,4,4], camposes[V,3]")
+    lib = _lib.lib()
+    dev = means3D.device
+    V, P, H, W = viewmatrices.size(0), means3D.size(0), int(image_height), int(image_width)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    means3D = _f32c(means3D, dev); colors = _f32c(colors, dev); opacity = _f32c(opacity, dev)
+    scales = _f32c(scales, dev); rotations = _f32c(rotations, dev); cov3D_precomp = _f32c(cov3D_precomp, dev)
+    sh = _f32c(sh, dev)
+    background = _f32c(background, dev); viewmatrices = _f32c(viewmatrices, dev)
+    projmatrices = _f32c(projmatrices, dev); camposes = _f32c(camposes, dev)
+    out_color = torch.empty((V, 3, H, W), dtype=torch.float32, device=dev)
+    out_depth = torch.empty((V, 1, H, W), dtype=torch.float32, device=dev)
+    out_alpha = torch.empty((V, 1, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((V, P), dtype=torch.int32, device=dev)
+    if V == 0:
+        return 0, out_color, out_depth, out_alpha, radii
+    arena = _Arena(dev)
+    s = _settings(background, viewmatrices, projmatrices, camposes, tan_fovx, tan_fovy, H, W, scale_modifier, degree,
+                  prefiltered, debug)
+    n = C.c_int(0)
+    with torch.cuda.device(dev):
+        rc = lib.gsr_rasterize_forward_views(
+            C.byref(s), V, P, M, ptr(means3D), ptr(sh), ptr(colors), ptr(opacity), ptr(scales), ptr(rotations),
+            ptr(cov3D_precomp), out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(), ptr(radii),
+            arena.fn, None, C.byref(n), _stream(dev))
+    if arena.error is not None:
+        raise arena.error
+    _lib.check(rc, "gsr_rasterize_forward_views")
+    return n.value, out_color, out_depth, out_alpha, radii
+
+
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,

@@ -110,6 +110,30 @@ class GaussianRasterizer(nn.Module):
             rs = self.raster_settings
             return _C.mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
+    def forward_views(self, viewmatrices, projmatrices, camposes, means3D, opacities, shs=None, colors_precomp=None,
+                      scales=None, rotations=None, cov3D_precomp=None):
+        """Extension (no reference counterpart): render the same Gaussians from V cameras of this rasterizer's
+        resolution / field of view in ONE call -- the pose sweeps of align_3dgs_clpe_9dof.py:146-160 and
+        utils/mask.py:120-122, which loop over forward(). viewmatrices[V,4,4], projmatrices[V,4,4], camposes[V,3]
+        replace the three camera fields of raster_settings. Forward only (runs under no_grad).
+        -> (color[V,3,H,W], radii[V,P], depth[V,1,H,W], alpha[V,1,H,W]); slice v equals forward() with camera v."""
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        have_sr = scales is not None and rotations is not None
+        any_sr = scales is not None or rotations is not None
+        if (not have_sr and cov3D_precomp is None) or (any_sr and cov3D_precomp is not None):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        rs = self.raster_settings
+        empty = torch.Tensor([])
+        with torch.no_grad():
+            _, color, depth, alpha, radii = _C.rasterize_gaussians_views(
+                rs.bg, means3D, empty if colors_precomp is None else colors_precomp, opacities,
+                empty if scales is None else scales, empty if rotations is None else rotations, rs.scale_modifier,
+                empty if cov3D_precomp is None else cov3D_precomp, viewmatrices, projmatrices, rs.tanfovx, rs.tanfovy,
+                rs.image_height, rs.image_width, empty if shs is None else shs, rs.sh_degree, camposes,
+                rs.prefiltered, rs.debug)
+        return color, radii, depth, alpha
+
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
                 rotations=None, cov3D_precomp=None):
         if (shs is None) == (colors_precomp is None):
