@@ -8,7 +8,8 @@
 //   l1_ssim_forward_kernel   reads image and gt once, writes the three per-pixel partial derivatives of the SSIM map
 //                            (w.r.t. mu1, E[x^2], E[xy]) and per-CTA partial sums of |x - y| and of the SSIM map
 //   l1_ssim_backward_kernel  convolves the three derivative maps with the same window and adds the L1 sign term
-// Both are separable (11 + 11 taps instead of 121) over a shared-memory tile with a 5-pixel zero-padded halo, exactly
+// Both are separable (11 + 11 taps instead of 121) over a 32x32 shared-memory tile with a 5-pixel zero-padded halo;
+// a thread produces four neighbouring outputs per pass from a 14-element sliding window held in registers. The halo is exactly
 // the zero padding of F.conv2d(padding = 5). The reduction is deterministic: per-CTA partials, then one CTA sums them
 // in double in a fixed order.
 #include "common.cuh"
@@ -17,8 +18,11 @@
 namespace gsr {
 
 constexpr int LW = 11, LR = 5;                 // window size, radius (loss_utils.py:45 window_size = 11)
-constexpr int LTX = 32, LTY = 8;               // output tile per CTA (one thread per pixel)
+constexpr int LTX = 32, LTY = 32;              // output tile per CTA
+constexpr int LV = 4;                          // outputs per thread: 4 along x in the horizontal pass, 4 along y in the vertical
+constexpr int LTHREADS = LTX * LTY / LV;       // 256
 constexpr int LHX = LTX + 2 * LR, LHY = LTY + 2 * LR;
+constexpr int LSPAN = LV + LW - 1;             // inputs a thread reads for its LV outputs (sliding window)
 constexpr float SSIM_C1 = 0.01f * 0.01f, SSIM_C2 = 0.03f * 0.03f;      // loss_utils.py:67-68
 
 struct LossWindow { float g[LW]; };
@@ -45,25 +49,38 @@ __device__ __forceinline__ float block_sum(float v, float* s_red) {
     __syncthreads();
     float t = 0.0f;
     if (warp == 0) {
-        t = lane < (LTX * LTY / 32) ? s_red[lane] : 0.0f;
+        t = lane < (LTHREADS / 32) ? s_red[lane] : 0.0f;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
     }
     return t;       // valid in thread 0
 }
 
-__global__ void __launch_bounds__(LTX * LTY)
+// LV sliding-window sums of one quantity: out[j] = sum_k g[k] * v[j + k], taps in the order k = 0..10
+__device__ __forceinline__ void window4(const LossWindow& win, const float (&v)[LSPAN], float (&out)[LV]) {
+#pragma unroll
+    for (int j = 0; j < LV; ++j) out[j] = 0.0f;
+#pragma unroll
+    for (int k = 0; k < LW; ++k)
+#pragma unroll
+        for (int j = 0; j < LV; ++j) out[j] = fmaf(win.g[k], v[j + k], out[j]);
+}
+
+// Shared-memory layout: halo rows have an odd stride (LHX + 1 = 43) and the horizontally filtered rows a stride of
+// LTX + 1 = 33, which makes every access pattern below bank-conflict free: the horizontal pass maps a warp to
+// 4 rows x 8 groups of 4 columns, the vertical pass to 32 consecutive columns.
+__global__ void __launch_bounds__(LTHREADS)
 l1_ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, LossWindow win,
                        float* __restrict__ dm_dmu1, float* __restrict__ dm_dsig1, float* __restrict__ dm_dsig12,
                        float* __restrict__ partial) {
     __shared__ float s_x[LHY][LHX + 1], s_y[LHY][LHX + 1];
     __shared__ float s_h[5][LHY][LTX + 1];
-    __shared__ float s_red[LTX * LTY / 32];
+    __shared__ float s_red[LTHREADS / 32];
     const int c = blockIdx.z;
     const int x0 = blockIdx.x * LTX, y0 = blockIdx.y * LTY;
     const size_t plane = (size_t)c * H * W;
     const int tid = threadIdx.x;
-    for (int e = tid; e < LHY * LHX; e += LTX * LTY) {
+    for (int e = tid; e < LHY * LHX; e += LTHREADS) {
         const int r = e / LHX, q = e - r * LHX;
         const int gy = y0 + r - LR, gx = x0 + q - LR;
         const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
@@ -71,47 +88,69 @@ l1_ssim_forward_kernel(int H, int W, const float* __restrict__ img, const float*
         s_y[r][q] = in ? __ldg(gt + plane + (size_t)gy * W + gx) : 0.0f;
     }
     __syncthreads();
-    for (int e = tid; e < LHY * LTX; e += LTX * LTY) {     // horizontal pass over all halo rows
-        const int r = e / LTX, q = e - r * LTX;
-        float a = 0.f, b = 0.f, aa = 0.f, bb = 0.f, ab = 0.f;
+    for (int it = tid; it < LHY * (LTX / LV); it += LTHREADS) {     // horizontal pass over all halo rows
+        const int r = it / (LTX / LV), c0 = (it - r * (LTX / LV)) * LV;
+        float xv[LSPAN], yv[LSPAN], t[LSPAN], o[LV];
 #pragma unroll
-        for (int k = 0; k < LW; ++k) {
-            const float w = win.g[k], x = s_x[r][q + k], y = s_y[r][q + k];
-            a = fmaf(w, x, a); b = fmaf(w, y, b);
-            aa = fmaf(w, x * x, aa); bb = fmaf(w, y * y, bb); ab = fmaf(w, x * y, ab);
-        }
-        s_h[0][r][q] = a; s_h[1][r][q] = b; s_h[2][r][q] = aa; s_h[3][r][q] = bb; s_h[4][r][q] = ab;
+        for (int i = 0; i < LSPAN; ++i) { xv[i] = s_x[r][c0 + i]; yv[i] = s_y[r][c0 + i]; }
+        window4(win, xv, o);
+#pragma unroll
+        for (int j = 0; j < LV; ++j) s_h[0][r][c0 + j] = o[j];
+        window4(win, yv, o);
+#pragma unroll
+        for (int j = 0; j < LV; ++j) s_h[1][r][c0 + j] = o[j];
+#pragma unroll
+        for (int i = 0; i < LSPAN; ++i) t[i] = xv[i] * xv[i];
+        window4(win, t, o);
+#pragma unroll
+        for (int j = 0; j < LV; ++j) s_h[2][r][c0 + j] = o[j];
+#pragma unroll
+        for (int i = 0; i < LSPAN; ++i) t[i] = yv[i] * yv[i];
+        window4(win, t, o);
+#pragma unroll
+        for (int j = 0; j < LV; ++j) s_h[3][r][c0 + j] = o[j];
+#pragma unroll
+        for (int i = 0; i < LSPAN; ++i) t[i] = xv[i] * yv[i];
+        window4(win, t, o);
+#pragma unroll
+        for (int j = 0; j < LV; ++j) s_h[4][r][c0 + j] = o[j];
     }
     __syncthreads();
-    const int tx = tid % LTX, ty = tid / LTX;
-    const int px = x0 + tx, py = y0 + ty;
-    float l1 = 0.0f, sm = 0.0f;
-    if (px < W && py < H) {
-        float mu1 = 0.f, mu2 = 0.f, e11 = 0.f, e22 = 0.f, e12 = 0.f;
+    const int tx = tid % LTX, ty0 = (tid / LTX) * LV;
+    const int px = x0 + tx;
+    float f[5][LV];
 #pragma unroll
-        for (int k = 0; k < LW; ++k) {
-            const float w = win.g[k];
-            mu1 = fmaf(w, s_h[0][ty + k][tx], mu1); mu2 = fmaf(w, s_h[1][ty + k][tx], mu2);
-            e11 = fmaf(w, s_h[2][ty + k][tx], e11); e22 = fmaf(w, s_h[3][ty + k][tx], e22);
-            e12 = fmaf(w, s_h[4][ty + k][tx], e12);
+    for (int q = 0; q < 5; ++q) {
+        float col[LSPAN];
+#pragma unroll
+        for (int i = 0; i < LSPAN; ++i) col[i] = s_h[q][ty0 + i][tx];
+        window4(win, col, f[q]);
+    }
+    float l1 = 0.0f, sm_sum = 0.0f;
+#pragma unroll
+    for (int j = 0; j < LV; ++j) {
+        const int py = y0 + ty0 + j;
+        if (px < W && py < H) {
+            const float mu1 = f[0][j], mu2 = f[1][j], e11 = f[2][j], e22 = f[3][j], e12 = f[4][j];
+            // loss_utils.py:59-70
+            const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
+            const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
+            const float A = 2.0f * mu1_mu2 + SSIM_C1, B = 2.0f * sigma12 + SSIM_C2;
+            const float Cc = mu1_sq + mu2_sq + SSIM_C1, D = sigma1_sq + sigma2_sq + SSIM_C2;
+            const float inv_cd = 1.0f / (Cc * D);
+            const float sm = A * B * inv_cd;
+            // partial derivatives of the map w.r.t. the three windowed sums that depend on img1:
+            //   mu1 (also inside sigma1_sq = E11 - mu1^2 and sigma12 = E12 - mu1 mu2), E11, E12
+            const size_t o = plane + (size_t)py * W + px;
+            dm_dmu1[o] = 2.0f * inv_cd * (mu2 * (B - A) - mu1 * sm * (D - Cc));
+            dm_dsig1[o] = -sm / D;
+            dm_dsig12[o] = 2.0f * A * inv_cd;
+            sm_sum += sm;
+            l1 += fabsf(s_x[ty0 + j + LR][tx + LR] - s_y[ty0 + j + LR][tx + LR]);
         }
-        // loss_utils.py:59-70
-        const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu1_mu2 = mu1 * mu2;
-        const float sigma1_sq = e11 - mu1_sq, sigma2_sq = e22 - mu2_sq, sigma12 = e12 - mu1_mu2;
-        const float A = 2.0f * mu1_mu2 + SSIM_C1, B = 2.0f * sigma12 + SSIM_C2;
-        const float Cc = mu1_sq + mu2_sq + SSIM_C1, D = sigma1_sq + sigma2_sq + SSIM_C2;
-        const float inv_cd = 1.0f / (Cc * D);
-        sm = A * B * inv_cd;
-        // partial derivatives of the map w.r.t. the three windowed sums that depend on img1:
-        //   mu1 (also inside sigma1_sq = E11 - mu1^2 and sigma12 = E12 - mu1 mu2), E11, E12
-        const size_t o = plane + (size_t)py * W + px;
-        dm_dmu1[o] = 2.0f * inv_cd * (mu2 * (B - A) - mu1 * sm * (D - Cc));
-        dm_dsig1[o] = -sm / D;
-        dm_dsig12[o] = 2.0f * A * inv_cd;
-        l1 = fabsf(s_x[ty + LR][tx + LR] - s_y[ty + LR][tx + LR]);
     }
     const float t1 = block_sum(l1, s_red);
-    const float t2 = block_sum(sm, s_red);
+    const float t2 = block_sum(sm_sum, s_red);
     if (tid == 0) {
         const size_t b = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
         partial[2 * b] = t1; partial[2 * b + 1] = t2;
@@ -137,7 +176,7 @@ l1_ssim_finalize_kernel(int nblocks, double inv_n, float lambda, const float* __
     }
 }
 
-__global__ void __launch_bounds__(LTX * LTY)
+__global__ void __launch_bounds__(LTHREADS)
 l1_ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float* __restrict__ gt, LossWindow win,
                         const float* __restrict__ dm_dmu1, const float* __restrict__ dm_dsig1,
                         const float* __restrict__ dm_dsig12, const float* __restrict__ upstream,
@@ -148,7 +187,7 @@ l1_ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float
     const int x0 = blockIdx.x * LTX, y0 = blockIdx.y * LTY;
     const size_t plane = (size_t)c * H * W;
     const int tid = threadIdx.x;
-    for (int e = tid; e < LHY * LHX; e += LTX * LTY) {
+    for (int e = tid; e < LHY * LHX; e += LTHREADS) {
         const int r = e / LHX, q = e - r * LHX;
         const int gy = y0 + r - LR, gx = x0 + q - LR;
         const bool in = gy >= 0 && gy < H && gx >= 0 && gx < W;
@@ -158,33 +197,42 @@ l1_ssim_backward_kernel(int H, int W, const float* __restrict__ img, const float
         s_m[2][r][q] = in ? __ldg(dm_dsig12 + o) : 0.0f;
     }
     __syncthreads();
-    for (int e = tid; e < LHY * LTX; e += LTX * LTY) {
-        const int r = e / LTX, q = e - r * LTX;
-        float a = 0.f, b = 0.f, d = 0.f;
+    for (int it = tid; it < LHY * (LTX / LV); it += LTHREADS) {
+        const int r = it / (LTX / LV), c0 = (it - r * (LTX / LV)) * LV;
 #pragma unroll
-        for (int k = 0; k < LW; ++k) {
-            const float w = win.g[k];
-            a = fmaf(w, s_m[0][r][q + k], a); b = fmaf(w, s_m[1][r][q + k], b); d = fmaf(w, s_m[2][r][q + k], d);
+        for (int q = 0; q < 3; ++q) {
+            float v[LSPAN], o[LV];
+#pragma unroll
+            for (int i = 0; i < LSPAN; ++i) v[i] = s_m[q][r][c0 + i];
+            window4(win, v, o);
+#pragma unroll
+            for (int j = 0; j < LV; ++j) s_h[q][r][c0 + j] = o[j];
         }
-        s_h[0][r][q] = a; s_h[1][r][q] = b; s_h[2][r][q] = d;
     }
     __syncthreads();
-    const int tx = tid % LTX, ty = tid / LTX;
-    const int px = x0 + tx, py = y0 + ty;
-    if (px >= W || py >= H) return;
-    float a = 0.f, b = 0.f, d = 0.f;
+    const int tx = tid % LTX, ty0 = (tid / LTX) * LV;
+    const int px = x0 + tx;
+    float f[3][LV];
 #pragma unroll
-    for (int k = 0; k < LW; ++k) {
-        const float w = win.g[k];
-        a = fmaf(w, s_h[0][ty + k][tx], a); b = fmaf(w, s_h[1][ty + k][tx], b); d = fmaf(w, s_h[2][ty + k][tx], d);
+    for (int q = 0; q < 3; ++q) {
+        float col[LSPAN];
+#pragma unroll
+        for (int i = 0; i < LSPAN; ++i) col[i] = s_h[q][ty0 + i][tx];
+        window4(win, col, f[q]);
     }
-    const size_t o = plane + (size_t)py * W + px;
-    const float x = __ldg(img + o), y = __ldg(gt + o);
-    const float dssim = a + 2.0f * x * b + y * d;                         // d mean-free SSIM map sum / d img[o]
-    const float diff = x - y;
-    const float dl1 = (diff > 0.0f) ? 1.0f : ((diff < 0.0f) ? -1.0f : 0.0f);    // torch.abs backward: sign, 0 at 0
     const float up = upstream ? __ldg(upstream) : 1.0f;
-    dL_dimg[o] = up * inv_n * (w_l1 * dl1 + w_ssim * dssim);
+#pragma unroll
+    for (int j = 0; j < LV; ++j) {
+        const int py = y0 + ty0 + j;
+        if (px < W && py < H) {
+            const size_t o = plane + (size_t)py * W + px;
+            const float x = __ldg(img + o), y = __ldg(gt + o);
+            const float dssim = f[0][j] + 2.0f * x * f[1][j] + y * f[2][j];       // d (sum of the SSIM map) / d img[o]
+            const float diff = x - y;
+            const float dl1 = (diff > 0.0f) ? 1.0f : ((diff < 0.0f) ? -1.0f : 0.0f);    // torch.abs backward: sign, 0 at 0
+            dL_dimg[o] = up * inv_n * (w_l1 * dl1 + w_ssim * dssim);
+        }
+    }
 }
 
 static size_t loss_blocks(int C, int H, int W) {
@@ -217,7 +265,7 @@ int gsr_l1_ssim_forward(int C, int H, int W, const float* img, const float* gt, 
     float* partial = (float*)(base + 3 * stride);
     const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
     if (grid.y > 65535) { set_error("image too tall"); return GSR_EUNSUPPORTED; }
-    l1_ssim_forward_kernel<<<grid, LTX * LTY, 0, st>>>(H, W, img, gt, win, m0, m1, m2, partial);
+    l1_ssim_forward_kernel<<<grid, LTHREADS, 0, st>>>(H, W, img, gt, win, m0, m1, m2, partial);
     int rc;
     if ((rc = check_cuda(cudaGetLastError(), "l1_ssim forward launch"))) return rc;
     l1_ssim_finalize_kernel<<<1, 256, 0, st>>>((int)loss_blocks(C, H, W), 1.0 / (double)n, lambda_dssim, partial, out3);
@@ -235,7 +283,7 @@ int gsr_l1_ssim_backward(int C, int H, int W, const float* img, const float* gt,
     const char* base = (const char*)workspace;
     const dim3 grid((W + LTX - 1) / LTX, (H + LTY - 1) / LTY, C);
     if (grid.y > 65535) { set_error("image too tall"); return GSR_EUNSUPPORTED; }
-    l1_ssim_backward_kernel<<<grid, LTX * LTY, 0, st>>>(H, W, img, gt, win, (const float*)base, (const float*)(base + stride),
+    l1_ssim_backward_kernel<<<grid, LTHREADS, 0, st>>>(H, W, img, gt, win, (const float*)base, (const float*)(base + stride),
                                                         (const float*)(base + 2 * stride), upstream, w_l1, w_ssim,
                                                         (float)(1.0 / (double)n), dL_dimg);
     return check_cuda(cudaGetLastError(), "l1_ssim backward launch");
