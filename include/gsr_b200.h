@@ -258,6 +258,28 @@ int gsr_l1_ssim_forward(int C, int H, int W, const float* img, const float* gt, 
 int gsr_l1_ssim_backward(int C, int H, int W, const float* img, const float* gt, const float* upstream,
                          float w_l1, float w_ssim, const void* workspace, float* dL_dimg, void* stream);
 
+/* ---- optimizer step and densification statistics ------------------------
+ * gsr_adam_step replaces gaussians.optimizer.step() -- torch.optim.Adam(l, lr=0.0, eps=1e-15) over the six parameter
+ * groups (gs3dgs/scene/gaussian_model.py:192-206, train_3dgs.py:192), i.e. torch's seven-pass multi-tensor update --
+ * with one launch over all groups: param, exp_avg, exp_avg_sq updated in place from grad, bit-identical to torch
+ * (amsgrad, weight_decay and maximize are off in the reference and not built). `groups` is a HOST array of at most 8
+ * entries; n = number of floats; lr per group; step = the 1-based step count after the increment, as torch uses it. */
+typedef struct GsrAdamGroup {
+    float*       param;
+    const float* grad;
+    float*       exp_avg;
+    float*       exp_avg_sq;
+    int64_t      n;
+    double       lr;
+} GsrAdamGroup;
+int gsr_adam_step(int n_groups, const GsrAdamGroup* groups, double beta1, double beta2, double eps, int step, void* stream);
+/* For every Gaussian with radii > 0 (train_3dgs.py:180-181, gaussian_model.py:603-605):
+ *   max_radii2D = max(max_radii2D, radii); xyz_gradient_accum += |dL_dmeans2D[:, :2]|; denom += 1.
+ * dL_dmeans2D has grad_stride floats per Gaussian (3); max_radii2D may be NULL. No host synchronisation (the
+ * reference's boolean-mask indexing runs nonzero()). */
+int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, int grad_stride,
+                            float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

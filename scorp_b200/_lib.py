@@ -40,6 +40,12 @@ class GsrModelGrads(C.Structure):
     _fields_ = [(n, c_void_p) for n in ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")]
 
 
+class GsrAdamGroup(C.Structure):
+    """struct GsrAdamGroup (include/gsr_b200.h)."""
+    _fields_ = [("param", c_void_p), ("grad", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p),
+                ("n", C.c_int64), ("lr", C.c_double)]
+
+
 _P = c_void_p
 # name -> (restype, argtypes); every symbol include/gsr_b200.h declares
 SIGNATURES = {
@@ -58,6 +64,8 @@ SIGNATURES = {
                                    + [_P] * 5 + [_P] * 3 + [_P, C.POINTER(GsrModelGrads), _P, c_size_t, _P]),
     "gsr_rasterize_forward_views": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int] + [_P] * 7 + [_P] * 4
                                     + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
+    "gsr_adam_step": (c_int, [c_int, C.POINTER(GsrAdamGroup), C.c_double, C.c_double, C.c_double, c_int, _P]),
+    "gsr_densification_stats": (c_int, [c_int, _P, _P, c_int, _P, _P, _P, _P]),
     "gsr_l1_ssim_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_l1_ssim_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, c_size_t, _P]),
     "gsr_l1_ssim_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),
