@@ -194,17 +194,87 @@ def row_optim(cfg, K, W):
             "densification_stats": {"torch_mask_indexing_ms": t_rs, "fused_ms": t_fs, "speedup": t_rs / t_fs}}
 
 
+def row_iteration(cfg, K, W):
+    """One whole training iteration as train_3dgs.py:85-193 runs it -- staging, render, loss, backward, densification
+    statistics, optimizer step -- (a) with the reference's torch code around the stock drop-in rasterizer, (b) with
+    every 8(f) row switched on."""
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    from scorp_b200 import model_space as ms, loss_utils as lu, optim
+    sc = synth.make_scene(cfg).to("cuda"); cam = sc.cameras[0]
+    P = sc.P
+    op = sc.opacities.clamp(1e-4, 1 - 1e-4)
+    rs = dgr.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, sc.bg, 1.0, cam.viewmatrix,
+                                           cam.projmatrix, sc.sh_degree, cam.campos, False, False)
+    gt = torch.rand(3, cam.H, cam.W, device="cuda")
+    g11 = torch.tensor([np.exp(-(x - 5) ** 2 / (2 * 1.5 ** 2)) for x in range(11)], dtype=torch.float32)
+    g11 = (g11 / g11.sum()).unsqueeze(1)
+    w = g11.mm(g11.t()).float()[None, None].expand(3, 1, 11, 11).contiguous().cuda()
+    lam = 0.2
+    lrs = (0.00016, 0.0025, 0.0025 / 20.0, 0.05, 0.005, 0.001)
+    names = ("xyz", "features_dc", "features_rest", "opacity", "scaling", "rotation")
+
+    def model():
+        st = dict(xyz=sc.means3D.clone(), features_dc=sc.shs[:, :1].contiguous().clone(),
+                  features_rest=sc.shs[:, 1:].contiguous().clone(), opacity=torch.log(op / (1 - op)),
+                  scaling=torch.log(sc.scales), rotation=sc.rotations * 1.7)
+        return {k: torch.nn.Parameter(v) for k, v in st.items()}
+
+    def stats():
+        return torch.zeros(P, 1, device="cuda"), torch.zeros(P, 1, device="cuda"), torch.zeros(P, device="cuda")
+
+    sa = model(); oa = torch.optim.Adam([{"params": [sa[n]], "lr": lr, "name": n} for n, lr in zip(names, lrs)], lr=0.0, eps=1e-15)
+    acc_a, den_a, maxr_a = stats()
+    sb = model(); ob = optim.Adam([{"params": [sb[n]], "lr": lr, "name": n} for n, lr in zip(names, lrs)], lr=0.0, eps=1e-15)
+    acc_b, den_b, maxr_b = stats()
+
+    def stock():
+        shs = torch.cat((sa["features_dc"], sa["features_rest"]), dim=1)
+        m2d = torch.zeros_like(sa["xyz"], requires_grad=True) + 0
+        m2d.retain_grad()
+        image, radii, depth, alpha = dgr.GaussianRasterizer(rs)(
+            means3D=sa["xyz"], means2D=m2d, opacities=torch.sigmoid(sa["opacity"]), shs=shs,
+            scales=torch.exp(sa["scaling"]), rotations=F.normalize(sa["rotation"]))
+        loss = torch_loss(image, gt, lam, w)
+        loss.backward()
+        vis = radii > 0
+        maxr_a[vis] = torch.max(maxr_a[vis], radii[vis])
+        acc_a[vis] += torch.norm(m2d.grad[vis, :2], dim=-1, keepdim=True)
+        den_a[vis] += 1
+        oa.step(); oa.zero_grad(set_to_none=True)
+        return loss
+
+    def fused():
+        m2d = torch.zeros_like(sb["xyz"], requires_grad=True) + 0
+        m2d.retain_grad()
+        image, radii, depth, alpha = ms.rasterize_model(sb["xyz"], m2d, sb["features_dc"], sb["features_rest"],
+                                                        sb["opacity"], sb["scaling"], sb["rotation"], rs)
+        loss = lu.l1_ssim_loss(image, gt, lam)
+        loss.backward()
+        optim.add_densification_stats(acc_b, den_b, maxr_b, m2d.grad, radii)
+        ob.step(); ob.zero_grad(set_to_none=True)
+        return loss
+
+    for _ in range(8):
+        la = stock(); lb = fused()
+    t_stock, sp_s = timeit(stock, K, W)
+    t_fused, sp_f = timeit(fused, K, W)
+    return {"row": "8f whole iteration", "config": cfg, "unit": "ms per training iteration (staging + render + loss + backward + densification statistics + Adam step), inputs resident",
+            "torch_around_stock_rasterizer_ms": t_stock, "all_rows_fused_ms": t_fused, "speedup": t_stock / t_fused,
+            "spread": {"stock": sp_s, "fused": sp_f}, "loss_after_warmup": {"stock": float(la.detach()), "fused": float(lb.detach())},
+            "Mpix_per_s": {"stock": cam.W * cam.H / t_stock / 1e3, "fused": cam.W * cam.H / t_fused / 1e3}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--config", default="C2")
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
-    ap.add_argument("--rows", default="staging,loss,optim")
+    ap.add_argument("--rows", default="staging,loss,optim,iteration")
     args = ap.parse_args()
     if not torch.cuda.is_available():
         raise SystemExit("needs a CUDA device")
     for r in args.rows.split(","):
-        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim}[r]
+        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim, "iteration": row_iteration}[r]
         print(json.dumps(fn(args.config, args.steps, args.warmup)), flush=True)
 
 
