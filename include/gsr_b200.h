@@ -155,6 +155,18 @@ int gsr_rasterize_backward_raw(
     const float* dL_dout_color, const float* dL_dout_depth, const float* dL_dout_alpha,
     float* dL_dmeans2D, const GsrModelGrads* grads, void* workspace, size_t workspace_bytes, void* stream);
 
+/* The same pair for the 2DGS surfel rasterizer (gs2dgs/scene/gaussian_model.py stores the same six tensors; scaling
+ * is [P*2]). Outputs as gsr_surfel_forward / gsr_surfel_backward; dL_dtransMat and dL_dcolors are not produced. */
+int gsr_surfel_forward_raw(
+    const GsrSettings* s, int P, int M, const GsrModelParams* params,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream);
+int gsr_surfel_backward_raw(
+    const GsrSettings* s, int P, int M, int R, const GsrModelParams* params,
+    const int32_t* radii, const void* geom, const void* binning, const void* image,
+    const float* dL_dout_color, const float* dL_dout_others,
+    float* dL_dmeans2D, const GsrModelGrads* grads, void* workspace, size_t workspace_bytes, void* stream);
+
 /* present[P] (1 byte each) = view-space z > 0.2 */
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);

@@ -62,6 +62,10 @@ SIGNATURES = {
                                   + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_rasterize_backward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int, C.POINTER(GsrModelParams)]
                                    + [_P] * 5 + [_P] * 3 + [_P, C.POINTER(GsrModelGrads), _P, c_size_t, _P]),
+    "gsr_surfel_forward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, C.POINTER(GsrModelParams)] + [_P] * 3
+                               + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
+    "gsr_surfel_backward_raw": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int, C.POINTER(GsrModelParams)]
+                                + [_P] * 4 + [_P] * 2 + [_P, C.POINTER(GsrModelGrads), _P, c_size_t, _P]),
     "gsr_rasterize_forward_views": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int] + [_P] * 7 + [_P] * 4
                                     + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_adam_step": (c_int, [c_int, C.POINTER(GsrAdamGroup), C.c_double, C.c_double, C.c_double, c_int, _P]),

@@ -47,6 +47,14 @@ void prof_mark(int i, cudaStream_t st) {
 
 static bool sh_count_ok(int M) { return M == 0 || M == 1 || M == 4 || M == 9 || M == 16; }
 
+// pinned landing pad for the one device->host readback of a forward (a pageable destination makes
+// cudaMemcpyAsync stage through a driver bounce buffer); one per host thread, never freed
+uint32_t* readback_pad() {
+    static thread_local uint32_t* pad = nullptr;
+    if (!pad && cudaHostAlloc((void**)&pad, 64, cudaHostAllocDefault) != cudaSuccess) { pad = nullptr; cudaGetLastError(); }
+    return pad;
+}
+
 thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false };
 EarlyRgb take_early_rgb() { const EarlyRgb e = g_early; g_early.armed = false; return e; }
 
@@ -154,7 +162,8 @@ static int forward_impl(
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
     if ((rc = check_cuda(launch_tile_scan(tiles, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
-    uint32_t n_host[2] = {0, 0};
+    uint32_t n_stack[2] = {0, 0};
+    uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
     if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
     const int N = (int)n_host[0], max_len = (int)n_host[1];

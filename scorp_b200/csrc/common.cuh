@@ -103,6 +103,8 @@ EarlyRgb take_early_rgb();          // returns the armed request (armed == false
 cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                         int rgb_off, float* drgb, cudaStream_t st);
 
+uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
+
 // error plumbing (api.cu)
 void set_error(const char* fmt, ...);
 int  check_cuda(cudaError_t e, const char* what);

@@ -86,6 +86,9 @@ struct SurfelFwdArgs {
     const float *means3D, *shs, *colors_precomp, *opacities, *scales, *rotations, *transMat_precomp;
     const float *view, *proj, *campos;
     bool prefiltered;
+    // model-space variant (gsr_surfel_forward_raw): see FwdArgs in common.cuh
+    const float* shs_rest = nullptr;
+    bool raw = false;
 };
 cudaError_t launch_surfel_preprocess(const SurfelFwdArgs& a, const SurfelGeom& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_surfel_render_forward(int W, int H, int gx, int gy, const SurfelGeom& g, const SurfelImage& img,
@@ -105,6 +108,11 @@ struct SurfelBwdArgs {
     const uint8_t* clamped;
     const float* acc;
     float *dL_dmeans2D, *dL_dcolors, *dL_dopacity, *dL_dmeans3D, *dL_dtransMat, *dL_dsh, *dL_dscales, *dL_drotations;
+    // model-space variant (gsr_surfel_backward_raw)
+    const float* shs_rest = nullptr;
+    const float* opacities = nullptr;
+    float* dL_dsh_rest = nullptr;
+    bool raw = false;
 };
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st);
 

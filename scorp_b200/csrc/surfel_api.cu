@@ -16,9 +16,9 @@ void gsr_surfel_geom_layout(int P, int tiles, size_t off[6], size_t* total) { *t
 void gsr_surfel_image_layout(int W, int H, size_t off[4], size_t* total) { *total = carve_surfel_image(nullptr, W, H, nullptr, off); }
 size_t gsr_surfel_backward_workspace_bytes(int P) { return align_up((size_t)(P > 0 ? P : 1) * SACC_STRIDE * sizeof(float)); }
 
-int gsr_surfel_forward(
+static int surfel_forward_impl(
     const GsrSettings* s, int P, int M,
-    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* means3D, const float* shs, const float* shs_rest, bool raw, const float* colors_precomp,
     const float* opacities, const float* scales, const float* rotations, const float* transMat_precomp,
     float* out_color, float* out_others, int32_t* radii,
     gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
@@ -62,6 +62,7 @@ int gsr_surfel_forward(
     a.scales = scales; a.rotations = rotations; a.transMat_precomp = transMat_precomp;
     a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos;
     a.prefiltered = s->prefiltered != 0;
+    a.shs_rest = shs_rest; a.raw = raw;
     if ((rc = check_cuda(launch_surfel_preprocess(a, g, radii, st), "surfel preprocess launch"))) return rc;
     if ((rc = stage_check(s, st, "surfel preprocess"))) return rc;
     prof_mark(1, st);
@@ -69,7 +70,8 @@ int gsr_surfel_forward(
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
     if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
-    uint32_t n_host[2] = {0, 0};
+    uint32_t n_stack[2] = {0, 0};
+    uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
     if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
     if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
     const int N = (int)n_host[0], max_len = (int)n_host[1];
@@ -88,6 +90,45 @@ int gsr_surfel_forward(
     return stage_check(s, st, "surfel render forward");
 }
 
+int gsr_surfel_forward(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* transMat_precomp,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    return surfel_forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations,
+                               transMat_precomp, out_color, out_others, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+static bool model_params_ok(int P, int M, const GsrModelParams* mp) {
+    return mp && (P <= 0 || (mp->xyz && mp->features_dc && mp->opacity && mp->scaling && mp->rotation && (M <= 1 || mp->features_rest)));
+}
+
+int gsr_surfel_forward_raw(
+    const GsrSettings* s, int P, int M, const GsrModelParams* mp,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+{
+    if (!model_params_ok(P, M, mp)) { set_error("null model parameter"); return GSR_EINVAL; }
+    if (M < 1) { set_error("model-space entry needs SH coefficients (M >= 1)"); return GSR_EUNSUPPORTED; }
+    return surfel_forward_impl(s, P, M, mp->xyz, mp->features_dc, mp->features_rest, true, nullptr, mp->opacity, mp->scaling,
+                               mp->rotation, nullptr, out_color, out_others, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+struct SurfelRawBwd { const float* shs_rest; const float* opacities; float* dL_dsh_rest; };
+
+static int surfel_backward_impl(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* transMat_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* dL_dout_color, const float* dL_dout_others,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dtransMat, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream, const SurfelRawBwd* raw);
+
 int gsr_surfel_backward(
     const GsrSettings* s, int P, int M, int R,
     const float* means3D, const float* shs, const float* colors_precomp,
@@ -98,6 +139,41 @@ int gsr_surfel_backward(
     float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
     float* dL_dtransMat, float* dL_dsh, float* dL_dscales, float* dL_drotations,
     void* workspace, size_t workspace_bytes, void* stream)
+{
+    return surfel_backward_impl(s, P, M, R, means3D, shs, colors_precomp, scales, rotations, transMat_precomp, radii, geom,
+                                binning, image, dL_dout_color, dL_dout_others, dL_dmeans2D, dL_dcolors, dL_dopacity,
+                                dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations, workspace, workspace_bytes,
+                                stream, nullptr);
+}
+
+int gsr_surfel_backward_raw(
+    const GsrSettings* s, int P, int M, int R, const GsrModelParams* mp,
+    const int32_t* radii, const void* geom, const void* binning, const void* image,
+    const float* dL_dout_color, const float* dL_dout_others,
+    float* dL_dmeans2D, const GsrModelGrads* mg, void* workspace, size_t workspace_bytes, void* stream)
+{
+    if (!model_params_ok(P, M, mp) || !mg) { set_error("null model parameters/gradients"); return GSR_EINVAL; }
+    if (P > 0 && (!mg->xyz || !mg->features_dc || !mg->opacity || !mg->scaling || !mg->rotation || (M > 1 && !mg->features_rest))) {
+        set_error("null model gradient"); return GSR_EINVAL;
+    }
+    if (M < 1) { set_error("model-space entry needs SH coefficients (M >= 1)"); return GSR_EUNSUPPORTED; }
+    const SurfelRawBwd raw = { mp->features_rest, mp->opacity, mg->features_rest };
+    // dL_dcolors / dL_dtransMat have no model parameter behind them: not produced (any non-NULL pointer passes the checks)
+    return surfel_backward_impl(s, P, M, R, mp->xyz, mp->features_dc, nullptr, mp->scaling, mp->rotation, nullptr, radii, geom,
+                                binning, image, dL_dout_color, dL_dout_others, dL_dmeans2D, mg->xyz, mg->opacity, mg->xyz,
+                                mg->xyz, mg->features_dc, mg->scaling, mg->rotation, workspace, workspace_bytes, stream, &raw);
+}
+
+static int surfel_backward_impl(
+    const GsrSettings* s, int P, int M, int R,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* scales, const float* rotations, const float* transMat_precomp,
+    const int32_t* radii,
+    const void* geom, const void* binning, const void* image,
+    const float* dL_dout_color, const float* dL_dout_others,
+    float* dL_dmeans2D, float* dL_dcolors, float* dL_dopacity, float* dL_dmeans3D,
+    float* dL_dtransMat, float* dL_dsh, float* dL_dscales, float* dL_drotations,
+    void* workspace, size_t workspace_bytes, void* stream, const SurfelRawBwd* raw)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
@@ -143,6 +219,7 @@ int gsr_surfel_backward(
     b.radii = radii; b.rec = g.rec; b.clamped = g.clamped; b.acc = acc;
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dtransMat = dL_dtransMat; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
+    if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
     if ((rc = check_cuda(launch_surfel_preprocess_backward(b, st), "surfel preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "surfel preprocess backward");

@@ -125,7 +125,7 @@ __device__ __forceinline__ float4 surfel_cull_box(const M3& T, float cx, float c
     return make_float4(lo[0], hi[0], lo[1], hi[1]);
 }
 
-template <bool VEC>
+template <bool VEC, bool RAW>
 __global__ void __launch_bounds__(256, 4)
 surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ radii) {
     const int idx = blockIdx.x * 256 + threadIdx.x;
@@ -143,8 +143,10 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
             M3 T; float3 normal;
             if (a.transMat_precomp == nullptr) {
                 const float* qp = a.rotations + 4 * (size_t)idx;
-                surfel_transmat(px, py, pz, __ldg(a.scales + 2 * idx), __ldg(a.scales + 2 * idx + 1), a.scale_modifier,
-                                __ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3), a.proj, a.view, a.W, a.H, T, normal);
+                float4 q = make_float4(__ldg(qp), __ldg(qp + 1), __ldg(qp + 2), __ldg(qp + 3));
+                float s0 = __ldg(a.scales + 2 * idx), s1 = __ldg(a.scales + 2 * idx + 1);
+                if constexpr (RAW) { q = act_rotation(q); s0 = act_scale(s0); s1 = act_scale(s1); }
+                surfel_transmat(px, py, pz, s0, s1, a.scale_modifier, q.x, q.y, q.z, q.w, a.proj, a.view, a.W, a.H, T, normal);
             } else {
                 const float* tp = a.transMat_precomp + 9 * (size_t)idx;
 #pragma unroll
@@ -173,8 +175,9 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
                 cr = __ldg(a.colors_precomp + 3 * idx); cg = __ldg(a.colors_precomp + 3 * idx + 1); cb = __ldg(a.colors_precomp + 3 * idx + 2);
             } else {
                 ShReader<VEC> sh;
-                const float* base = a.shs + (size_t)idx * a.M * 3;
-                sh.base = base; sh.rest = base + 3;
+                const float* base = RAW ? a.shs + (size_t)idx * 3 : a.shs + (size_t)idx * a.M * 3;
+                sh.base = base;
+                sh.rest = RAW ? a.shs_rest + (size_t)idx * (a.M - 1) * 3 : base + 3;
                 if constexpr (VEC) {
 #pragma unroll
                     for (int k = 0; k < 12; ++k) sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k);
@@ -185,7 +188,7 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
                 g.clamped[idx] = (col.r < 0.0f ? 1 : 0) | (col.g < 0.0f ? 2 : 0) | (col.b < 0.0f ? 4 : 0);
                 cr = (col.r < 0.0f) ? 0.0f : col.r; cg = (col.g < 0.0f) ? 0.0f : col.g; cb = (col.b < 0.0f) ? 0.0f : col.b;
             }
-            const float op = __ldg(a.opacities + idx);
+            const float op = RAW ? act_opacity(__ldg(a.opacities + idx)) : __ldg(a.opacities + idx);
             const float4 box = surfel_cull_box(T, center.x, center.y, op);
             float4* dst = reinterpret_cast<float4*>(g.rec + idx);
             dst[0] = make_float4(center.x, center.y, T.c[0][0], T.c[0][1]);
@@ -209,8 +212,9 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
 cudaError_t launch_surfel_preprocess(const SurfelFwdArgs& a, const SurfelGeom& g, int32_t* radii, cudaStream_t st) {
     const int blocks = (a.P + 255) / 256;
     const bool vec = a.shs && a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
-    if (vec) surfel_preprocess_kernel<true><<<blocks, 256, 0, st>>>(a, g, radii);
-    else     surfel_preprocess_kernel<false><<<blocks, 256, 0, st>>>(a, g, radii);
+    if (a.raw)    surfel_preprocess_kernel<false, true><<<blocks, 256, 0, st>>>(a, g, radii);
+    else if (vec) surfel_preprocess_kernel<true, false><<<blocks, 256, 0, st>>>(a, g, radii);
+    else          surfel_preprocess_kernel<false, false><<<blocks, 256, 0, st>>>(a, g, radii);
     return cudaGetLastError();
 }
 

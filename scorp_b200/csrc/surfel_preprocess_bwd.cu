@@ -11,7 +11,9 @@
 
 namespace gsr {
 
-template <int M3>       // 3 * SH coefficients per Gaussian (0: colours were precomputed)
+// M3: 3 * SH coefficients per surfel (0: colours were precomputed). RAW: model-space variant (split SH rows,
+// gradients taken through sigmoid / exp / normalize to the stored parameters), as in preprocess_bwd.cu.
+template <int M3, bool RAW>
 __global__ void __launch_bounds__(SH_TILE, 8)
 surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
     __shared__ float s_sh[M3 ? SH_TILE * ShTile<M3>::STRIDE : 1];
@@ -25,7 +27,8 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         s_vis[threadIdx.x] = vis;
         __syncthreads();
         // asynchronous (LDGSTS): in flight while the per-surfel inputs are fetched and the transMat part is computed
-        sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
+        if constexpr (RAW) sh_tile_load_async_split<M3>(a.shs, a.shs_rest, row0, nrows, s_vis, s_sh);
+        else               sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
     }
 
     float dT[3][3] = { { 0, 0, 0 }, { 0, 0, 0 }, { 0, 0, 0 } };   // column-major like glm: dT[j] = gradient of row j of transMat
@@ -61,7 +64,7 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         const float* pr = a.proj;
 
         float T[3][3], Pm[3][4], R[3][3];
-        float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f, sc0 = 0.f, sc1 = 0.f;
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f, sc0 = 0.f, sc1 = 0.f, qn = 1.0f;
         V3 normal = { 0, 0, 0 };
         if (a.T_precomp) {
 #pragma unroll
@@ -72,6 +75,13 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             const float* qp = a.rotations + 4 * (size_t)idx;
             q0 = __ldg(qp); q1 = __ldg(qp + 1); q2 = __ldg(qp + 2); q3 = __ldg(qp + 3);
             sc0 = __ldg(a.scales + 2 * idx); sc1 = __ldg(a.scales + 2 * idx + 1);
+            if constexpr (RAW) {
+                const float4 qr = make_float4(q0, q1, q2, q3);
+                qn = quat_norm(qr);
+                const float4 qa = act_rotation(qr);
+                q0 = qa.x; q1 = qa.y; q2 = qa.z; q3 = qa.w;
+                sc0 = act_scale(sc0); sc1 = act_scale(sc1);
+            }
             const float s = rsqrtf(q3 * q3 + q0 * q0 + q1 * q1 + q2 * q2);
             const float w = q0 * s, x = q1 * s, y = q2 * s, z = q3 * s;
             R[0][0] = 1.f - 2.f * (y * y + z * z); R[0][1] = 2.f * (x * y + w * z); R[0][2] = 2.f * (x * z - w * y);
@@ -163,6 +173,16 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             dscale0 = dRS0.x * R[0][0] + dRS0.y * R[0][1] + dRS0.z * R[0][2];
             dscale1 = dRS1.x * R[1][0] + dRS1.y * R[1][1] + dRS1.z * R[1][2];
             dmean = { dM[2][0], dM[2][1], dM[2][2] };
+            if constexpr (RAW) {      // exp and normalize (preprocess_bwd.cu)
+                dscale0 *= sc0; dscale1 *= sc1;
+                const float qg = q0 * drot.x + q1 * drot.y + q2 * drot.z + q3 * drot.w;
+                const float in = 1.0f / qn;
+                drot = make_float4((drot.x - q0 * qg) * in, (drot.y - q1 * qg) * in, (drot.z - q2 * qg) * in, (drot.w - q3 * qg) * in);
+            }
+        }
+        if constexpr (RAW) {          // sigmoid
+            const float so = act_opacity(__ldg(a.opacities + idx));
+            dop = dop * ((1.0f - so) * so);
         }
 
         // densification hack (backward.cu:632-635)
@@ -170,11 +190,15 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         dm2d.x = (float)(dT_out[2] * depth * 0.5 * float(W));
         dm2d.y = (float)(dT_out[5] * depth * 0.5 * float(H));
         dm2d.z = 0.0f;
+        if constexpr (!RAW) {
 #pragma unroll
-        for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = dT_out[k];
+            for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = dT_out[k];
+        }
     } else if (valid) {
+        if constexpr (!RAW) {
 #pragma unroll
-        for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = 0.0f;
+            for (int k = 0; k < 9; ++k) a.dL_dtransMat[9 * (size_t)idx + k] = 0.0f;
+        }
     }
     if constexpr (M3 != 0) {
         // ---- colour -> SH (+ mean), once the tile has landed
@@ -186,13 +210,14 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
             dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
         __syncthreads();
-        if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
+        if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
+        else if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
     if (!valid) return;
 
     st3(a.dL_dmeans3D + 3 * idx, dmean);
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
-    st3(a.dL_dcolors + 3 * idx, dcol);
+    if constexpr (!RAW) st3(a.dL_dcolors + 3 * idx, dcol);
     a.dL_dopacity[idx] = dop;
     a.dL_dscales[2 * (size_t)idx] = dscale0; a.dL_dscales[2 * (size_t)idx + 1] = dscale1;
     float* dq = a.dL_drotations + 4 * (size_t)idx;
@@ -201,12 +226,22 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
 
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st) {
     const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    if (a.raw) {
+        switch (3 * a.M) {
+        case 3:  surfel_preprocess_backward_kernel<3, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 12: surfel_preprocess_backward_kernel<12, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 27: surfel_preprocess_backward_kernel<27, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        case 48: surfel_preprocess_backward_kernel<48, true><<<blocks, SH_TILE, 0, st>>>(a); break;
+        default: return cudaErrorInvalidValue;
+        }
+        return cudaGetLastError();
+    }
     switch (a.shs ? 3 * a.M : 0) {
-    case 0:  surfel_preprocess_backward_kernel<0><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 3:  surfel_preprocess_backward_kernel<3><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 12: surfel_preprocess_backward_kernel<12><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 27: surfel_preprocess_backward_kernel<27><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 48: surfel_preprocess_backward_kernel<48><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 0:  surfel_preprocess_backward_kernel<0, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 3:  surfel_preprocess_backward_kernel<3, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 12: surfel_preprocess_backward_kernel<12, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 27: surfel_preprocess_backward_kernel<27, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 48: surfel_preprocess_backward_kernel<48, false><<<blocks, SH_TILE, 0, st>>>(a); break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();

@@ -140,3 +140,38 @@ def test_empty_and_errors():
                            torch.zeros(4, 1), torch.zeros(4, 3), torch.zeros(4, 4), rs)
     with pytest.raises(RuntimeError, match="features_dc"):
         ms.rasterize_model(z(4, 3), z(4, 3), z(3, 1, 3), z(4, 0, 3), z(4, 1), z(4, 3), z(4, 4), rs)
+
+
+@pytest.mark.parametrize("kw,smod", [(dict(P=40_000, W=300, H=200), 1.0), (dict(P=15_000, W=160, H=120, sh_degree=1), 0.8)])
+def test_surfel_model_space_matches_torch_staging(kw, smod):
+    """2DGS: rasterize_surfel_model == torch staging + the stock surfel rasterizer (gs2dgs render path)."""
+    import scorp_b200.diff_surfel_rasterization as dsr
+    from scorp_b200 import model_space as ms
+    sc = h.make("C4", **kw); cam = sc.cameras[0]
+    rs = _settings(sc, cam, dsr, smod)
+    sa, sb = _stored(sc), _stored(sc)
+    m2a = torch.zeros_like(sa["xyz"], requires_grad=True) + 0; m2a.retain_grad()
+    m2b = torch.zeros_like(sb["xyz"], requires_grad=True) + 0; m2b.retain_grad()
+    ca, ra, oa = dsr.GaussianRasterizer(rs)(
+        means3D=sa["xyz"], means2D=m2a, opacities=torch.sigmoid(sa["opacity"]),
+        shs=torch.cat((sa["features_dc"], sa["features_rest"]), dim=1), scales=torch.exp(sa["scaling"]),
+        rotations=torch.nn.functional.normalize(sa["rotation"]))
+    cb, rb, ob = ms.rasterize_surfel_model(sb["xyz"], m2b, sb["features_dc"], sb["features_rest"], sb["opacity"],
+                                           sb["scaling"], sb["rotation"], rs)
+    assert torch.equal(ra, rb), f"{int((ra != rb).sum())} radii differ"
+    assert torch.equal(ca, cb) and torch.equal(oa, ob)
+    gc, go = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 17, channels=(3, 7))]
+    for c, o in ((ca, oa), (cb, ob)):
+        ((c * gc).sum() + (o * go).sum()).backward()
+
+    def same(x, y):      # two backward runs differ by the order of float atomics in the blend backward
+        return torch.allclose(x, y, rtol=1e-3, atol=1e-5 * float(y.abs().max()) + 1e-30)
+    for k in sa:
+        if sa[k].numel():
+            assert sb[k].grad is not None and same(sb[k].grad, sa[k].grad), \
+                (k, float((sb[k].grad - sa[k].grad).abs().max()), float(sa[k].grad.abs().max()))
+    assert same(m2b.grad, m2a.grad)
+    inv = rb == 0
+    for k in sb:
+        if sb[k].numel() and inv.any():
+            assert float(sb[k].grad[inv].abs().max()) == 0.0, k
