@@ -23,5 +23,40 @@ for cfg, kw, surfel in (("C1", dict(P=6000, W=200, H=136), False), ("C1", dict(P
 sc = h.make("C1", P=5000, W=64, H=64)
 print("visible", int(c3.mark_visible(sc.means3D, sc.cameras[0].viewmatrix, sc.cameras[0].projmatrix).sum()))
 print("knn", float(distCUDA2(torch.rand(10000, 3, device="cuda")).mean()))
+
+# rows next to the boundary: model-space 3DGS / 2DGS, batched views, loss, Adam, densification statistics
+import torch.nn.functional as F
+from scorp_b200 import model_space as ms, loss_utils as lu, optim
+import scorp_b200.diff_gaussian_rasterization as dgr
+import scorp_b200.diff_surfel_rasterization as dsr
+for cfg, kw, mod in (("C2", dict(P=5000, W=150, H=90), dgr), ("C1", dict(P=3000, W=70, H=50), dgr), ("C4", dict(P=5000, W=150, H=90), dsr)):
+    sc = h.make(cfg, **kw); cam = sc.cameras[0]
+    rs = mod.GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, sc.bg, 1.0, cam.viewmatrix, cam.projmatrix,
+                                           sc.sh_degree, cam.campos, False, False)
+    op = sc.opacities.clamp(1e-4, 1 - 1e-4)
+    st = [t.clone().requires_grad_(True) for t in (sc.means3D, sc.shs[:, :1].contiguous(), sc.shs[:, 1:].contiguous(),
+                                                   torch.log(op / (1 - op)), torch.log(sc.scales), sc.rotations * 2.0)]
+    m2d = torch.zeros_like(st[0], requires_grad=True)
+    fn = ms.rasterize_surfel_model if mod is dsr else ms.rasterize_model
+    outs = fn(st[0], m2d, st[1], st[2], st[3], st[4], st[5], rs)
+    gt = torch.rand_like(outs[0])
+    loss = lu.l1_ssim_loss(outs[0], gt, 0.2) + 0.01 * outs[2].sum()
+    loss.backward()
+    accum = torch.zeros(sc.P, 1, device="cuda"); den = torch.zeros(sc.P, 1, device="cuda"); mr = torch.zeros(sc.P, device="cuda")
+    optim.add_densification_stats(accum, den, mr, m2d.grad, outs[1])
+    params = [torch.nn.Parameter(t.detach().clone()) for t in st if t.numel()]
+    for p_, t in zip(params, [t for t in st if t.numel()]):
+        p_.grad = t.grad
+    optim.Adam([{"params": [p_], "lr": 1e-3} for p_ in params], lr=0.0, eps=1e-15).step()
+    torch.cuda.synchronize()
+    print("model-space", cfg, kw, "loss", float(loss.detach()), "stats", float(den.sum()))
+sc = synth.make_scene("C5", P=4000, W=100, H=80, n_views=5, rotations_npz=synth.random_rotations(5)).to("cuda")
+cams = sc.cameras
+E = torch.Tensor([])
+n, col, dep, alp, rad = c3.rasterize_gaussians_views(sc.bg, sc.means3D, E, sc.opacities, sc.scales, sc.rotations, 1.0, E,
+                                                     torch.stack([c.viewmatrix for c in cams]), torch.stack([c.projmatrix for c in cams]),
+                                                     cams[0].tanfovx, cams[0].tanfovy, 80, 100, sc.shs, sc.sh_degree,
+                                                     torch.stack([c.campos for c in cams]), False, False)
 torch.cuda.synchronize()
+print("views", n, float(col.sum()))
 print("done")
