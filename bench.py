@@ -50,8 +50,9 @@ def parse():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--config", default="C2", choices=list(synth.CONFIGS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--exchange", choices=["auto", "dense", "factored"], default="auto",
-                    help="N>1, ours: dense = one all_reduce over the gradient arena; factored = multiview.FactoredExchange")
+    ap.add_argument("--exchange", choices=["auto", "dense", "factored", "peer"], default="auto",
+                    help="N>1, ours: dense = one all_reduce over the gradient arena; factored = multiview.FactoredExchange "
+                         "(NCCL all-gather of dL_dRGB); peer = multiview.PeerExchange (the backward stores dL_dRGB into peer memory itself)")
     ap.add_argument("--views-per-rank", type=int, default=0, help="views each rank renders per step (0: the config's default)")
     ap.add_argument("--view-loop", action="store_true",
                     help="ours, forward-only configs: one forward call per view (the reference's loop) instead of the batched gsr_rasterize_forward_views")
@@ -447,12 +448,15 @@ def run(arm, args, rank, world, local):
     exchange = "none"
     if world > 1 and not fwd_only:
         exchange = "one all_reduce over the parameter-gradient arena"
-        want = args.exchange == "factored" or (args.exchange == "auto" and mv.FactoredExchange.worth_it(world, M))
+        want = args.exchange in ("factored", "peer") or (args.exchange == "auto" and mv.FactoredExchange.worth_it(world, M))
         if arm.name == "ours" and vpr == 1 and M > 0 and want:
             # one view per rank: gather 3 floats per Gaussian per rank and rebuild the SH gradient (multiview.FactoredExchange)
-            mv.install_factored_exchange()
+            use_peer = args.exchange in ("peer", "auto")      # auto: peer memory, NCCL gather if symmetric memory is unavailable
+            mv.install_factored_exchange(peer=use_peer)
             arm.factored = True
             exchange = "factored: all_gather of dL_dRGB (12 B x world per Gaussian) + all_reduce of the 11 non-SH floats"
+            if use_peer:
+                exchange = "peer: dL_dRGB stored into every rank's gather buffer by the backward itself (NVLink peer pointers, symmetric memory) + all_reduce of the 11 non-SH floats"
         elif arm.name == "reference":
             exchange = "five all_reduce calls (one per gradient tensor)"
     n, radii, _ = step_resident()
@@ -525,6 +529,10 @@ def run(arm, args, rank, world, local):
     if arm.name == "ours":
         # preprocess, scan, scatter, sort, blend (+ blend bwd, preprocess bwd) (+ clamped colour gradient, SH rebuild)
         launches = ((4 if fwd_only else 7) + (2 if arm.factored else 0)) * (1 if batched else len(cams)) * args.steps
+    if arm.name == "ours" and arm.factored and args.exchange in ("peer", "auto"):
+        from scorp_b200.diff_gaussian_rasterization import _C as _c3
+        fx = _c3._factored[0]
+        exchange += "" if getattr(fx, "ok", False) else f" [symmetric memory unavailable, ran as factored: {getattr(fx, 'why', '')}]"
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),

@@ -232,6 +232,15 @@ int gsr_clamped_color_grad(int P, int W, int H, int surfel, const void* geom_buf
  * calls ready(user) on the host, so the caller can start the all-gather of drgb underneath the rest of the backward.
  * drgb == NULL disarms. Only takes effect when the backward is given SH coefficients. */
 int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
+/* Peer-memory variant: instead of writing drgb locally for a later all-gather, the next backward writes it straight
+ * into every rank's gather buffer through NVLink peer pointers -- drgb_dst[k] / campos_dst[k] (host arrays of n_dst
+ * device pointers, n_dst <= 16) are THIS rank's slot in rank k's buffer ([P*3] floats and [3] floats; the local rank
+ * included) -- from a kernel on side_stream that the library orders after its blend kernel, so the stores travel
+ * underneath the preprocess-backward kernel. ready(user) is called once that kernel is enqueued; the caller then
+ * synchronises the ranks (scorp_b200/multiview.py:PeerExchange uses torch symmetric memory for pointers and barrier).
+ * n_dst <= 0 disarms. */
+int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,
+                                 void* side_stream, void (*ready)(void* user), void* user);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
                            const float* drgb, float* dL_dsh, void* stream);
 

@@ -88,6 +88,7 @@ SIGNATURES = {
     "gsr_knn_dist2": (c_int, [c_int, _P, _P, _P, c_size_t, _P]),
     "gsr_clamped_color_grad": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "gsr_backward_early_rgb": (c_int, [_P, _P, _P]),
+    "gsr_backward_early_rgb_peers": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), _P, _P, _P, _P]),
     "gsr_sh_grad_from_views": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
 }
 

@@ -55,7 +55,7 @@ uint32_t* readback_pad() {
     return pad;
 }
 
-thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false };
+thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false, {} };
 EarlyRgb take_early_rgb() { const EarlyRgb e = g_early; g_early.armed = false; return e; }
 
 }  // namespace gsr
@@ -309,8 +309,11 @@ static int backward_impl(
     {   // multi-GPU: the colour gradient is final here; hand it out so its all-gather overlaps the next kernel
         const EarlyRgb e = take_early_rgb();
         if (e.armed && shs) {
-            if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.drgb, st),
-                                 "early colour gradient launch"))) return rc;
+            if (e.peers.n > 0) {
+                if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.peers, st),
+                                     "peer colour gradient push"))) return rc;
+            } else if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.drgb, st),
+                                        "early colour gradient launch"))) return rc;
             if (e.ready) e.ready(e.user);
         }
     }
@@ -333,8 +336,25 @@ static int backward_impl(
 }
 
 int gsr_backward_early_rgb(float* drgb, void (*ready)(void*), void* user) {
-    if (!drgb) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false}; return GSR_OK; }
-    gsr::g_early = gsr::EarlyRgb{drgb, ready, user, true};
+    if (!drgb) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false, {}}; return GSR_OK; }
+    gsr::g_early = gsr::EarlyRgb{drgb, ready, user, true, {}};
+    return GSR_OK;
+}
+
+int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,
+                                 void* side_stream, void (*ready)(void*), void* user) {
+    if (n_dst <= 0) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false, {}}; return GSR_OK; }
+    if (n_dst > gsr::PEER_MAX || !drgb_dst || !campos_dst || !campos_src || !side_stream) {
+        set_error("gsr_backward_early_rgb_peers: bad argument (at most %d destinations, a side stream is required)", gsr::PEER_MAX);
+        return GSR_EINVAL;
+    }
+    gsr::EarlyRgb e{nullptr, ready, user, true, {}};
+    e.peers.n = n_dst; e.peers.campos_src = campos_src; e.peers.side = (cudaStream_t)side_stream;
+    for (int k = 0; k < n_dst; ++k) {
+        if (!drgb_dst[k] || !campos_dst[k]) { set_error("gsr_backward_early_rgb_peers: null destination %d", k); return GSR_EINVAL; }
+        e.peers.drgb[k] = drgb_dst[k]; e.peers.campos[k] = campos_dst[k];
+    }
+    gsr::g_early = e;
     return GSR_OK;
 }
 

@@ -98,10 +98,21 @@ inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nu
 }
 
 // gsr_backward_early_rgb (api.cu): armed per thread for the next backward call
-struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; };
+constexpr int PEER_MAX = 16;
+struct PeerDst {                    // gsr_backward_early_rgb_peers: one destination per rank (this rank's slot in that rank's buffer)
+    int n = 0;
+    float* drgb[PEER_MAX] = {};
+    float* campos[PEER_MAX] = {};
+    const float* campos_src = nullptr;
+    cudaStream_t side = nullptr;    // the push kernel runs here, ordered after the blend backward by an event
+};
+struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; PeerDst peers; };
 EarlyRgb take_early_rgb();          // returns the armed request (armed == false if none) and disarms it
 cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                         int rgb_off, float* drgb, cudaStream_t st);
+// the same values written straight into every rank's gather buffer through peer pointers (all-gather by stores)
+cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
+                                    int rgb_off, const PeerDst& dst, cudaStream_t main);
 
 uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
 

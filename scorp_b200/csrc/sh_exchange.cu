@@ -41,6 +41,36 @@ cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8
     return cudaGetLastError();
 }
 
+// Peer variant: the three floats go straight into every rank's gather buffer through NVLink peer pointers (this
+// rank's slot in each buffer, the local one included), i.e. the all-gather is done by the producing kernel's stores
+// instead of a collective afterwards. Runs on a side stream ordered after the blend backward, so the stores travel
+// underneath the preprocess-backward kernel of the main stream. Block 0 also publishes the camera position.
+__global__ void __launch_bounds__(256)
+clamped_rgb_push_kernel(int P, const int32_t* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                        const float* __restrict__ acc, int stride, int rgb_off, PeerDst d) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x < 3) {
+        const float c = d.campos_src[threadIdx.x];
+        for (int k = 0; k < d.n; ++k) d.campos[k][threadIdx.x] = c;
+    }
+    if (i >= 3 * P) return;
+    const int g = i / 3, c = i - 3 * g;
+    float v = 0.0f;
+    if (radii[g] > 0 && !((clamped[g] >> c) & 1)) v = acc[(size_t)g * stride + rgb_off + c];
+#pragma unroll 4
+    for (int k = 0; k < d.n; ++k) d.drgb[k][i] = v;
+}
+cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
+                                    int rgb_off, const PeerDst& dst, cudaStream_t main) {
+    static thread_local cudaEvent_t ev = nullptr;
+    cudaError_t e;
+    if (!ev && (e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
+    if ((e = cudaEventRecord(ev, main)) != cudaSuccess) return e;
+    if ((e = cudaStreamWaitEvent(dst.side, ev, 0)) != cudaSuccess) return e;
+    if (P > 0) clamped_rgb_push_kernel<<<(3 * P + 255) / 256, 256, 0, dst.side>>>(P, radii, clamped, acc, stride, rgb_off, dst);
+    return cudaGetLastError();
+}
+
 // One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
 // sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
 template <int M3>

@@ -204,8 +204,11 @@ static int surfel_backward_impl(
     {   // multi-GPU: see gsr_rasterize_backward
         const EarlyRgb e = take_early_rgb();
         if (e.armed && shs) {
-            if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.drgb, st),
-                                 "early colour gradient launch"))) return rc;
+            if (e.peers.n > 0) {
+                if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.peers, st),
+                                     "peer colour gradient push"))) return rc;
+            } else if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.drgb, st),
+                                        "early colour gradient launch"))) return rc;
             if (e.ready) e.ready(e.user);
         }
     }

@@ -69,6 +69,10 @@ def _arm_early(lib, fx, g_drgb, campos, P):
     its blend kernel and start gathering it there (gsr_backward_early_rgb). Returns (callback to keep alive until the
     backward returned, list that receives an exception raised inside it); no reference cycle: the closure does not
     see the callback object."""
+    if hasattr(fx, "arm"):             # multiview.PeerExchange: the backward pushes drgb into peer memory itself
+        armed = fx.arm(lib, campos, P, g_drgb.device)
+        if armed is not None:
+            return armed
     errors = []
 
     def _ready(_user):

@@ -13,6 +13,7 @@ host-side logic).
 """
 from __future__ import annotations
 
+import ctypes as C
 from typing import Iterable, List, Optional, Sequence
 
 import torch
@@ -162,6 +163,96 @@ class FactoredExchange:
         self.finish(head, means3D, dsh_out, P, M, D)
 
 
+class PeerExchange(FactoredExchange):
+    """FactoredExchange whose all-gather is done by the producing kernel itself: the backward writes this rank's
+    clamped colour gradient straight into every rank's gather buffer through NVLink peer pointers
+    (gsr_backward_early_rgb_peers, csrc/sh_exchange.cu:clamped_rgb_push_kernel) on a side stream, underneath the
+    preprocess-backward kernel; a device-side barrier over symmetric-memory signal pads replaces the collective's
+    synchronisation. The gather buffers live in torch symmetric memory (torch.distributed._symmetric_memory: peer
+    pointers + barrier) and are double-buffered by step parity, so a fast rank's next push cannot overwrite what a
+    slow rank's rebuild kernel is still reading (the barrier bounds the skew to one step). The 11 / 10 non-SH floats
+    are still all-reduced by NCCL (NVLS in-switch reduction), underneath the rebuild kernel.
+
+    Construction is collective. If symmetric memory cannot be set up (no P2P access, a backend without it), `ok` is
+    False and the object behaves exactly like FactoredExchange (NCCL all-gather): both are GPU paths of this library."""
+
+    def __init__(self, group=None, rebuild=None):
+        super().__init__(group, rebuild)
+        self._symm = {}
+        self._parity = 0
+        self._side = None
+        self.ok = True
+        self.why = ""
+
+    def _setup(self, world, P, dev):
+        key = (world, P, str(dev))
+        if key in self._symm:
+            return self._symm[key]
+        import torch.distributed._symmetric_memory as symm
+        grp = self.group if self.group is not None else dist.group.WORLD
+        half = world * P * 3 + world * 4
+        t = symm.empty(2 * half, dtype=torch.float32, device=dev)
+        hdl = symm.rendezvous(t, grp)
+        rank = dist.get_rank(grp)
+        ptrs = [int(p) for p in hdl.buffer_ptrs]
+        views, dst = [], []
+        for b in range(2):
+            base = b * half
+            views.append((t[base: base + world * P * 3].view(world, P, 3),
+                          t[base + world * P * 3: base + world * P * 3 + world * 3].view(world, 3)))
+            drgb_dst = (C.c_void_p * world)(*[p + 4 * (base + rank * P * 3) for p in ptrs])
+            cam_dst = (C.c_void_p * world)(*[p + 4 * (base + world * P * 3 + rank * 3) for p in ptrs])
+            dst.append((drgb_dst, cam_dst))
+        t.zero_()
+        torch.cuda.synchronize(dev)
+        dist.barrier(group=grp)
+        self._symm = {key: (t, hdl, views, dst)}
+        self._side = torch.cuda.Stream(dev)
+        return self._symm[key]
+
+    def arm(self, lib, campos, P, dev):
+        """Arm the next backward of this thread (called by the `_C` level in place of gsr_backward_early_rgb).
+        Returns (objects to keep alive until the backward returned, list receiving an exception of the callback)."""
+        from . import _lib
+        world = self._world()
+        errors = []
+        if self.ok and world > 1:
+            try:
+                t, hdl, views, dst = self._setup(world, P, dev)
+            except Exception as ex:        # collective failure: every rank takes the same branch
+                self.ok, self.why = False, repr(ex)
+        if not (self.ok and world > 1):
+            return None
+        drgb_dst, cam_dst = dst[self._parity]
+        campos = campos.reshape(3).contiguous()
+        side = self._side
+
+        def _ready(_user):
+            try:
+                with torch.cuda.stream(side):      # after the push kernel: all ranks' stores have landed once this passes
+                    hdl.barrier(channel=0)
+            except Exception as ex:                # never let an exception cross the C ABI
+                errors.append(ex)
+
+        cb = _lib.READY_FN(_ready)
+        _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
+                                                    C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
+        return (cb, campos, drgb_dst, cam_dst), errors
+
+    def finish(self, head, means3D, dsh_out, P, M, D):
+        world = self._world()
+        key = (world, P, str(dsh_out.device))
+        if not (self.ok and world > 1 and key in self._symm):
+            return super().finish(head, means3D, dsh_out, P, M, D)
+        t, hdl, views, dst = self._symm[key]
+        drgb_all, campos_all = views[self._parity]
+        self._parity ^= 1
+        w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        torch.cuda.current_stream(dsh_out.device).wait_stream(self._side)
+        (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
+        w_r.wait()
+
+
 def _rebuild_cuda(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
     from . import _lib
     if not dsh_out.is_cuda:
@@ -173,12 +264,13 @@ def _rebuild_cuda(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
     _lib.check(rc, "gsr_sh_grad_from_views")
 
 
-def install_factored_exchange(group=None, enable: bool = True, rebuild=None) -> None:
+def install_factored_exchange(group=None, enable: bool = True, rebuild=None, peer: bool = False) -> None:
     """One view per rank per step: every backward of both rasterizer packages (autograd or `_C` level) returns
-    gradients already summed over ranks, exchanged with FactoredExchange. Replaces install_backward_allreduce."""
+    gradients already summed over ranks, exchanged with FactoredExchange (peer=True: PeerExchange, the all-gather
+    done by the backward's own stores into peer memory). Replaces install_backward_allreduce."""
     from .diff_gaussian_rasterization import _C as c3
     from .diff_surfel_rasterization import _C as c2
-    fx = FactoredExchange(group, rebuild) if enable else None
+    fx = (PeerExchange(group, rebuild) if peer else FactoredExchange(group, rebuild)) if enable else None
     c3._factored[0] = fx
     c2._factored[0] = fx
     if enable:

@@ -1,0 +1,63 @@
+"""Run under torchrun with 2+ GPUs (tests/test_gpu_peer_exchange.py launches it): the peer-memory exchange
+(multiview.PeerExchange) must give every rank the same gradients as the NCCL FactoredExchange and as the dense
+all-reduce of the parameter-gradient arena, over several steps (double-buffer parity) and for both rasterizers."""
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT)); sys.path.insert(0, str(ROOT / "tests"))
+import helpers as h  # noqa: E402
+from scorp_b200 import multiview as mv, synth  # noqa: E402
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    ok = True
+    for surfel in (False, True):
+        sc = synth.make_scene("C4" if surfel else "C2", P=40_000, W=320, H=208, n_views=world).to("cuda")
+        fwd_f, bwd_f = (h.ours_surfel_forward, h.ours_surfel_backward) if surfel else (h.ours_forward, h.ours_backward)
+        cam = sc.cameras[rank]
+        grads = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 5 + rank, channels=(3, 7) if surfel else (3, 1, 1))]
+        fo = fwd_f(sc, cam)
+        keys = ("means3D", "sh", "opacity", "scales", "rotations")
+        # reference: plain backward + one all_reduce per tensor
+        ref = bwd_f(sc, cam, fo, grads)
+        ref = {k: ref[k].clone() for k in keys}
+        for k in keys:
+            dist.all_reduce(ref[k])
+        for mode in ("factored", "peer"):
+            mv.install_factored_exchange(enable=True, peer=(mode == "peer"))
+            try:
+                for step in range(3):       # three steps: both parities of the double buffer, and reuse
+                    out = bwd_f(sc, cam, fo, grads)
+                    torch.cuda.synchronize()
+                    for k in keys:
+                        good, worst = h.close(out[k], ref[k], rtol=1e-3, atol_scale=1e-5)
+                        if not good:
+                            ok = False
+                            print(f"rank {rank} surfel={surfel} {mode} step {step} {k}: worst ratio {worst}", flush=True)
+                if mode == "peer":
+                    from scorp_b200.diff_gaussian_rasterization import _C as c3
+                    fx = c3._factored[0]
+                    if rank == 0:
+                        print(f"peer exchange active: {fx.ok} {fx.why}", flush=True)
+                    if not fx.ok:
+                        ok = False
+            finally:
+                mv.install_factored_exchange(enable=False)
+    t = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("PEER_CHECK_OK" if int(t) == 1 else "PEER_CHECK_FAILED", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if int(t) == 1 else 1)
+
+
+if __name__ == "__main__":
+    main()
