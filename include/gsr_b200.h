@@ -241,6 +241,15 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
  * n_dst <= 0 disarms. */
 int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,
                                  void* side_stream, void (*ready)(void* user), void* user);
+/* Arms the NEXT gsr_rasterize_backward / gsr_surfel_backward of this thread (SH colours only) to ADD the four non-SH
+ * parameter gradients of its visible Gaussians into multicast_head -- the multicast (NVLS) address of a symmetric,
+ * zero-initialised buffer of P rows of 12 floats (means3D xyz, opacity | scales, rotations, padding), 16-byte
+ * aligned -- with 16-byte multimem.red operations, so the sum over ranks forms in the switch while the
+ * preprocess-backward kernel runs; dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations are then NOT written by
+ * that call. After a cross-rank barrier gsr_peer_consume un-interleaves this rank's replica into dst = the planar
+ * head [means3D 3P | opacity P | scales 3P (2P surfels) | rotations 4P] and clears the rows. NULL disarms. */
+int gsr_backward_peer_head(float* multicast_head);
+int gsr_peer_consume(float* symmetric_src, float* dst, int P, int surfel, void* stream);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
                            const float* drgb, float* dL_dsh, void* stream);
 

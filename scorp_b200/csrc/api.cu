@@ -56,6 +56,8 @@ uint32_t* readback_pad() {
 }
 
 thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false, {} };
+thread_local float* g_peer_head = nullptr;
+float* take_peer_head() { float* h = g_peer_head; g_peer_head = nullptr; return h; }
 EarlyRgb take_early_rgb() { const EarlyRgb e = g_early; g_early.armed = false; return e; }
 
 }  // namespace gsr
@@ -330,6 +332,7 @@ static int backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
+    b.mc_head = take_peer_head();
     if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");
@@ -339,6 +342,14 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void*), void* user) {
     if (!drgb) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false, {}}; return GSR_OK; }
     gsr::g_early = gsr::EarlyRgb{drgb, ready, user, true, {}};
     return GSR_OK;
+}
+
+int gsr_backward_peer_head(float* multicast_head) { gsr::g_peer_head = multicast_head; return GSR_OK; }
+
+int gsr_peer_consume(float* symmetric_src, float* dst, int P, int surfel, void* stream) {
+    if (P == 0) return GSR_OK;
+    if (P < 0 || !symmetric_src || !dst) { set_error("gsr_peer_consume: bad argument"); return GSR_EINVAL; }
+    return check_cuda(gsr::launch_peer_consume(symmetric_src, dst, P, surfel != 0, (cudaStream_t)stream), "peer consume launch");
 }
 
 int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,

@@ -110,10 +110,14 @@ struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; Pee
 EarlyRgb take_early_rgb();          // returns the armed request (armed == false if none) and disarms it
 cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                         int rgb_off, float* drgb, cudaStream_t st);
+// head rows [P][12] -> the planar arena head [means3D 3P | opacity P | scales 3P (2P) | rotations 4P], and clears the
+// rows for their next use
+cudaError_t launch_peer_consume(float* src, float* dst, int P, bool surfel, cudaStream_t st);
 // the same values written straight into every rank's gather buffer through peer pointers (all-gather by stores)
 cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                     int rgb_off, const PeerDst& dst, cudaStream_t main);
 
+float* take_peer_head();            // api.cu: multicast head armed for the next backward of this thread (NULL if none); disarms
 uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
 
 // error plumbing (api.cu)
@@ -190,6 +194,31 @@ __device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uin
     }
 }
 
+// multimem.red: ONE store-like instruction adds v into the same offset of every rank's replica of a multicast-mapped
+// buffer; the NVSwitch performs the reduction (NVLS). p must be a multicast address (symmetric memory).
+__device__ __forceinline__ void mc_add4(float4* p, float4 v) {
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+constexpr int PEER_HEAD_STRIDE = 12;        // floats per Gaussian in the switch-reduced head (three 16-byte groups)
+// CTA-wide: every thread brings the 12 head floats of its Gaussian (zeros if it has none); the rows are staged in
+// shared memory and leave as 16-byte multimem.red operations at consecutive addresses (a warp instruction covers
+// 512 contiguous bytes); all-zero groups (invisible Gaussians) are not sent. `stage` holds THREADS * 12 floats.
+template <int THREADS>
+__device__ __forceinline__ void peer_head_add(float* mc_head, size_t row0, int nrows, const float (&v)[PEER_HEAD_STRIDE],
+                                              float* stage) {
+    __syncthreads();                        // the staging area may alias a tile other threads are still reading
+#pragma unroll
+    for (int k = 0; k < PEER_HEAD_STRIDE; ++k) stage[threadIdx.x * PEER_HEAD_STRIDE + k] = v[k];
+    __syncthreads();
+    float4* dst = reinterpret_cast<float4*>(mc_head + row0 * PEER_HEAD_STRIDE);
+    const float4* src = reinterpret_cast<const float4*>(stage);
+    for (int e = threadIdx.x; e < nrows * (PEER_HEAD_STRIDE / 4); e += THREADS) {
+        const float4 q = src[e];
+        if (q.x != 0.0f || q.y != 0.0f || q.z != 0.0f || q.w != 0.0f) mc_add4(dst + e, q);
+    }
+}
+
 // cp.async 16-byte global->shared (LDGSTS), L2-only caching: the records are read once per CTA.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
@@ -242,6 +271,9 @@ struct BwdArgs {
     const float* opacities = nullptr;      // raw opacity (only read when raw)
     float* dL_dsh_rest = nullptr;
     bool raw = false;
+    // gsr_backward_peer_head: multicast address of the head [P][12] = (means3D xyz, opacity | scales xyz, rot r | rot xyz, 0);
+    // the four parameter gradients of visible Gaussians are ADDED there (in every rank's replica) instead of stored
+    float* mc_head = nullptr;
 };
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st);
 

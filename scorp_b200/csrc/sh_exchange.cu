@@ -71,6 +71,30 @@ cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* 
     return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(256)
+peer_consume_kernel(float* __restrict__ src, float* __restrict__ dst, int P, bool surfel) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g >= P) return;
+    float4* row = reinterpret_cast<float4*>(src + (size_t)g * PEER_HEAD_STRIDE);
+    const float4 a = row[0], b = row[1], c = row[2];
+    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+    row[0] = z; row[1] = z; row[2] = z;
+    const size_t Pz = (size_t)P;
+    dst[3 * (size_t)g] = a.x; dst[3 * (size_t)g + 1] = a.y; dst[3 * (size_t)g + 2] = a.z;
+    dst[3 * Pz + g] = a.w;
+    if (surfel) {       // scales 2, rotations 4
+        float* sc = dst + 4 * Pz + 2 * (size_t)g; sc[0] = b.x; sc[1] = b.y;
+        float* rq = dst + 6 * Pz + 4 * (size_t)g; rq[0] = b.z; rq[1] = b.w; rq[2] = c.x; rq[3] = c.y;
+    } else {            // scales 3, rotations 4
+        float* sc = dst + 4 * Pz + 3 * (size_t)g; sc[0] = b.x; sc[1] = b.y; sc[2] = b.z;
+        float* rq = dst + 7 * Pz + 4 * (size_t)g; rq[0] = b.w; rq[1] = c.x; rq[2] = c.y; rq[3] = c.z;
+    }
+}
+cudaError_t launch_peer_consume(float* src, float* dst, int P, bool surfel, cudaStream_t st) {
+    peer_consume_kernel<<<(P + 255) / 256, 256, 0, st>>>(src, dst, P, surfel);
+    return cudaGetLastError();
+}
+
 // One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
 // sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
 template <int M3>

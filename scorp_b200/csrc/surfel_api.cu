@@ -223,6 +223,7 @@ static int surfel_backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dtransMat = dL_dtransMat; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
+    b.mc_head = take_peer_head();
     if ((rc = check_cuda(launch_surfel_preprocess_backward(b, st), "surfel preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "surfel preprocess backward");

@@ -14,6 +14,7 @@ host-side logic).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Iterable, List, Optional, Sequence
 
 import torch
@@ -171,7 +172,10 @@ class PeerExchange(FactoredExchange):
     synchronisation. The gather buffers live in torch symmetric memory (torch.distributed._symmetric_memory: peer
     pointers + barrier) and are double-buffered by step parity, so a fast rank's next push cannot overwrite what a
     slow rank's rebuild kernel is still reading (the barrier bounds the skew to one step). The 11 / 10 non-SH floats
-    are still all-reduced by NCCL (NVLS in-switch reduction), underneath the rebuild kernel.
+    are reduced IN THE SWITCH by the preprocess-backward kernel itself when the symmetric buffer has a multicast
+    mapping (NVLS): it adds its visible rows into every rank's head with multimem.red (gsr_backward_peer_head), and
+    gsr_peer_consume hands the sum over after the barrier -- a step then contains no NCCL call at all. Without
+    multicast support they are all-reduced by NCCL underneath the rebuild kernel.
 
     Construction is collective. If symmetric memory cannot be set up (no P2P access, a backend without it), `ok` is
     False and the object behaves exactly like FactoredExchange (NCCL all-gather): both are GPU paths of this library."""
@@ -190,24 +194,32 @@ class PeerExchange(FactoredExchange):
             return self._symm[key]
         import torch.distributed._symmetric_memory as symm
         grp = self.group if self.group is not None else dist.group.WORLD
-        half = world * P * 3 + world * 4
+        r4 = lambda n: (n + 3) // 4 * 4
+        n_rgb, n_cam, n_head = r4(world * P * 3), r4(world * 3), P * 12
+        half = n_rgb + n_cam + n_head              # one parity: gathered drgb | gathered campos | switch-reduced head
         t = symm.empty(2 * half, dtype=torch.float32, device=dev)
         hdl = symm.rendezvous(t, grp)
         rank = dist.get_rank(grp)
         ptrs = [int(p) for p in hdl.buffer_ptrs]
-        views, dst = [], []
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        if os.environ.get("GSR_PEER_NO_MULTICAST"):
+            mc = 0
+        views, dst, heads = [], [], []
         for b in range(2):
             base = b * half
             views.append((t[base: base + world * P * 3].view(world, P, 3),
-                          t[base + world * P * 3: base + world * P * 3 + world * 3].view(world, 3)))
+                          t[base + n_rgb: base + n_rgb + world * 3].view(world, 3)))
             drgb_dst = (C.c_void_p * world)(*[p + 4 * (base + rank * P * 3) for p in ptrs])
-            cam_dst = (C.c_void_p * world)(*[p + 4 * (base + world * P * 3 + rank * 3) for p in ptrs])
+            cam_dst = (C.c_void_p * world)(*[p + 4 * (base + n_rgb + rank * 3) for p in ptrs])
             dst.append((drgb_dst, cam_dst))
+            h0 = base + n_rgb + n_cam
+            heads.append((t[h0: h0 + P * 12], (mc + 4 * h0) if mc else 0))
         t.zero_()
         torch.cuda.synchronize(dev)
         dist.barrier(group=grp)
-        self._symm = {key: (t, hdl, views, dst)}
+        self._symm = {key: (t, hdl, views, dst, heads)}
         self._side = torch.cuda.Stream(dev)
+        self.multicast = bool(mc)
         return self._symm[key]
 
     def arm(self, lib, campos, P, dev):
@@ -218,7 +230,7 @@ class PeerExchange(FactoredExchange):
         errors = []
         if self.ok and world > 1:
             try:
-                t, hdl, views, dst = self._setup(world, P, dev)
+                t, hdl, views, dst, heads = self._setup(world, P, dev)
             except Exception as ex:        # collective failure: every rank takes the same branch
                 self.ok, self.why = False, repr(ex)
         if not (self.ok and world > 1):
@@ -226,8 +238,11 @@ class PeerExchange(FactoredExchange):
         drgb_dst, cam_dst = dst[self._parity]
         campos = campos.reshape(3).contiguous()
         side = self._side
+        use_mc = heads[self._parity][1] != 0
 
         def _ready(_user):
+            if use_mc:
+                return                             # one barrier on the main stream in finish() covers push and head
             try:
                 with torch.cuda.stream(side):      # after the push kernel: all ranks' stores have landed once this passes
                     hdl.barrier(channel=0)
@@ -237,6 +252,8 @@ class PeerExchange(FactoredExchange):
         cb = _lib.READY_FN(_ready)
         _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
                                                     C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
+        if use_mc:      # the four non-SH gradients are added into every rank's head by the preprocess-backward kernel
+            _lib.check(lib.gsr_backward_peer_head(C.c_void_p(heads[self._parity][1])), "gsr_backward_peer_head")
         return (cb, campos, drgb_dst, cam_dst), errors
 
     def finish(self, head, means3D, dsh_out, P, M, D):
@@ -244,11 +261,24 @@ class PeerExchange(FactoredExchange):
         key = (world, P, str(dsh_out.device))
         if not (self.ok and world > 1 and key in self._symm):
             return super().finish(head, means3D, dsh_out, P, M, D)
-        t, hdl, views, dst = self._symm[key]
+        from . import _lib
+        t, hdl, views, dst, heads = self._symm[key]
         drgb_all, campos_all = views[self._parity]
+        head_sym, mc = heads[self._parity]
         self._parity ^= 1
+        dev = dsh_out.device
+        main = torch.cuda.current_stream(dev)
+        if mc:
+            # push kernel (side stream) and preprocess-backward (this stream) of EVERY rank are complete after this
+            main.wait_stream(self._side)
+            hdl.barrier(channel=0)
+            with torch.cuda.device(dev):
+                _lib.check(_lib.lib().gsr_peer_consume(head_sym.data_ptr(), head.data_ptr(), P, int(head.numel() == 10 * P),
+                                                       C.c_void_p(main.cuda_stream)), "gsr_peer_consume")
+            (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
+            return
         w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
-        torch.cuda.current_stream(dsh_out.device).wait_stream(self._side)
+        main.wait_stream(self._side)
         (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
         w_r.wait()
 

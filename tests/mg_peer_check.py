@@ -46,7 +46,7 @@ def main():
                     from scorp_b200.diff_gaussian_rasterization import _C as c3
                     fx = c3._factored[0]
                     if rank == 0:
-                        print(f"peer exchange active: {fx.ok} {fx.why}", flush=True)
+                        print(f"peer exchange active: {fx.ok} multicast={getattr(fx, 'multicast', None)} {fx.why}", flush=True)
                     if not fx.ok:
                         ok = False
             finally:
