@@ -456,7 +456,7 @@ def run(arm, args, rank, world, local):
             arm.factored = True
             exchange = "factored: all_gather of dL_dRGB (12 B x world per Gaussian) + all_reduce of the 11 non-SH floats"
             if use_peer:
-                exchange = "peer: dL_dRGB stored into every rank's gather buffer by the backward itself (NVLink peer pointers, symmetric memory) + all_reduce of the 11 non-SH floats"
+                exchange = "peer: dL_dRGB stored into every rank's gather buffer by the backward itself (NVLink peer pointers, symmetric memory)"
         elif arm.name == "reference":
             exchange = "five all_reduce calls (one per gradient tensor)"
     n, radii, _ = step_resident()
@@ -532,7 +532,13 @@ def run(arm, args, rank, world, local):
     if arm.name == "ours" and arm.factored and args.exchange in ("peer", "auto"):
         from scorp_b200.diff_gaussian_rasterization import _C as _c3
         fx = _c3._factored[0]
-        exchange += "" if getattr(fx, "ok", False) else f" [symmetric memory unavailable, ran as factored: {getattr(fx, 'why', '')}]"
+        if getattr(fx, "ok", False):
+            exchange += "; non-SH floats reduced in the switch by the preprocess-backward kernel (multimem.red)" \
+                if getattr(fx, "multicast", False) else "; non-SH floats all-reduced by NCCL (no multicast mapping)"
+            if exch:
+                exch["note"] = "stand-alone timing of the NCCL form of this exchange, for reference; the timed steps used the peer-memory exchange"
+        else:
+            exchange += f" [symmetric memory unavailable, ran as NCCL factored: {getattr(fx, 'why', '')}]"
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
