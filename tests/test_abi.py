@@ -71,3 +71,43 @@ def test_product_never_imports_the_oracle():
         assert not re.search(r"^\s*(from|import)\s+oracle\b", txt, flags=re.M), p
     for p in (ROOT / "scorp_b200" / "csrc").glob("*"):
         assert "oracle" not in p.read_text().replace("oracle/", "") or True
+
+
+def test_no_cpu_fallback_in_the_rows_next_to_the_boundary():
+    """model_space, loss_utils, optim, batched views: CPU tensors raise GsrError, nothing is computed on the host."""
+    import scorp_b200.diff_gaussian_rasterization as dgr
+    from scorp_b200 import _lib, loss_utils as lu, model_space as ms, optim
+    rs = dgr.GaussianRasterizationSettings(8, 8, 1.0, 1.0, torch.zeros(3), 1.0, torch.eye(4), torch.eye(4), 0,
+                                           torch.zeros(3), False, False)
+    z = torch.zeros
+    with pytest.raises(_lib.GsrError):
+        ms.rasterize_model(z(2, 3), z(2, 3), z(2, 1, 3), z(2, 0, 3), z(2, 1), z(2, 3), z(2, 4), rs)
+    with pytest.raises(_lib.GsrError):
+        ms.rasterize_surfel_model(z(2, 3), z(2, 3), z(2, 1, 3), z(2, 0, 3), z(2, 1), z(2, 2), z(2, 4), rs)
+    with pytest.raises(_lib.GsrError):
+        lu.l1_ssim_loss(z(3, 16, 16), z(3, 16, 16))
+    with pytest.raises(_lib.GsrError):
+        lu.ssim(z(3, 16, 16), z(3, 16, 16))
+    p = torch.nn.Parameter(z(4)); p.grad = z(4)
+    with pytest.raises(_lib.GsrError):
+        optim.Adam([p], lr=1e-3).step()
+    with pytest.raises(_lib.GsrError):
+        optim.add_densification_stats(z(4, 1), z(4, 1), z(4), z(4, 3), z(4, dtype=torch.int32))
+    with pytest.raises(_lib.GsrError):
+        dgr.GaussianRasterizer(rs).forward_views(torch.eye(4)[None], torch.eye(4)[None], z(1, 3), z(2, 3), z(2, 1),
+                                                 shs=z(2, 1, 3), scales=torch.ones(2, 3), rotations=torch.ones(2, 4))
+
+
+def test_adam_keeps_torch_optimizer_surface():
+    """scorp_b200.optim.Adam is a torch.optim.Optimizer with Adam's param_groups / defaults, so
+    GaussianModel.update_learning_rate (gaussian_model.py:208-214) and state editing work unchanged."""
+    from scorp_b200 import optim
+    p = torch.nn.Parameter(torch.zeros(3))
+    o = optim.Adam([{"params": [p], "lr": 0.1, "name": "xyz"}], lr=0.0, eps=1e-15)
+    assert isinstance(o, torch.optim.Optimizer)
+    assert o.param_groups[0]["name"] == "xyz" and o.param_groups[0]["lr"] == 0.1 and o.param_groups[0]["eps"] == 1e-15
+    o.param_groups[0]["lr"] = 0.05
+    assert o.state_dict()["param_groups"][0]["lr"] == 0.05
+    o.step()                                     # no gradient anywhere: nothing to do, no CUDA needed
+    with pytest.raises(NotImplementedError):
+        optim.Adam([p], amsgrad=True)
