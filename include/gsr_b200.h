@@ -310,6 +310,53 @@ int gsr_adam_step(int n_groups, const GsrAdamGroup* groups, double beta1, double
 int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, int grad_stride,
                             float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
 
+/* --- densify_and_prune ------------------------------------------------------------------------------------------
+ * Replaces GaussianModel.densify_and_prune (gs3dgs/scene/gaussian_model.py:572-586, gs2dgs/scene/gaussian_model.py:
+ * 478-492) with everything below it: densify_and_clone (:559-570), densify_and_split (:502-527),
+ * densification_postfix (:482-500), cat_tensors_to_optimizer (:460-480), prune_points (:443-458). The reference's four
+ * rounds of mask indexing and torch.cat become one per-Gaussian decision (plan) and one gather of every surviving row
+ * of the parameters and Adam moments (apply). Result rows, in the reference's order: surviving originals, surviving
+ * clones, then the n_split copies of the surviving split children (copy-major).
+ * Thresholds are the reference's Python floats rounded to float:
+ *   grad_threshold = max_grad, dense_extent = percent_dense * extent, min_opacity, big_extent = 0.1 * extent,
+ *   prune_big = bool(max_screen_size), max_screen_size (only its sign matters: max_radii2D has just been zeroed,
+ *   :498), n_split = N (2). */
+typedef struct GsrDensifyCfg {
+    float grad_threshold;
+    float dense_extent;
+    float min_opacity;
+    float big_extent;
+    float max_screen_size;
+    int   prune_big;
+    int   n_split;
+} GsrDensifyCfg;
+size_t gsr_densify_workspace_bytes(int P, int n_split);
+/* Plan. scaling [P][scale_dim] (3: 3DGS, 2: 2DGS) and opacity [P] are the STORED (pre-activation) tensors;
+ * xyz_gradient_accum, denom [P]. Writes the decision into workspace and returns, after one stream synchronisation,
+ * counts = { surviving originals, surviving clones, surviving split parents (each yields n_split rows),
+ *            split-selected Gaussians before the prune (the reference draws n_split * counts[3] normal samples) }. */
+int gsr_densify_plan(int P, int scale_dim, const float* scaling, const float* opacity, const float* xyz_gradient_accum,
+                     const float* denom, const GsrDensifyCfg* cfg, void* workspace, int32_t counts[4], void* stream);
+#define GSR_DENSIFY_COPY    0   /* rows are copied                                                   */
+#define GSR_DENSIFY_XYZ     1   /* children: R(rotation) . (normal * exp(scaling)) + xyz     (:511-515) */
+#define GSR_DENSIFY_SCALING 2   /* children: log(exp(scaling) / (0.8 * n_split))             (:516)     */
+typedef struct GsrDensifyGroup {
+    const float* param;         /* [P][width]                                         */
+    const float* exp_avg;       /* [P][width] or NULL (no optimizer state yet)        */
+    const float* exp_avg_sq;
+    float*       out_param;     /* [rows][width], rows = counts[0] + counts[1] + n_split * counts[2] */
+    float*       out_exp_avg;   /* [rows][width] or NULL; new rows are zero           */
+    float*       out_exp_avg_sq;
+    int          width;
+    int          kind;
+} GsrDensifyGroup;
+/* Apply the plan held in workspace: up to 8 groups in one gather launch. rotation [P][4] and scaling [P][scale_dim]
+ * are the stored tensors, normals [n_split * counts[3]][3] standard normal samples (what torch.normal draws before it
+ * scales by std); needed only when a GSR_DENSIFY_XYZ group is present and counts[2] > 0. No synchronisation. */
+int gsr_densify_apply(int P, int scale_dim, const GsrDensifyCfg* cfg, void* workspace, const int32_t counts[4],
+                      int n_groups, const GsrDensifyGroup* groups, const float* rotation, const float* scaling,
+                      const float* normals, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

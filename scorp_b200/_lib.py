@@ -46,6 +46,18 @@ class GsrAdamGroup(C.Structure):
                 ("n", C.c_int64), ("lr", C.c_double)]
 
 
+class GsrDensifyCfg(C.Structure):
+    """struct GsrDensifyCfg (include/gsr_b200.h)."""
+    _fields_ = [("grad_threshold", c_float), ("dense_extent", c_float), ("min_opacity", c_float),
+                ("big_extent", c_float), ("max_screen_size", c_float), ("prune_big", c_int), ("n_split", c_int)]
+
+
+class GsrDensifyGroup(C.Structure):
+    """struct GsrDensifyGroup (include/gsr_b200.h)."""
+    _fields_ = [("param", c_void_p), ("exp_avg", c_void_p), ("exp_avg_sq", c_void_p), ("out_param", c_void_p),
+                ("out_exp_avg", c_void_p), ("out_exp_avg_sq", c_void_p), ("width", c_int), ("kind", c_int)]
+
+
 _P = c_void_p
 # name -> (restype, argtypes); every symbol include/gsr_b200.h declares
 SIGNATURES = {
@@ -70,6 +82,10 @@ SIGNATURES = {
                                     + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_adam_step": (c_int, [c_int, C.POINTER(GsrAdamGroup), C.c_double, C.c_double, C.c_double, c_int, _P]),
     "gsr_densification_stats": (c_int, [c_int, _P, _P, c_int, _P, _P, _P, _P]),
+    "gsr_densify_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "gsr_densify_plan": (c_int, [c_int, c_int, _P, _P, _P, _P, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), _P]),
+    "gsr_densify_apply": (c_int, [c_int, c_int, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), c_int,
+                                  C.POINTER(GsrDensifyGroup), _P, _P, _P, _P]),
     "gsr_l1_ssim_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_l1_ssim_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, c_size_t, _P]),
     "gsr_l1_ssim_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),

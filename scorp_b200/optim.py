@@ -10,6 +10,11 @@ launch (csrc/optim.cu) and is bit-identical to torch's default (foreach) impleme
 
 `add_densification_stats(model_or_tensors, ...)` is train_3dgs.py:180-181 + gaussian_model.py:603-605 in one launch
 without the host synchronisation of boolean-mask indexing. CUDA tensors only: there is no CPU path.
+
+`densify_and_prune(gaussians, max_grad, min_opacity, extent, max_screen_size)` is GaussianModel.densify_and_prune
+(gaussian_model.py:572-586; gs2dgs/scene/gaussian_model.py:478-492) with the model as first argument: clone, split,
+prune of the six parameter tensors and their Adam moments in one plan + one gather (csrc/densify.cu) instead of four
+rounds of mask indexing and torch.cat. `densify_and_prune_tensors` is the same on plain tensors.
 """
 from __future__ import annotations
 
@@ -19,7 +24,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["Adam", "add_densification_stats"]
+__all__ = ["Adam", "add_densification_stats", "densify_and_prune", "densify_and_prune_tensors"]
 
 
 class Adam(torch.optim.Optimizer):
@@ -94,3 +99,114 @@ def add_densification_stats(xyz_gradient_accum, denom, max_radii2D, viewspace_gr
                                          _lib.ptr(max_radii2D) if max_radii2D is not None else None,
                                          C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
     _lib.check(rc, "gsr_densification_stats")
+
+
+# optimizer group name -> (GaussianModel attribute, gather kind); gaussian_model.py:193-200
+_GROUPS = (("xyz", "_xyz", 1), ("f_dc", "_features_dc", 0), ("f_rest", "_features_rest", 0),
+           ("opacity", "_opacity", 0), ("scaling", "_scaling", 2), ("rotation", "_rotation", 0))
+
+
+def densify_and_prune_tensors(params, moments, xyz_gradient_accum, denom, max_grad, min_opacity, extent,
+                              max_screen_size, percent_dense, N=2, normals=None, generator=None):
+    """The whole clone / split / prune sequence on plain tensors.
+
+    params:  {"xyz": [P,3], "f_dc": [P,1,3], "f_rest": [P,R,3], "opacity": [P,1], "scaling": [P,3|2], "rotation": [P,4]}
+             stored (pre-activation) CUDA fp32 tensors.
+    moments: {name: (exp_avg, exp_avg_sq)} for the groups that have optimizer state (others: absent or None).
+    normals: [N * n_selected, 3] standard normal samples; drawn with `generator` when None, with the shape the
+             reference's torch.normal call draws (gaussian_model.py:511-513), so the same seed gives the same children.
+    Returns (new_params, new_moments, counts) with counts = (kept originals, clones, split parents kept, selected)."""
+    lib = _lib.lib()
+    xyz = params["xyz"]
+    if not xyz.is_cuda:
+        raise _lib.GsrError("densify_and_prune needs CUDA tensors: there is no CPU path")
+    dev, P = xyz.device, xyz.shape[0]
+    src = {}
+    for name, _, _ in _GROUPS:
+        t = params[name]
+        if t.dtype != torch.float32 or t.shape[0] != P or t.device != dev:
+            raise RuntimeError(f"{name}: expected an fp32 tensor with {P} rows on {dev}")
+        src[name] = t.detach().contiguous()
+    scale_dim = src["scaling"].shape[1]
+    if src["rotation"].shape[1:] != (4,) or src["xyz"].shape[1:] != (3,) or src["opacity"].numel() != P:
+        raise RuntimeError("expected xyz [P,3], opacity [P,1], rotation [P,4]")
+    acc, den = xyz_gradient_accum.detach().contiguous(), denom.detach().contiguous()
+    if acc.numel() != P or den.numel() != P or acc.dtype != torch.float32 or den.dtype != torch.float32:
+        raise RuntimeError("xyz_gradient_accum and denom must be fp32 with one element per Gaussian")
+    cfg = _lib.GsrDensifyCfg(float(max_grad), float(percent_dense * extent), float(min_opacity), float(0.1 * extent),
+                             float(max_screen_size) if max_screen_size else 0.0, 1 if max_screen_size else 0, int(N))
+    stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    counts = (C.c_int32 * 4)()
+    with torch.cuda.device(dev):
+        ws = torch.empty(max(int(lib.gsr_densify_workspace_bytes(P, int(N))), 16), dtype=torch.uint8, device=dev)
+        _lib.check(lib.gsr_densify_plan(P, scale_dim, _lib.ptr(src["scaling"]), _lib.ptr(src["opacity"]), _lib.ptr(acc),
+                                        _lib.ptr(den), C.byref(cfg), _lib.ptr(ws), counts, stream), "gsr_densify_plan")
+        n_keep, n_clone, n_child, n_sel = (int(c) for c in counts)
+        rows = n_keep + n_clone + int(N) * n_child
+        if normals is None:
+            normals = torch.empty((int(N) * n_sel, 3), device=dev).normal_(generator=generator)
+        if normals.shape != (int(N) * n_sel, 3) or normals.dtype != torch.float32 or normals.device != dev:
+            raise RuntimeError(f"normals: expected fp32 [{int(N) * n_sel}, 3] on {dev}")
+        normals = normals.contiguous()
+        arr = (_lib.GsrDensifyGroup * len(_GROUPS))()
+        out, out_m, keep = {}, {}, []
+        for a, (name, _, kind) in zip(arr, _GROUPS):
+            t = src[name]
+            out[name] = torch.empty((rows,) + tuple(t.shape[1:]), device=dev)
+            mv = (moments or {}).get(name)
+            a.param, a.out_param = _lib.ptr(t), _lib.ptr(out[name])
+            a.width, a.kind = (t.numel() // P if P else 0), kind
+            if mv is not None:
+                m, v = (x.detach().contiguous() for x in mv)
+                if m.shape != t.shape or v.shape != t.shape:
+                    raise RuntimeError(f"{name}: optimizer moments do not have the parameter's shape")
+                out_m[name] = (torch.empty_like(out[name]), torch.empty_like(out[name]))
+                a.exp_avg, a.exp_avg_sq = _lib.ptr(m), _lib.ptr(v)
+                a.out_exp_avg, a.out_exp_avg_sq = _lib.ptr(out_m[name][0]), _lib.ptr(out_m[name][1])
+                keep.append((m, v))          # the contiguous copies live until the launch is queued
+        live = [g for g in arr if g.width > 0 and rows > 0]
+        if P and rows:
+            packed = (_lib.GsrDensifyGroup * len(live))(*live)
+            _lib.check(lib.gsr_densify_apply(P, scale_dim, C.byref(cfg), _lib.ptr(ws), counts, len(live), packed,
+                                             _lib.ptr(src["rotation"]), _lib.ptr(src["scaling"]), _lib.ptr(normals),
+                                             stream), "gsr_densify_apply")
+    return out, out_m, (n_keep, n_clone, n_child, n_sel)
+
+
+@torch.no_grad()
+def densify_and_prune(gaussians, max_grad, min_opacity, extent, max_screen_size, N=2, generator=None, empty_cache=True):
+    """GaussianModel.densify_and_prune (gaussian_model.py:572-586) on a GaussianModel-shaped object: replaces the six
+    nn.Parameters and the optimizer's per-group state exactly as cat_tensors_to_optimizer / _prune_optimizer leave them
+    (new nn.Parameter per group, state moved to it, `step` kept), and zeroes xyz_gradient_accum, denom, max_radii2D
+    at the new size (densification_postfix :496-498)."""
+    opt = gaussians.optimizer
+    by_name = {g["name"]: g for g in opt.param_groups}
+    params, moments = {}, {}
+    for name, attr, _ in _GROUPS:
+        params[name] = getattr(gaussians, attr)
+        st = opt.state.get(by_name[name]["params"][0], None) if name in by_name else None
+        if st is not None and "exp_avg" in st:
+            moments[name] = (st["exp_avg"], st["exp_avg_sq"])
+    out, out_m, counts = densify_and_prune_tensors(params, moments, gaussians.xyz_gradient_accum, gaussians.denom, max_grad,
+                                                   min_opacity, extent, max_screen_size, gaussians.percent_dense, N=N,
+                                                   generator=generator)
+    for name, attr, _ in _GROUPS:
+        new = torch.nn.Parameter(out[name].requires_grad_(True))
+        if name in by_name:
+            group = by_name[name]
+            old = group["params"][0]
+            st = opt.state.get(old, None)
+            if st is not None:
+                if name in out_m:
+                    st["exp_avg"], st["exp_avg_sq"] = out_m[name]
+                del opt.state[old]
+                opt.state[new] = st
+            group["params"][0] = new
+        setattr(gaussians, attr, new)
+    rows, dev = out["xyz"].shape[0], out["xyz"].device
+    gaussians.xyz_gradient_accum = torch.zeros((rows, 1), device=dev)
+    gaussians.denom = torch.zeros((rows, 1), device=dev)
+    gaussians.max_radii2D = torch.zeros((rows,), device=dev)
+    if empty_cache:
+        torch.cuda.empty_cache()          # as the reference does (:586)
+    return counts

@@ -94,6 +94,9 @@ def test_no_cpu_fallback_in_the_rows_next_to_the_boundary():
     with pytest.raises(_lib.GsrError):
         optim.add_densification_stats(z(4, 1), z(4, 1), z(4), z(4, 3), z(4, dtype=torch.int32))
     with pytest.raises(_lib.GsrError):
+        optim.densify_and_prune_tensors(dict(xyz=z(4, 3), f_dc=z(4, 1, 3), f_rest=z(4, 0, 3), opacity=z(4, 1), scaling=z(4, 3),
+                                             rotation=torch.ones(4, 4)), {}, z(4, 1), z(4, 1), 0.0002, 0.005, 4.0, 20, 0.01)
+    with pytest.raises(_lib.GsrError):
         dgr.GaussianRasterizer(rs).forward_views(torch.eye(4)[None], torch.eye(4)[None], z(1, 3), z(2, 3), z(2, 1),
                                                  shs=z(2, 1, 3), scales=torch.ones(2, 3), rotations=torch.ones(2, 4))
 

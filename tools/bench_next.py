@@ -194,6 +194,41 @@ def row_optim(cfg, K, W):
             "densification_stats": {"torch_mask_indexing_ms": t_rs, "fused_ms": t_fs, "speedup": t_rs / t_fs}}
 
 
+def row_densify(cfg, K, W):
+    """8(f) rank 4: GaussianModel.densify_and_prune on a C2-sized model with Adam moments -- the reference's rounds of
+    mask indexing and torch.cat (tools/torch_densify_sequence.py) against the plan + gather kernels."""
+    sys.path.insert(0, str(ROOT / "tools"))
+    from torch_densify_sequence import ATTR, model, torch_sequence
+    from scorp_b200 import optim
+    P = synth.CONFIGS[cfg]["P"]; M = (synth.CONFIGS[cfg]["sh_degree"] + 1) ** 2
+    pc = model(P, M - 1, 3, seed=1)
+    par = {n: getattr(pc, a).detach() for n, a in ATTR.items()}
+    mom = {n: (pc.optimizer.state[getattr(pc, a)]["exp_avg"], pc.optimizer.state[getattr(pc, a)]["exp_avg_sq"])
+           for n, a in ATTR.items() if par[n].numel()}
+    args = (0.0002, 0.005, 4.0, 20, 0.01)
+    K, W = min(K, 10), min(W, 3)
+    t_torch, sp_t = timeit(lambda: torch_sequence(par, mom, pc.xyz_gradient_accum, pc.denom, *args), K, W)
+    res = {}
+
+    def fused():
+        res["out"] = optim.densify_and_prune_tensors(par, mom, pc.xyz_gradient_accum, pc.denom, *args)
+    t_fused, sp_f = timeit(fused, K, W)
+    out, _, counts = res["out"]
+    rows = out["xyz"].shape[0]
+    floats = sum(t.numel() // max(P, 1) for t in par.values())
+    # read the surviving source rows of parameters and moments once, write every output row once (moments of new rows
+    # are zeros that still have to be written), plus the plan's inputs (scaling, opacity, accum, denom)
+    bytes_ = 4 * floats * (counts[0] * 3 + (rows - counts[0])) + 4 * floats * rows * 3 + P * (12 + 4 + 4 + 4)
+    pk, src = peak()
+    return {"row": "8f-4 densify_and_prune", "config": cfg, "P": P, "rows_after": rows, "counts": list(counts),
+            "unit": "ms per densify_and_prune (six parameter tensors + twelve Adam moment tensors)",
+            "torch_sequence_ms": t_torch, "fused_ms": t_fused, "speedup": t_torch / t_fused,
+            "spread": {"torch": sp_t, "fused": sp_f},
+            "roofline": {"bound": "hbm", "peak": pk, "peak_source": src, "unit": "GB/s", "algorithmic_bytes": bytes_,
+                         "achieved": bytes_ / t_fused / 1e6, "frac": bytes_ / t_fused / 1e6 / pk,
+                         "note": "whole call including the count readback, output allocation and the normal draw"}}
+
+
 def row_iteration(cfg, K, W):
     """One whole training iteration as train_3dgs.py:85-193 runs it -- staging, render, loss, backward, densification
     statistics, optimizer step -- (a) with the reference's torch code around the stock drop-in rasterizer, (b) with
@@ -274,7 +309,8 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("needs a CUDA device")
     for r in args.rows.split(","):
-        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim, "iteration": row_iteration}[r]
+        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim, "densify": row_densify,
+              "iteration": row_iteration}[r]
         print(json.dumps(fn(args.config, args.steps, args.warmup)), flush=True)
 
 
