@@ -48,8 +48,12 @@ for cfg, kw, mod in (("C2", dict(P=5000, W=150, H=90), dgr), ("C1", dict(P=3000,
     for p_, t in zip(params, [t for t in st if t.numel()]):
         p_.grad = t.grad
     optim.Adam([{"params": [p_], "lr": 1e-3} for p_ in params], lr=0.0, eps=1e-15).step()
+    # densify_and_prune at an odd size (the statistics just accumulated decide who is cloned / split)
+    names = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
+    dn, _, cnt = optim.densify_and_prune_tensors({n_: t.detach() for n_, t in zip(names, st)}, {}, accum * 50, den, 0.0002, 0.005,
+                                                 4.0, 20, 0.01)
     torch.cuda.synchronize()
-    print("model-space", cfg, kw, "loss", float(loss.detach()), "stats", float(den.sum()))
+    print("model-space", cfg, kw, "loss", float(loss.detach()), "stats", float(den.sum()), "densify", cnt, tuple(dn["xyz"].shape))
 sc = synth.make_scene("C5", P=4000, W=100, H=80, n_views=5, rotations_npz=synth.random_rotations(5)).to("cuda")
 cams = sc.cameras
 E = torch.Tensor([])
