@@ -357,6 +357,22 @@ int gsr_densify_apply(int P, int scale_dim, const GsrDensifyCfg* cfg, void* work
                       int n_groups, const GsrDensifyGroup* groups, const float* rotation, const float* scaling,
                       const float* normals, void* stream);
 
+/* --- PLY vertex rows ---------------------------------------------------------------------------------------------
+ * The tensor shuffling of GaussianModel.save_ply / load_ply (gs3dgs/scene/gaussian_model.py:220-251, 287-332; same
+ * pair in gs2dgs/scene/gaussian_model.py) as one kernel each, so the model crosses PCIe in a single copy. A vertex row
+ * is  x y z nx ny nz f_dc_0..2 f_rest_0..3R-1 opacity scale_0..S-1 rot_0..3  (float32, normals zero, SH channel-major:
+ * f_rest_{c*R+k} = features_rest[i][k][c], :238-239). The PLY header is written / parsed by the host layer
+ * (scorp_b200/ply_io.py). */
+int gsr_ply_row_floats(int sh_rest, int scale_dim);
+/* rows [P][gsr_ply_row_floats(sh_rest, scale_dim)] (device) <- the stored model tensors (sh_rest = R coefficients
+ * per channel besides DC; features_rest may be NULL when R == 0). */
+int gsr_ply_pack(int P, int sh_rest, int scale_dim, const GsrModelParams* model, float* rows, void* stream);
+/* The inverse for any property order: rows [P][row_floats] (device, float32 properties only) and a HOST array
+ * columns[3 + 3 + 3R + 1 + S + 4] giving, for every model float in the order xyz, features_dc[c], features_rest[k][c],
+ * opacity, scaling, rotation, the column of the row it is read from. `out` tensors have GsrModelParams' shapes. */
+int gsr_ply_unpack(int P, int row_floats, const float* rows, const int32_t* columns, int sh_rest, int scale_dim,
+                   const GsrModelGrads* out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -86,6 +86,9 @@ SIGNATURES = {
     "gsr_densify_plan": (c_int, [c_int, c_int, _P, _P, _P, _P, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), _P]),
     "gsr_densify_apply": (c_int, [c_int, c_int, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), c_int,
                                   C.POINTER(GsrDensifyGroup), _P, _P, _P, _P]),
+    "gsr_ply_row_floats": (c_int, [c_int, c_int]),
+    "gsr_ply_pack": (c_int, [c_int, c_int, c_int, C.POINTER(GsrModelParams), _P, _P]),
+    "gsr_ply_unpack": (c_int, [c_int, c_int, _P, C.POINTER(C.c_int32), c_int, c_int, C.POINTER(GsrModelGrads), _P]),
     "gsr_l1_ssim_workspace_bytes": (c_size_t, [c_int, c_int, c_int]),
     "gsr_l1_ssim_forward": (c_int, [c_int, c_int, c_int, _P, _P, c_float, _P, _P, c_size_t, _P]),
     "gsr_l1_ssim_backward": (c_int, [c_int, c_int, c_int, _P, _P, _P, c_float, c_float, _P, _P, _P]),

@@ -229,6 +229,77 @@ def row_densify(cfg, K, W):
                          "note": "whole call including the count readback, output allocation and the normal draw"}}
 
 
+def row_ply(cfg, K, W):
+    """8(f) rank 4, last item: save_ply / load_ply of a C2-sized model. The torch/numpy arm is the reference's own statement
+    sequence (gaussian_model.py:236-247 and :292-326) without the plyfile call that follows it, which is not in this image:
+    it is charged only for building / consuming the structured array, so the real reference is slower than this arm."""
+    import os
+    import tempfile
+    import time
+    from scorp_b200 import ply_io
+    P = synth.CONFIGS[cfg]["P"]; R = (synth.CONFIGS[cfg]["sh_degree"] + 1) ** 2 - 1
+    g = torch.Generator().manual_seed(0)
+    r = lambda *s: torch.randn(*s, generator=g).cuda()
+    m = dict(xyz=r(P, 3), features_dc=r(P, 1, 3), features_rest=r(P, R, 3), opacity=r(P, 1), scaling=r(P, 3), rotation=r(P, 4))
+    names = ply_io.construct_list_of_attributes(R, 3)
+    tmp = tempfile.mkdtemp()
+    path = os.path.join(tmp, "point_cloud.ply")
+
+    def wall(fn, n):
+        fn(); torch.cuda.synchronize()
+        t = []
+        for _ in range(n):
+            t0 = time.perf_counter(); fn(); torch.cuda.synchronize(); t.append((time.perf_counter() - t0) * 1e3)
+        return sorted(t)[len(t) // 2]
+
+    def ref_save_rows():
+        xyz = m["xyz"].detach().cpu().numpy()
+        normals = np.zeros_like(xyz)
+        f_dc = m["features_dc"].detach().transpose(1, 2).flatten(start_dim=1).contiguous().cpu().numpy()
+        f_rest = m["features_rest"].detach().transpose(1, 2).flatten(start_dim=1).contiguous().cpu().numpy()
+        elements = np.empty(xyz.shape[0], dtype=[(a, "f4") for a in names])
+        attributes = np.concatenate((xyz, normals, f_dc, f_rest, m["opacity"].cpu().numpy(), m["scaling"].cpu().numpy(),
+                                     m["rotation"].cpu().numpy()), axis=1)
+        elements[:] = list(map(tuple, attributes))
+        return elements
+
+    t0 = time.perf_counter(); el = ref_save_rows(); t_ref_save = (time.perf_counter() - t0) * 1e3
+    t_save = wall(lambda: ply_io.save_ply(m, path), 5)
+
+    def ref_load():
+        rec = np.fromfile(path, dtype=el.dtype, offset=os.path.getsize(path) - el.nbytes)
+        xyz = np.stack((np.asarray(rec["x"]), np.asarray(rec["y"]), np.asarray(rec["z"])), axis=1)
+        fe = np.zeros((P, 3 * R))
+        for idx in range(3 * R):
+            fe[:, idx] = np.asarray(rec["f_rest_%d" % idx])
+        fe = fe.reshape((P, 3, R))
+        fd = np.zeros((P, 3, 1))
+        for c in range(3):
+            fd[:, c, 0] = np.asarray(rec["f_dc_%d" % c])
+        sc = np.zeros((P, 3)); ro = np.zeros((P, 4))
+        for c in range(3):
+            sc[:, c] = np.asarray(rec["scale_%d" % c])
+        for c in range(4):
+            ro[:, c] = np.asarray(rec["rot_%d" % c])
+        op = np.asarray(rec["opacity"])[..., np.newaxis]
+        return [torch.tensor(a, dtype=torch.float, device="cuda") for a in (xyz, op, sc, ro)] + \
+               [torch.tensor(fd, dtype=torch.float, device="cuda").transpose(1, 2).contiguous(),
+                torch.tensor(fe, dtype=torch.float, device="cuda").transpose(1, 2).contiguous()]
+
+    t_ref_load = wall(ref_load, 3)
+    t_load = wall(lambda: ply_io.load_ply(path, max_sh_degree=3), 5)
+    back = ply_io.load_ply(path, max_sh_degree=3)
+    ok = all(torch.equal(back[k], m[k]) for k in m)
+    size = os.path.getsize(path)
+    os.remove(path); os.rmdir(tmp)
+    return {"row": "8f-4 ply", "config": cfg, "P": P, "file_bytes": size, "round_trip_exact": ok,
+            "unit": "ms wall clock per call (file system included on our side)",
+            "reference_statements_save_ms": t_ref_save, "save_ply_ms": t_save, "save_speedup": t_ref_save / t_save,
+            "reference_statements_load_ms": t_ref_load, "load_ply_ms": t_load, "load_speedup": t_ref_load / t_load,
+            "note": "reference arm = its numpy statements only (structured array through list(map(tuple, ...)) on save, one "
+                    "column at a time on load), without plyfile's own write / read"}
+
+
 def row_iteration(cfg, K, W):
     """One whole training iteration as train_3dgs.py:85-193 runs it -- staging, render, loss, backward, densification
     statistics, optimizer step -- (a) with the reference's torch code around the stock drop-in rasterizer, (b) with
@@ -309,7 +380,7 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("needs a CUDA device")
     for r in args.rows.split(","):
-        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim, "densify": row_densify,
+        fn = {"staging": row_staging, "loss": row_loss, "optim": row_optim, "densify": row_densify, "ply": row_ply,
               "iteration": row_iteration}[r]
         print(json.dumps(fn(args.config, args.steps, args.warmup)), flush=True)
 
