@@ -63,4 +63,12 @@ n, col, dep, alp, rad = c3.rasterize_gaussians_views(sc.bg, sc.means3D, E, sc.op
                                                      torch.stack([c.campos for c in cams]), False, False)
 torch.cuda.synchronize()
 print("views", n, float(col.sum()))
+import tempfile
+from scorp_b200 import ply_io
+with tempfile.TemporaryDirectory() as tmp:
+    mdl = dict(xyz=st[0].detach(), features_dc=st[1].detach(), features_rest=st[2].detach(), opacity=st[3].detach(),
+               scaling=st[4].detach(), rotation=st[5].detach())
+    ply_io.save_ply(mdl, os.path.join(tmp, "m.ply"))
+    bk = ply_io.load_ply(os.path.join(tmp, "m.ply"))
+    print("ply", tuple(bk["features_rest"].shape), all(torch.equal(bk[k], mdl[k]) for k in mdl))
 print("done")
