@@ -310,6 +310,11 @@ int gsr_adam_step(int n_groups, const GsrAdamGroup* groups, double beta1, double
 int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, int grad_stride,
                             float* xyz_gradient_accum, float* denom, float* max_radii2D, void* stream);
 
+/* GaussianModel.reset_opacity (gaussian_model.py:253-256; train_3dgs.py:187-188) in place:
+ *   opacity = inverse_sigmoid(min(sigmoid(opacity), cap)), cap = 0.01, and -- replace_tensor_to_optimizer, :410-423 --
+ *   the opacity group's Adam moments zeroed (either may be NULL). */
+int gsr_reset_opacity(int P, float* opacity, float* exp_avg, float* exp_avg_sq, float cap, void* stream);
+
 /* --- densify_and_prune ------------------------------------------------------------------------------------------
  * Replaces GaussianModel.densify_and_prune (gs3dgs/scene/gaussian_model.py:572-586, gs2dgs/scene/gaussian_model.py:
  * 478-492) with everything below it: densify_and_clone (:559-570), densify_and_split (:502-527),

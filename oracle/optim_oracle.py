@@ -129,3 +129,12 @@ def densify_and_prune(params, moments, accum, denom, max_grad, min_opacity, exte
         mask = mask | (np.zeros(mask.shape, f32) > f32(max_screen_size)) | (scaling().max(1) > big)
     prune(mask)
     return par, mom
+
+
+def reset_opacity(opacity, cap=0.01):
+    """GaussianModel.reset_opacity (/root/reference/gs3dgs/scene/gaussian_model.py:253-256) with inverse_sigmoid
+    (gs3dgs/utils/general_utils.py:20-21): log(x / (1 - x)) of min(sigmoid(opacity), 0.01); the moments become zeros."""
+    o = np.asarray(opacity, f32)
+    a = (f32(1) / (f32(1) + np.exp(-o).astype(f32)).astype(f32)).astype(f32)
+    x = np.minimum(a, f32(cap))
+    return np.log((x / (f32(1) - x).astype(f32)).astype(f32)).astype(f32)

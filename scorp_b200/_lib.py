@@ -82,6 +82,7 @@ SIGNATURES = {
                                     + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
     "gsr_adam_step": (c_int, [c_int, C.POINTER(GsrAdamGroup), C.c_double, C.c_double, C.c_double, c_int, _P]),
     "gsr_densification_stats": (c_int, [c_int, _P, _P, c_int, _P, _P, _P, _P]),
+    "gsr_reset_opacity": (c_int, [c_int, _P, _P, _P, c_float, _P]),
     "gsr_densify_workspace_bytes": (c_size_t, [c_int, c_int]),
     "gsr_densify_plan": (c_int, [c_int, c_int, _P, _P, _P, _P, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), _P]),
     "gsr_densify_apply": (c_int, [c_int, c_int, C.POINTER(GsrDensifyCfg), _P, C.POINTER(C.c_int32), c_int,

@@ -97,6 +97,20 @@ densify_stats_kernel(int P, const int32_t* __restrict__ radii, const float* __re
     if (max_radii) max_radii[i] = fmaxf(max_radii[i], (float)r);
 }
 
+// GaussianModel.reset_opacity (gaussian_model.py:253-256) + replace_tensor_to_optimizer (:410-423):
+//   opacity = inverse_sigmoid(min(sigmoid(opacity), 0.01)) = log(x / (1 - x));  exp_avg = exp_avg_sq = 0
+// (torch: sigmoid, ones_like * 0.01, min, rsub, div, log -- one rounding each).
+__global__ void __launch_bounds__(256)
+reset_opacity_kernel(int n, float* __restrict__ opacity, float* __restrict__ exp_avg, float* __restrict__ exp_avg_sq, float cap) {
+    const int i = blockIdx.x * 256 + threadIdx.x;
+    if (i >= n) return;
+    const float a = act_opacity(opacity[i]);
+    const float x = (a != a) ? a : fminf(a, cap);                     // torch.min propagates NaN
+    opacity[i] = logf(divr(x, subr(1.0f, x)));
+    if (exp_avg) exp_avg[i] = 0.0f;
+    if (exp_avg_sq) exp_avg_sq[i] = 0.0f;
+}
+
 }  // namespace gsr
 
 using namespace gsr;
@@ -132,6 +146,14 @@ int gsr_adam_step(int n_groups, const GsrAdamGroup* groups, double beta1, double
     if (chunks > 0x7fffffffLL) { set_error("gsr_adam_step: too many elements"); return GSR_EUNSUPPORTED; }
     adam_kernel<<<(unsigned)chunks, ADAM_THREADS, 0, (cudaStream_t)stream>>>(a);
     return check_cuda(cudaGetLastError(), "adam launch");
+}
+
+int gsr_reset_opacity(int P, float* opacity, float* exp_avg, float* exp_avg_sq, float cap, void* stream)
+{
+    if (P == 0) return GSR_OK;
+    if (P < 0 || !opacity) { set_error("bad argument to gsr_reset_opacity"); return GSR_EINVAL; }
+    reset_opacity_kernel<<<(P + 255) / 256, 256, 0, (cudaStream_t)stream>>>(P, opacity, exp_avg, exp_avg_sq, cap);
+    return check_cuda(cudaGetLastError(), "reset opacity launch");
 }
 
 int gsr_densification_stats(int P, const int32_t* radii, const float* dL_dmeans2D, int grad_stride,

@@ -24,7 +24,7 @@ import torch
 
 from . import _lib
 
-__all__ = ["Adam", "add_densification_stats", "densify_and_prune", "densify_and_prune_tensors"]
+__all__ = ["Adam", "add_densification_stats", "densify_and_prune", "densify_and_prune_tensors", "reset_opacity"]
 
 
 class Adam(torch.optim.Optimizer):
@@ -210,3 +210,36 @@ def densify_and_prune(gaussians, max_grad, min_opacity, extent, max_screen_size,
     if empty_cache:
         torch.cuda.empty_cache()          # as the reference does (:586)
     return counts
+
+
+@torch.no_grad()
+def reset_opacity(gaussians, cap: float = 0.01):
+    """GaussianModel.reset_opacity (gaussian_model.py:253-256): opacity <- inverse_sigmoid(min(sigmoid(opacity), 0.01)),
+    and, as replace_tensor_to_optimizer does (:410-423), a new nn.Parameter in the "opacity" group with zeroed moments
+    (`step` kept). One launch; the values are written into a fresh tensor's storage like the reference's new tensor."""
+    lib = _lib.lib()
+    old = gaussians._opacity
+    if not old.is_cuda:
+        raise _lib.GsrError("reset_opacity needs CUDA tensors: there is no CPU path")
+    new = old.detach().clone(memory_format=torch.contiguous_format)
+    group = next((g for g in gaussians.optimizer.param_groups if g.get("name") == "opacity"), None)
+    st = gaussians.optimizer.state.get(group["params"][0], None) if group is not None else None
+    m = v = None
+    if st is not None and "exp_avg" in st:
+        m, v = torch.empty_like(new), torch.empty_like(new)
+    dev = new.device
+    with torch.cuda.device(dev):
+        rc = lib.gsr_reset_opacity(new.numel(), _lib.ptr(new), _lib.ptr(m) if m is not None else None,
+                                   _lib.ptr(v) if v is not None else None, float(cap),
+                                   C.c_void_p(torch.cuda.current_stream(dev).cuda_stream))
+    _lib.check(rc, "gsr_reset_opacity")
+    param = torch.nn.Parameter(new.requires_grad_(True))
+    if group is not None:
+        if st is not None:
+            if m is not None:
+                st["exp_avg"], st["exp_avg_sq"] = m, v
+            del gaussians.optimizer.state[group["params"][0]]
+            gaussians.optimizer.state[param] = st
+        group["params"][0] = param
+    gaussians._opacity = param
+    return param

@@ -143,3 +143,30 @@ def test_edges():
     with pytest.raises(RuntimeError, match="normals"):
         optim.densify_and_prune_tensors(par, {}, pc.xyz_gradient_accum, pc.denom, 0.0002, 0.005, 4.0, 20, 0.01,
                                         normals=torch.zeros(3, 3, device="cuda"))
+
+
+def test_reset_opacity():
+    """optim.reset_opacity == GaussianModel.reset_opacity: the reference-model golden, the torch expressions on the same
+    GPU bit for bit, and the optimizer surgery of replace_tensor_to_optimizer."""
+    from scorp_b200 import optim
+    pc = _model(50_001, 1, 3, seed=4)
+    pc._opacity.data.mul_(1.7)
+    old, st_old = pc._opacity, pc.optimizer.state[pc._opacity]
+    step = st_old["step"]
+    x = torch.sigmoid(old.detach())
+    ref = torch.log(torch.min(x, torch.ones_like(x) * 0.01) / (1 - torch.min(x, torch.ones_like(x) * 0.01)))
+    new = optim.reset_opacity(pc)
+    assert new is pc._opacity and new is not old and isinstance(new, torch.nn.Parameter) and new.requires_grad
+    assert torch.equal(new.detach(), ref)
+    group = [g for g in pc.optimizer.param_groups if g["name"] == "opacity"][0]
+    assert group["params"][0] is new and old not in pc.optimizer.state
+    st = pc.optimizer.state[new]
+    assert st["step"] is step and float(st["exp_avg"].abs().max()) == 0 and float(st["exp_avg_sq"].abs().max()) == 0
+    # golden from the reference's own model (CPU run): same values up to the CPU/CUDA exp, log
+    pc2 = _model(900, 1, 3, seed=1, with_state=False)
+    pc2._opacity = torch.nn.Parameter(torch.from_numpy(G["reset_in_opacity"]).cuda())
+    pc2.optimizer.param_groups[3]["params"][0] = pc2._opacity
+    optim.reset_opacity(pc2)
+    np.testing.assert_allclose(pc2._opacity.detach().cpu().numpy(), G["reset_out_opacity"], rtol=2e-6, atol=2e-6)
+    assert np.array_equal(pc2._opacity.detach().cpu().numpy(), O.reset_opacity(G["reset_in_opacity"])) or \
+        np.allclose(pc2._opacity.detach().cpu().numpy(), O.reset_opacity(G["reset_in_opacity"]), rtol=2e-6, atol=2e-6)

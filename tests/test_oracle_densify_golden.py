@@ -32,3 +32,11 @@ def test_oracle_matches_reference_model(c):
             assert np.array_equal(mom[n][0], G[f"{c}_out_m_{n}"]) and np.array_equal(mom[n][1], G[f"{c}_out_v_{n}"]), n
         else:
             assert n not in mom
+
+
+def test_reset_opacity_oracle_matches_reference_model():
+    """GaussianModel.reset_opacity run on CPU (tools/make_golden_densify.py:reset_case)"""
+    got = O.reset_opacity(G["reset_in_opacity"])
+    ref = G["reset_out_opacity"]
+    np.testing.assert_allclose(got, ref, rtol=2e-6, atol=2e-6)        # numpy exp/log vs torch's CPU kernels
+    assert float(ref.max()) <= np.log(0.01 / 0.99) + 1e-5 and (ref < ref.max() - 1e-3).any()   # capped and not all capped

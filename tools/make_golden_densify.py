@@ -107,6 +107,33 @@ def case(pkg, P, sh_rest, scale_dim, seed, max_grad, min_opacity, extent, max_sc
     return out
 
 
+def reset_case(P=900, seed=21):
+    """GaussianModel.reset_opacity (gaussian_model.py:253-256) after one optimizer step"""
+    GaussianModel = _reference("gs3dgs")
+    g = torch.Generator().manual_seed(seed)
+    pc = GaussianModel(3)
+    pc._xyz = torch.nn.Parameter(torch.randn(P, 3, generator=g))
+    pc._features_dc = torch.nn.Parameter(torch.randn(P, 1, 3, generator=g))
+    pc._features_rest = torch.nn.Parameter(torch.randn(P, 15, 3, generator=g))
+    pc._opacity = torch.nn.Parameter(torch.randn(P, 1, generator=g) * 4)
+    pc._scaling = torch.nn.Parameter(torch.randn(P, 3, generator=g))
+    pc._rotation = torch.nn.Parameter(torch.randn(P, 4, generator=g))
+    with _cpu_literals():
+        pc.training_setup(types.SimpleNamespace(percent_dense=0.01, position_lr_init=0.00016, position_lr_final=1.6e-6,
+                                                position_lr_delay_mult=0.01, position_lr_max_steps=30000, feature_lr=0.0025,
+                                                opacity_lr=0.05, scaling_lr=0.005, rotation_lr=0.001))
+    pc._opacity.grad = torch.randn(P, 1, generator=g) * 1e-3
+    pc.optimizer.step()
+    out = {"in_opacity": pc._opacity.detach().numpy().copy()}
+    step = pc.optimizer.state[pc._opacity]["step"]
+    with _cpu_literals():
+        pc.reset_opacity()
+    st = pc.optimizer.state[pc._opacity]
+    assert st["step"] is step and float(st["exp_avg"].abs().max()) == 0 and float(st["exp_avg_sq"].abs().max()) == 0
+    out["out_opacity"] = pc._opacity.detach().numpy().copy()
+    return out
+
+
 def main():
     cases = {
         "a": case("gs3dgs", 1200, 15, 3, 11, 0.0002, 0.005, 4.0, 20, 0.01),
@@ -115,6 +142,7 @@ def main():
         "d": case("gs3dgs", 600, 3, 3, 14, 0.0002, 0.005, 5.0, 20, 0.01, with_state=False),   # no optimizer state yet
     }
     flat = {f"{c}_{k}": v for c, d in cases.items() for k, v in d.items()}
+    flat.update({f"reset_{k}": v for k, v in reset_case().items()})
     np.savez_compressed(ROOT / "tests" / "golden" / "densify.npz", cases=np.array(sorted(cases)), **flat)
     for c, d in cases.items():
         print(c, "P", d["in_xyz"].shape[0], "->", d["out_xyz"].shape[0], "rows; samples", d["normals"].shape)
