@@ -7,7 +7,7 @@ import pytest
 
 from oracle import gs_oracle as O
 
-GOLD = sorted((Path(__file__).resolve().parent / "golden").glob("g*.npz"))
+GOLD = sorted((Path(__file__).resolve().parent / "golden").glob("g[0-9]*.npz"))
 
 
 def _run(d):

@@ -9,8 +9,8 @@ import pytest
 from oracle import gs_oracle as O
 
 GDIR = Path(__file__).resolve().parent / "golden"
-SGOLD = sorted(GDIR.glob("s*.npz"))
-KGOLD = sorted(GDIR.glob("k*.npz"))
+SGOLD = sorted(GDIR.glob("s[0-9]*.npz"))
+KGOLD = sorted(GDIR.glob("k[0-9]*.npz"))
 
 
 def test_golden_families_present():
