@@ -208,6 +208,19 @@ def ncu_traffic(cfg_name, stage):
         return None
 
 
+def sha_of(tensors):
+    """sha256 (first 16 hex digits) over the bytes of device tensors, in order, as they sit in HBM."""
+    import hashlib
+    h = hashlib.sha256()
+    for t in tensors:
+        h.update(t.detach().contiguous().cpu().numpy().tobytes())
+    return h.hexdigest()[:16]
+
+
+def inputs_sha(sc, cam):
+    return sha_of([sc.means3D, sc.scales, sc.rotations, sc.opacities, sc.shs, cam.viewmatrix, cam.projmatrix])
+
+
 def out_channels(surfel):
     return (3, 7) if surfel else (3, 1, 1)
 
@@ -250,7 +263,7 @@ class Ours:
         self.mod, self.C, self.lib = mod, _C, _lib.lib()
         self.E = torch.Tensor([])
 
-    def fwd_bwd(self, sc, cam, bg, view, proj, campos, grads, fwd_only):
+    def fwd_bwd(self, sc, cam, bg, view, proj, campos, grads, fwd_only, full=False):
         C_, E = self.C, self.E
         out = C_.rasterize_gaussians(bg, sc.means3D, E, sc.opacities, sc.scales, sc.rotations, 1.0, E, view, proj,
                                      cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, False, False)
@@ -268,6 +281,8 @@ class Ours:
             g = C_.rasterize_gaussians_backward(bg, sc.means3D, radii, E, sc.scales, sc.rotations, 1.0, E, view, proj,
                                                 cam.tanfovx, cam.tanfovy, grads[0], grads[1], grads[2], sc.shs,
                                                 sc.sh_degree, campos, geom, n, binning, img, alpha, False)
+        if full:        # the five parameter gradients: means3D, sh, opacity, scales, rotations
+            return n, radii, color, (g[3], g[5], g[2], g[6], g[7])
         return n, radii, color, g[3]          # g[3] = dL_dmeans3D, the head of the gradient arena
 
     def tile_stats(self, sc, cam):
@@ -282,6 +297,18 @@ class Ours:
         rg = img[off[0]: off[0] + 8 * tiles].view(torch.int32).view(tiles, 2).long()
         ln = rg[:, 1] - rg[:, 0]
         return {"tiles": tiles, "mean_list": float(ln.float().mean()), "max_list": int(ln.max()), "pairs": int(ln.sum()) * 256}
+
+    def binning_sha(self, sc, cam):
+        """sha256 over radii and the sorted (tile | depth) keys of one forward of `cam` (bit-exactness evidence: the
+        reference arm prints the same hash from its own buffers)."""
+        out = self.C.rasterize_gaussians(sc.bg, sc.means3D, self.E, sc.opacities, sc.scales, sc.rotations, 1.0, self.E,
+                                         cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs,
+                                         sc.sh_degree, cam.campos, False, False)
+        n, radii, binning = out[0], out[-4], out[-2]
+        off = (C.c_size_t * 3)(); tot = C.c_size_t(0)
+        self.lib.gsr_binning_layout(n, off, C.byref(tot))
+        keys = binning[off[1]: off[1] + 8 * n].view(torch.int64)
+        return sha_of([radii, keys]), n
 
     def accumulate(self, total, g_means3D, P, M):
         from scorp_b200 import multiview as mv
@@ -335,6 +362,7 @@ class Reference:
         if self.surfel:
             f = rc.dsr_forward(bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, view, proj,
                                cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, sync=False)
+            self._last_fwd = f
             if fwd_only:
                 return f["num_rendered"], f["radii"], f["color"], None
             g = rc.dsr_backward(f, bg, sc.means3D, None, sc.scales, sc.rotations, 1.0, None, view, proj, cam.tanfovx,
@@ -342,6 +370,7 @@ class Reference:
         else:
             f = rc.dgr_forward(bg, sc.means3D, None, sc.opacities, sc.scales, sc.rotations, 1.0, None, view, proj,
                                cam.tanfovx, cam.tanfovy, cam.H, cam.W, sc.shs, sc.sh_degree, campos, sync=False)
+            self._last_fwd = f
             if fwd_only:
                 return f["num_rendered"], f["radii"], f["color"], None
             g = rc.dgr_backward(f, bg, sc.means3D, None, sc.scales, sc.rotations, 1.0, None, view, proj, cam.tanfovx,
@@ -349,6 +378,13 @@ class Reference:
         return f["num_rendered"], f["radii"], f["color"], g
 
     KEYS = ("means3D", "sh", "opacity", "scales", "rotations")
+
+    def binning_sha(self, sc, cam):
+        n, radii, color, _ = self.fwd_bwd(sc, cam, sc.bg, cam.viewmatrix, cam.projmatrix, cam.campos, None, True)
+        torch.cuda.synchronize()
+        f = self._last_fwd
+        keys = (self.rc.dsr_intermediates(f) if self.surfel else self.rc.dgr_intermediates(f))["point_list_keys"]
+        return sha_of([radii, keys]), n
 
     def accumulate(self, total, g, P, M):
         if total is None:
@@ -373,6 +409,54 @@ class Reference:
         if world > 1 and g is not None:
             self.reduce(g, sc.P, sc.shs.shape[1])
         return color
+
+
+def exchange_check(arm, sc, cam, grads, world, dev):
+    """Correctness of the exchange the timed steps used (N > 1, product arm): one backward through the installed
+    exchange against the SAME backward with the exchange switched off followed by one plain dist.all_reduce per
+    gradient tensor. Tolerance as in the single-GPU parity tests (tests/test_gpu_dgr_parity.py:_grad_ok): rtol 1e-4,
+    atol = 1e-6 * max|ref| + 2 x the run-to-run spread of the plain path (float atomics in the blend backward).
+    Returns {"ok", "worst_ratio", ...}; the caller exits non-zero when it fails."""
+    from scorp_b200 import multiview as mv
+    from scorp_b200.diff_gaussian_rasterization import _C as c3
+    from scorp_b200.diff_surfel_rasterization import _C as c2
+    names = ("means3D", "sh", "opacity", "scales", "rotations")
+    fx = c3._factored[0]
+
+    def run(dense_head=False):
+        g = arm.fwd_bwd(sc, cam, sc.bg, cam.viewmatrix, cam.projmatrix, cam.campos, grads, False, full=True)[3]
+        if dense_head:      # the un-factored product path: ONE all_reduce over the head of the gradient arena
+            arm.reduce(g[0], sc.P, sc.shs.shape[1])
+        return [t.clone() for t in g]
+    got = run(dense_head=fx is None)                    # through the exchange that ran in the timed region
+    saved = (c3._factored[0], c2._factored[0], c3._backward_hook[0], c2._backward_hook[0])
+    c3._factored[0] = c2._factored[0] = None
+    c3._backward_hook[0] = c2._backward_hook[0] = None
+    try:
+        refs = []
+        for _ in range(3):                              # three plain runs: their spread is the atomics noise
+            loc = run()
+            for t in loc:
+                dist.all_reduce(t)
+            refs.append(loc)
+    finally:
+        c3._factored[0], c2._factored[0], c3._backward_hook[0], c2._backward_hook[0] = saved
+    worst, worst_name = 0.0, None
+    for i, name in enumerate(names):
+        st = torch.stack([r[i].double().reshape(-1) for r in refs])
+        mean = st.mean(0)
+        spread = float((st.max(0).values - st.min(0).values).max())
+        tol = 1e-6 * float(mean.abs().max()) + 2.0 * spread + 1e-4 * mean.abs()
+        ratio = float(((got[i].double().reshape(-1) - mean).abs() / tol.clamp_min(1e-300)).max())
+        if ratio > worst:
+            worst, worst_name = ratio, name
+    t = torch.tensor([worst], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return {"ok": bool(float(t) <= 1.0), "worst_ratio": float(t), "worst_tensor_rank0": worst_name, "rtol": 1e-4,
+            "atol": "1e-6*max|ref| + 2*spread of 3 plain runs", "ranks": world,
+            "path": type(fx).__name__ if fx is not None else "dense all_reduce of the arena head",
+            "peer_ok": bool(getattr(fx, "ok", False)), "multicast": bool(getattr(fx, "multicast", False)),
+            "against": "same backward with the exchange off + one dist.all_reduce per gradient tensor"}
 
 
 def time_exchange(arm, P, M, surfel, world, dev, reps=10):
@@ -413,10 +497,17 @@ def run(arm, args, rank, world, local):
     cfg = synth.CONFIGS[args.config]
     surfel, fwd_only = cfg["surfel"], cfg.get("forward_only", False)
     dev = torch.device("cuda", local)
-    vpr = args.views_per_rank or cfg.get("views_per_rank", 1)
+    sweep = cfg.get("sweep_views", 0)       # C5: the whole pose sweep (128 rotations) is the job, split over the ranks
+    vpr = args.views_per_rank or (max(sweep // world, 1) if sweep else cfg.get("views_per_rank", 1))
     n_views = world * vpr
-    rots = synth.random_rotations(n_views, seed=128) if fwd_only else None      # stand-in for rotations_128.npz
-    sc = synth.make_scene(args.config, n_views=n_views, rotations_npz=rots).to(dev)
+    cameras = None
+    if sweep:
+        # the reference's own pose set: rotation_matrices/rotations_128.npz (utils/graphic.py:150-360, consumed by
+        # align_3dgs_clpe_9dof.py / align_2dgs_clpe_9dof.py:298-305), committed as a fixture under tests/golden/
+        import numpy as np
+        rots = np.load(ROOT / "tests" / "golden" / "rotations_128.npz")["rotations"]
+        cameras = [synth.orbit_camera(cfg["W"], cfg["H"], rots[v % len(rots)]) for v in range(n_views)]
+    sc = synth.make_scene(args.config, n_views=n_views, cameras=cameras).to(dev)
     from scorp_b200 import multiview as mv
     my_views = mv.views_for_rank(n_views, rank, world)
     cams = [sc.cameras[v] for v in my_views]
@@ -459,6 +550,8 @@ def run(arm, args, rank, world, local):
                 exchange = "peer: dL_dRGB stored into every rank's gather buffer by the backward itself (NVLink peer pointers, symmetric memory)"
         elif arm.name == "reference":
             exchange = "five all_reduce calls (one per gradient tensor)"
+    in_sha = inputs_sha(sc, cams[0])
+    bin_sha, n_first = arm.binning_sha(sc, cams[0])
     n, radii, _ = step_resident()
     Pvis = int((radii > 0).sum())          # batched: radii is [V, P] and n the total, so the stage bytes cover all views
     prime(step_resident, world)
@@ -521,9 +614,11 @@ def run(arm, args, rank, world, local):
 
     prime(step_e2e, world)                 # setup, not warm-up: caching-allocator growth for the autograd path
     ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
-    exch = None
+    exch, xcheck = None, None
     if world > 1 and not fwd_only:
         exch = time_exchange(arm, P, M, surfel, world, dev)
+        if arm.name == "ours":
+            xcheck = exchange_check(arm, sc, cams[0], grads[0], world, dev)
     tstats = arm.tile_stats(sc, cams[0]) if arm.name == "ours" else None
     launches = 0
     if arm.name == "ours":
@@ -533,16 +628,24 @@ def run(arm, args, rank, world, local):
         from scorp_b200.diff_gaussian_rasterization import _C as _c3
         fx = _c3._factored[0]
         if getattr(fx, "ok", False):
-            exchange += "; non-SH floats reduced in the switch by the preprocess-backward kernel (multimem.red)" \
+            exchange += "; non-SH floats reduced in the switch in two phases (local stores, then multimem.ld_reduce + multimem.st on a 1/N share per rank)" \
                 if getattr(fx, "multicast", False) else "; non-SH floats all-reduced by NCCL (no multicast mapping)"
             if exch:
-                exch["note"] = "stand-alone timing of the NCCL form of this exchange, for reference; the timed steps used the peer-memory exchange"
+                exch["note"] = "stand-alone timing of the NCCL form of this exchange, for reference; the timed steps used the peer-memory exchange (peer_phases_ms)"
+                # CUDA-event times of the path that actually ran: 10 more steps with events around the phases of
+                # PeerExchange.finish (rank 0; the barrier phases include waiting for the slowest rank)
+                fx.profile = True
+                for _ in range(10):
+                    step_resident()
+                fx.profile = False
+                exch["peer_phases_ms"] = fx.stage_ms()
         else:
             exchange += f" [symmetric memory unavailable, ran as NCCL factored: {getattr(fx, 'why', '')}]"
     return dict(W=W, H=H, P=P, M=M, Pvis=Pvis, N=n, ms_step=ms_step, ms_e2e=ms_e2e_total / args.steps, stages=stages,
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
-                d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched)
+                d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched,
+                inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck)
 
 
 def main():
@@ -559,9 +662,12 @@ def main():
             dist.destroy_process_group()
         return
     r = run(arm, args, rank, world, local)
+    failed = bool(r.get("xcheck")) and not r["xcheck"]["ok"]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
+        if failed:
+            raise SystemExit(3)
         return
     W, H = r["W"], r["H"]
     mpix = W * H * r["views"] / 1e6
@@ -578,6 +684,10 @@ def main():
         "config": {"workload": synth.CONFIGS[args.config]["desc"], "id": args.config, "mode": mode, "P": r["P"],
                    "sh_coeffs": r["M"], "width": W, "height": H, "visible": r["Pvis"], "num_rendered": r["N"],
                    "views_per_step": r["views"], "views_per_rank": r["vpr"],
+                   # self-verification: both arms hash the device-resident inputs and the binning result (radii + sorted
+                   # tile|depth keys) of rank 0's first camera; equal hashes = identical inputs and bit-exact binning
+                   "inputs_sha": r["inputs_sha"], "binning_sha": r["binning_sha"], "num_rendered_first_view": r["n_first"],
+                   "host_threads": torch.get_num_threads(),
                    "parallelism": f"view-sharded dp{world}; exchange: {r['exchange']}" if world > 1 else "single GPU",
                    "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"
                          if r["P"] * (44 + 12 * r["M"]) > 126e6 else "working set below the 126 MB L2: numbers are L2-warm, as in the reference's own loop"},
@@ -585,9 +695,15 @@ def main():
                 "d2h_bytes_per_step": r["d2h"],
                 "note": "public API + autograd; per view the camera and the upstream-gradient maps are copied from pinned host memory (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
+        # the contract's value/ms_per_step are MEANS over the K steps; the medians say what a typical step costs, and
+        # `outlier` flags a run whose slowest step is > 3x its median (one allocator or host hiccup moves a mean)
+        "value_median": mpix / (r["per"]["median"] * 1e-3), "e2e_value_median": mpix / (r["per_e2e"]["median"] * 1e-3),
+        "outlier": bool(r["per"]["max"] > 3 * r["per"]["median"] or r["per_e2e"]["max"] > 3 * r["per_e2e"]["median"]),
     }
     if r["exch"]:
         line["exchange"] = r["exch"]
+    if r.get("xcheck"):
+        line["exchange_check"] = r["xcheck"]
     if r["tstats"]:
         line["config"]["tile_lists"] = r["tstats"]
     if args.impl == "ours":
@@ -616,9 +732,11 @@ def main():
         line["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                                 "sample": "full workload; the reference has no CPU rasterizer, its own implementation of this path is CUDA (oracle/_ref, unmodified sources, sm_100a) on the same GPU"}
         line["e2e"]["note"] = "reference library calls + its torch glue's allocations; same host copies as the product arm"
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+    if failed:
+        raise SystemExit("exchange_check failed: the exchanged gradients differ from the plain all_reduce (see exchange_check)")
 
 
 if __name__ == "__main__":

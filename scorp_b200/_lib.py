@@ -111,6 +111,8 @@ SIGNATURES = {
     "gsr_backward_early_rgb_peers": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), _P, _P, _P, _P]),
     "gsr_backward_peer_head": (c_int, [_P]),
     "gsr_peer_consume": (c_int, [_P, _P, c_int, c_int, _P]),
+    "gsr_peer_reduce_shard": (c_int, [_P, c_int, c_int, c_int, _P]),
+    "gsr_peer_finish": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, _P]),
     "gsr_sh_grad_from_views": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
 }
 

@@ -284,6 +284,10 @@ static int backward_impl(
     void* workspace, size_t workspace_bytes, void* stream, const RawBwd* raw)
 {
     cudaStream_t st = (cudaStream_t)stream;
+    // whatever was armed for "the next backward of this thread" is consumed by THIS call, also when it returns early:
+    // the armed state holds raw pointers into a caller-owned gradient arena and into peer buffers
+    const EarlyRgb e = take_early_rgb();
+    float* const peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
     if (P == 0) return GSR_OK;
     const int W = s->image_width, H = s->image_height;
@@ -309,7 +313,6 @@ static int backward_impl(
     }
     prof_mark(5, st);
     {   // multi-GPU: the colour gradient is final here; hand it out so its all-gather overlaps the next kernel
-        const EarlyRgb e = take_early_rgb();
         if (e.armed && shs) {
             if (e.peers.n > 0) {
                 if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.peers, st),
@@ -332,7 +335,7 @@ static int backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
-    b.mc_head = take_peer_head();
+    b.peer_head = peer_head;
     if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");
@@ -344,9 +347,12 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void*), void* user) {
     return GSR_OK;
 }
 
-int gsr_backward_peer_head(float* multicast_head) { gsr::g_peer_head = multicast_head; return GSR_OK; }
+int gsr_backward_peer_head(float* symmetric_head) {
+    if ((uintptr_t)symmetric_head & 15) { set_error("gsr_backward_peer_head: the head must be 16-byte aligned"); return GSR_EINVAL; }
+    gsr::g_peer_head = symmetric_head; return GSR_OK;
+}
 
-int gsr_peer_consume(float* symmetric_src, float* dst, int P, int surfel, void* stream) {
+int gsr_peer_consume(const float* symmetric_src, float* dst, int P, int surfel, void* stream) {
     if (P == 0) return GSR_OK;
     if (P < 0 || !symmetric_src || !dst) { set_error("gsr_peer_consume: bad argument"); return GSR_EINVAL; }
     return check_cuda(gsr::launch_peer_consume(symmetric_src, dst, P, surfel != 0, (cudaStream_t)stream), "peer consume launch");

@@ -110,14 +110,13 @@ struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; Pee
 EarlyRgb take_early_rgb();          // returns the armed request (armed == false if none) and disarms it
 cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                         int rgb_off, float* drgb, cudaStream_t st);
-// head rows [P][12] -> the planar arena head [means3D 3P | opacity P | scales 3P (2P) | rotations 4P], and clears the
-// rows for their next use
-cudaError_t launch_peer_consume(float* src, float* dst, int P, bool surfel, cudaStream_t st);
+// head rows [P][12] -> the planar arena head [means3D 3P | opacity P | scales 3P (2P) | rotations 4P]
+cudaError_t launch_peer_consume(const float* src, float* dst, int P, bool surfel, cudaStream_t st);
 // the same values written straight into every rank's gather buffer through peer pointers (all-gather by stores)
 cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                     int rgb_off, const PeerDst& dst, cudaStream_t main);
 
-float* take_peer_head();            // api.cu: multicast head armed for the next backward of this thread (NULL if none); disarms
+float* take_peer_head();            // api.cu: symmetric head (local replica) armed for the next backward of this thread (NULL if none); disarms
 uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
 
 // error plumbing (api.cu)
@@ -194,29 +193,34 @@ __device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uin
     }
 }
 
-// multimem.red: ONE store-like instruction adds v into the same offset of every rank's replica of a multicast-mapped
-// buffer; the NVSwitch performs the reduction (NVLS). p must be a multicast address (symmetric memory).
-__device__ __forceinline__ void mc_add4(float4* p, float4 v) {
-    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
-                 :: "l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+// ---- view-sharded multi-GPU: the non-SH parameter gradients are summed over ranks in the NVSwitch (NVLS) -------------
+// Two-phase (reduce-scatter + all-gather) so the bytes a GPU moves do not grow with the number of ranks:
+//   phase 0  the preprocess-backward kernel stores its 12 head floats per Gaussian into its LOCAL replica of a
+//            symmetric buffer [P][12] (peer_head_store; every row, zeros for invisible Gaussians: nothing to clear);
+//   barrier  (symmetric-memory signal pads, scorp_b200/multiview.py)
+//   phase 1  rank r reads rows [r*P/n, (r+1)*P/n) with multimem.ld_reduce -- the switch pulls the row from every
+//            replica and returns the sum -- and writes the sum back with multimem.st, which the switch stores into
+//            every replica (peer_reduce_shard_kernel, sh_exchange.cu). Per GPU: 48 B x P out, 48 B x P in, for any n.
+//   barrier, then phase 2 reads the local replica (peer_finish_kernel).
+// (Round 1 added every row into every replica with multimem.red from inside the preprocess-backward kernel: an
+// all-reduce made of n multicast reductions, n x 48 B x P_vis of ingress per GPU -- 0.28 ms of the step at 8 GPUs.)
+constexpr int PEER_HEAD_STRIDE = 12;        // floats per Gaussian in the head rows (three 16-byte groups)
+__device__ __forceinline__ float4 mc_ld_reduce4(const float4* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
 }
-constexpr int PEER_HEAD_STRIDE = 12;        // floats per Gaussian in the switch-reduced head (three 16-byte groups)
-// CTA-wide: every thread brings the 12 head floats of its Gaussian (zeros if it has none); the rows are staged in
-// shared memory and leave as 16-byte multimem.red operations at consecutive addresses (a warp instruction covers
-// 512 contiguous bytes); all-zero groups (invisible Gaussians) are not sent. `stage` holds THREADS * 12 floats.
-template <int THREADS>
-__device__ __forceinline__ void peer_head_add(float* mc_head, size_t row0, int nrows, const float (&v)[PEER_HEAD_STRIDE],
-                                              float* stage) {
-    __syncthreads();                        // the staging area may alias a tile other threads are still reading
-#pragma unroll
-    for (int k = 0; k < PEER_HEAD_STRIDE; ++k) stage[threadIdx.x * PEER_HEAD_STRIDE + k] = v[k];
-    __syncthreads();
-    float4* dst = reinterpret_cast<float4*>(mc_head + row0 * PEER_HEAD_STRIDE);
-    const float4* src = reinterpret_cast<const float4*>(stage);
-    for (int e = threadIdx.x; e < nrows * (PEER_HEAD_STRIDE / 4); e += THREADS) {
-        const float4 q = src[e];
-        if (q.x != 0.0f || q.y != 0.0f || q.z != 0.0f || q.w != 0.0f) mc_add4(dst + e, q);
-    }
+__device__ __forceinline__ void mc_st4(float4* mc, float4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+// one Gaussian's head row into the local replica (three 16-byte stores)
+__device__ __forceinline__ void peer_head_store(float* head, int idx, const float (&v)[PEER_HEAD_STRIDE]) {
+    float4* row = reinterpret_cast<float4*>(head + (size_t)idx * PEER_HEAD_STRIDE);
+    row[0] = make_float4(v[0], v[1], v[2], v[3]);
+    row[1] = make_float4(v[4], v[5], v[6], v[7]);
+    row[2] = make_float4(v[8], v[9], v[10], v[11]);
 }
 
 // cp.async 16-byte global->shared (LDGSTS), L2-only caching: the records are read once per CTA.
@@ -271,9 +275,9 @@ struct BwdArgs {
     const float* opacities = nullptr;      // raw opacity (only read when raw)
     float* dL_dsh_rest = nullptr;
     bool raw = false;
-    // gsr_backward_peer_head: multicast address of the head [P][12] = (means3D xyz, opacity | scales xyz, rot r | rot xyz, 0);
-    // the four parameter gradients of visible Gaussians are ADDED there (in every rank's replica) instead of stored
-    float* mc_head = nullptr;
+    // gsr_backward_peer_head: this rank's replica of the symmetric head [P][12] = (means3D xyz, opacity | scales xyz,
+    // rot r | rot xyz, 0); the four parameter gradients are stored there (every row) instead of into the arena
+    float* peer_head = nullptr;
 };
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st);
 

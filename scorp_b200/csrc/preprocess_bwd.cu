@@ -15,8 +15,7 @@ namespace gsr {
 template <int M3, bool RAW>
 __global__ void __launch_bounds__(SH_TILE, 8)
 preprocess_backward_kernel(BwdArgs a) {
-    // (also the staging area of peer_head_add, hence at least SH_TILE * 12 floats when there are SH coefficients)
-    constexpr int TILE_FLOATS = M3 ? (SH_TILE * ShTile<M3>::STRIDE > SH_TILE * PEER_HEAD_STRIDE ? SH_TILE * ShTile<M3>::STRIDE : SH_TILE * PEER_HEAD_STRIDE) : 4;
+    constexpr int TILE_FLOATS = M3 ? SH_TILE * ShTile<M3>::STRIDE : 4;
     __shared__ __align__(16) float s_sh[TILE_FLOATS];
     __shared__ uint8_t s_vis[SH_TILE];
     const size_t row0 = (size_t)blockIdx.x * SH_TILE;
@@ -172,16 +171,16 @@ preprocess_backward_kernel(BwdArgs a) {
         if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
         else if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
+    if (!valid) return;
     bool head_sent = false;
     if constexpr (!RAW && M3 != 0) {
-        if (a.mc_head) {        // multi-GPU: reduce in the switch, into every rank's head (invisible rows add nothing)
+        if (a.peer_head) {      // multi-GPU: the row goes to this rank's replica of the symmetric head (common.cuh, phase 0)
             const float hv[PEER_HEAD_STRIDE] = { dmean.x, dmean.y, dmean.z, dop, dscale.x, dscale.y, dscale.z, drot.x,
                                                  drot.y, drot.z, drot.w, 0.0f };
-            peer_head_add<SH_TILE>(a.mc_head, row0, nrows, hv, s_sh);
+            peer_head_store(a.peer_head, idx, hv);
             head_sent = true;
         }
     }
-    if (!valid) return;
 
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
     if constexpr (!RAW) {       // no model parameter behind these two in the model-space variant

@@ -71,14 +71,10 @@ cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* 
     return cudaGetLastError();
 }
 
-__global__ void __launch_bounds__(256)
-peer_consume_kernel(float* __restrict__ src, float* __restrict__ dst, int P, bool surfel) {
-    const int g = blockIdx.x * 256 + threadIdx.x;
-    if (g >= P) return;
-    float4* row = reinterpret_cast<float4*>(src + (size_t)g * PEER_HEAD_STRIDE);
+// head row (common.cuh: PEER_HEAD_STRIDE floats) -> the planar arena head [means3D 3P | opacity P | scales 3P (2P) | rotations 4P]
+__device__ __forceinline__ void head_row_to_planar(const float* __restrict__ src, float* __restrict__ dst, int P, int g, bool surfel) {
+    const float4* row = reinterpret_cast<const float4*>(src + (size_t)g * PEER_HEAD_STRIDE);
     const float4 a = row[0], b = row[1], c = row[2];
-    const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-    row[0] = z; row[1] = z; row[2] = z;
     const size_t Pz = (size_t)P;
     dst[3 * (size_t)g] = a.x; dst[3 * (size_t)g + 1] = a.y; dst[3 * (size_t)g + 2] = a.z;
     dst[3 * Pz + g] = a.w;
@@ -90,17 +86,33 @@ peer_consume_kernel(float* __restrict__ src, float* __restrict__ dst, int P, boo
         float* rq = dst + 7 * Pz + 4 * (size_t)g; rq[0] = b.w; rq[1] = c.x; rq[2] = c.y; rq[3] = c.z;
     }
 }
-cudaError_t launch_peer_consume(float* src, float* dst, int P, bool surfel, cudaStream_t st) {
+__global__ void __launch_bounds__(256)
+peer_consume_kernel(const float* __restrict__ src, float* __restrict__ dst, int P, bool surfel) {
+    const int g = blockIdx.x * 256 + threadIdx.x;
+    if (g < P) head_row_to_planar(src, dst, P, g, surfel);
+}
+cudaError_t launch_peer_consume(const float* src, float* dst, int P, bool surfel, cudaStream_t st) {
     peer_consume_kernel<<<(P + 255) / 256, 256, 0, st>>>(src, dst, P, surfel);
     return cudaGetLastError();
 }
 
+// Phase 1 of the head reduce (common.cuh): this rank's share of the 16-byte groups, [q0, q1), summed over all replicas by
+// the switch (multimem.ld_reduce) and stored back into all replicas (multimem.st). One group per thread per round,
+// consecutive lanes on consecutive groups (a warp instruction covers 512 contiguous bytes).
+__global__ void __launch_bounds__(256)
+peer_reduce_shard_kernel(float4* __restrict__ mc, size_t q0, size_t q1) {
+    for (size_t q = q0 + (size_t)blockIdx.x * 256 + threadIdx.x; q < q1; q += (size_t)gridDim.x * 256)
+        mc_st4(mc + q, mc_ld_reduce4(mc + q));
+}
+
 // One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
 // sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
+// head != NULL: also hands over the switch-reduced head rows of the same Gaussians (phase 2 of the head reduce).
 template <int M3>
 __global__ void __launch_bounds__(SH_TILE)
 sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ means3D,
-                          const float* __restrict__ campos, const float* __restrict__ drgb, float* __restrict__ dsh) {
+                          const float* __restrict__ campos, const float* __restrict__ drgb, float* __restrict__ dsh,
+                          const float* __restrict__ head, float* __restrict__ head_dst, bool surfel) {
     constexpr int M = M3 / 3;
     __shared__ float s_sh[SH_TILE * ShTile<M3>::STRIDE];
     __shared__ uint8_t s_all[SH_TILE];
@@ -111,6 +123,7 @@ sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ m
 #pragma unroll
     for (int i = 0; i < M3; ++i) acc[i] = 0.0f;
     if (g < P) {
+        if (head) head_row_to_planar(head, head_dst, P, g, surfel);
         const V3 m = ld3(means3D + 3 * (size_t)g);
         for (int v = 0; v < n_views; ++v) {
             const V3 d = ld3(drgb + ((size_t)v * P + g) * 3);
@@ -155,8 +168,8 @@ extern "C" int gsr_clamped_color_grad(int P, int W, int H, int surfel, const voi
     return check_cuda(cudaGetLastError(), "clamped colour gradient launch");
 }
 
-extern "C" int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
-                                      const float* drgb, float* dL_dsh, void* stream) {
+static int sh_from_views_impl(int P, int M, int D, int n_views, const float* means3D, const float* campos,
+                              const float* drgb, float* dL_dsh, const float* head, float* head_dst, bool surfel, void* stream) {
     if (P < 0 || M < 1 || M > 16 || D < 0 || D > 3 || (D + 1) * (D + 1) > M || n_views < 1) {
         set_error("bad sizes in gsr_sh_grad_from_views"); return GSR_EINVAL;
     }
@@ -165,11 +178,36 @@ extern "C" int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const fl
     cudaStream_t st = (cudaStream_t)stream;
     const int blocks = (P + SH_TILE - 1) / SH_TILE;
     switch (3 * M) {
-    case 3:  sh_grad_from_views_kernel<3><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
-    case 12: sh_grad_from_views_kernel<12><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
-    case 27: sh_grad_from_views_kernel<27><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
-    case 48: sh_grad_from_views_kernel<48><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh); break;
+    case 3:  sh_grad_from_views_kernel<3><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh, head, head_dst, surfel); break;
+    case 12: sh_grad_from_views_kernel<12><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh, head, head_dst, surfel); break;
+    case 27: sh_grad_from_views_kernel<27><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh, head, head_dst, surfel); break;
+    case 48: sh_grad_from_views_kernel<48><<<blocks, SH_TILE, 0, st>>>(P, D, n_views, means3D, campos, drgb, dL_dsh, head, head_dst, surfel); break;
     default: set_error("gsr_sh_grad_from_views: M must be 1, 4, 9 or 16"); return GSR_EINVAL;
     }
     return check_cuda(cudaGetLastError(), "SH gradient from views launch");
+}
+
+extern "C" int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,
+                                      const float* drgb, float* dL_dsh, void* stream) {
+    return sh_from_views_impl(P, M, D, n_views, means3D, campos, drgb, dL_dsh, nullptr, nullptr, false, stream);
+}
+
+extern "C" int gsr_peer_finish(int P, int M, int D, int n_views, const float* means3D, const float* campos, const float* drgb,
+                               float* dL_dsh, const float* head_rows, float* head_dst, int surfel, void* stream) {
+    if (P > 0 && (!head_rows || !head_dst)) { set_error("gsr_peer_finish: null head"); return GSR_EINVAL; }
+    return sh_from_views_impl(P, M, D, n_views, means3D, campos, drgb, dL_dsh, head_rows, head_dst, surfel != 0, stream);
+}
+
+extern "C" int gsr_peer_reduce_shard(float* multicast_head, int P, int rank, int world, void* stream) {
+    if (P == 0) return GSR_OK;
+    if (P < 0 || !multicast_head || world < 1 || rank < 0 || rank >= world || ((uintptr_t)multicast_head & 15)) {
+        set_error("gsr_peer_reduce_shard: bad argument"); return GSR_EINVAL;
+    }
+    const size_t groups = (size_t)P * (PEER_HEAD_STRIDE / 4), per = (groups + world - 1) / world;
+    const size_t q0 = per * (size_t)rank, q1 = q0 + per < groups ? q0 + per : groups;
+    if (q0 >= q1) return GSR_OK;
+    const size_t want = (q1 - q0 + 255) / 256;
+    const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);        // grid-stride; 16 CTAs of 256 per SM keep the switch busy
+    peer_reduce_shard_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_head), q0, q1);
+    return check_cuda(cudaGetLastError(), "peer head reduce launch");
 }

@@ -113,7 +113,7 @@ struct SurfelBwdArgs {
     const float* opacities = nullptr;
     float* dL_dsh_rest = nullptr;
     bool raw = false;
-    float* mc_head = nullptr;      // as BwdArgs::mc_head: [P][12] = (means3D xyz, opacity | scales xy, rot rx | rot yz, 0, 0)
+    float* peer_head = nullptr;    // as BwdArgs::peer_head: [P][12] = (means3D xyz, opacity | scales xy, rot rx | rot yz, 0, 0)
 };
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st);
 

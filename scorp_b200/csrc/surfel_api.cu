@@ -176,6 +176,8 @@ static int surfel_backward_impl(
     void* workspace, size_t workspace_bytes, void* stream, const SurfelRawBwd* raw)
 {
     cudaStream_t st = (cudaStream_t)stream;
+    const EarlyRgb e = take_early_rgb();         // consumed by THIS call, also when it returns early (see api.cu)
+    float* const peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
     if (P == 0) return GSR_OK;
     const int W = s->image_width, H = s->image_height;
@@ -202,7 +204,6 @@ static int surfel_backward_impl(
     }
     prof_mark(5, st);
     {   // multi-GPU: see gsr_rasterize_backward
-        const EarlyRgb e = take_early_rgb();
         if (e.armed && shs) {
             if (e.peers.n > 0) {
                 if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.peers, st),
@@ -223,7 +224,7 @@ static int surfel_backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dtransMat = dL_dtransMat; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
-    b.mc_head = take_peer_head();
+    b.peer_head = peer_head;
     if ((rc = check_cuda(launch_surfel_preprocess_backward(b, st), "surfel preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "surfel preprocess backward");

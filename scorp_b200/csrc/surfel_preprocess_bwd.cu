@@ -16,8 +16,8 @@ namespace gsr {
 template <int M3, bool RAW>
 __global__ void __launch_bounds__(SH_TILE, 8)
 surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
-    constexpr int TILE_FLOATS = M3 ? (SH_TILE * ShTile<M3>::STRIDE > SH_TILE * PEER_HEAD_STRIDE ? SH_TILE * ShTile<M3>::STRIDE : SH_TILE * PEER_HEAD_STRIDE) : 4;
-    __shared__ __align__(16) float s_sh[TILE_FLOATS];      // SH tile, then the staging area of peer_head_add
+    constexpr int TILE_FLOATS = M3 ? SH_TILE * ShTile<M3>::STRIDE : 4;
+    __shared__ __align__(16) float s_sh[TILE_FLOATS];
     __shared__ uint8_t s_vis[SH_TILE];
     const size_t row0 = (size_t)blockIdx.x * SH_TILE;
     const int nrows = min(SH_TILE, a.P - (int)row0);
@@ -214,16 +214,16 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
         else if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
+    if (!valid) return;
     bool head_sent = false;
     if constexpr (!RAW && M3 != 0) {
-        if (a.mc_head) {        // multi-GPU: reduce in the switch (preprocess_bwd.cu)
+        if (a.peer_head) {      // multi-GPU: the row goes to this rank's replica of the symmetric head (common.cuh, phase 0)
             const float hv[PEER_HEAD_STRIDE] = { dmean.x, dmean.y, dmean.z, dop, dscale0, dscale1, drot.x, drot.y,
                                                  drot.z, drot.w, 0.0f, 0.0f };
-            peer_head_add<SH_TILE>(a.mc_head, row0, nrows, hv, s_sh);
+            peer_head_store(a.peer_head, idx, hv);
             head_sent = true;
         }
     }
-    if (!valid) return;
 
     st3(a.dL_dmeans2D + 3 * idx, dm2d);
     if constexpr (!RAW) st3(a.dL_dcolors + 3 * idx, dcol);

@@ -204,7 +204,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     # With multiview.install_factored_exchange the SH gradient is NOT produced by the backward (dL_dsh = NULL): the
     # arena head is [means3D, opacity, scales, rotations] (all-reduced), followed by the clamped colour gradient that
     # is all-gathered, and dL_dsh is rebuilt from all ranks' colour gradients (csrc/sh_exchange.cu).
-    fx = _factored[0] if (M > 0 and P != 0) else None
+    fx_installed = _factored[0]
+    fx = fx_installed if (M > 0 and P != 0) else None
     if fx is not None:
         widths = (3, 1, 3, 4, 3, 3, 3, 6)       # means3D, opacity, scales, rotations | drgb | means2D, colors, cov3D
     else:
@@ -236,6 +237,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             if early[1]:
                 raise early[1][0]
             fx.finish(flat[: P * 11], means3D, g_sh, P, M, int(degree))
+        elif fx_installed is not None:
+            # precomputed colours (M == 0): there is no SH gradient to factor, but install_factored_exchange promises
+            # gradients summed over ranks from EVERY backward, so the head is reduced with one all_reduce in its group
+            from .. import multiview as _mv
+            _mv.reduce_without_factoring(fx_installed, flat[: P * param_grad_floats(M)])
         elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_cov.view(P, 6),

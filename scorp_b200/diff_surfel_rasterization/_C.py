@@ -72,7 +72,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     # parameter gradients first and contiguous (one allreduce), then the rest; with
     # multiview.install_factored_exchange the SH rows are rebuilt from all ranks' colour gradients instead
     # (see diff_gaussian_rasterization/_C.py and csrc/sh_exchange.cu)
-    fx = _factored[0] if (M > 0 and P != 0) else None
+    fx_installed = _factored[0]
+    fx = fx_installed if (M > 0 and P != 0) else None
     if fx is not None:
         widths = (3, 1, 2, 4, 3, 3, 3, 9)       # means3D, opacity, scales, rotations | drgb | means2D, colors, transMat
     else:
@@ -104,6 +105,11 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             if early[1]:
                 raise early[1][0]
             fx.finish(flat[: P * 10], means3D, g_sh, P, M, int(degree))
+        elif fx_installed is not None:
+            # precomputed colours (M == 0): there is no SH gradient to factor, but install_factored_exchange promises
+            # gradients summed over ranks from EVERY backward, so the head is reduced with one all_reduce in its group
+            from .. import multiview as _mv
+            _mv.reduce_without_factoring(fx_installed, flat[: P * param_grad_floats(M)])
         elif _backward_hook[0] is not None:     # e.g. multiview.install_backward_allreduce: reduce before autograd copies
             _backward_hook[0](flat[: P * param_grad_floats(M)])
     return (g_m2d.view(P, 3), g_col.view(P, 3), g_op.view(P, 1), g_m3d.view(P, 3), g_tm.view(P, 9),

@@ -172,10 +172,15 @@ class PeerExchange(FactoredExchange):
     synchronisation. The gather buffers live in torch symmetric memory (torch.distributed._symmetric_memory: peer
     pointers + barrier) and are double-buffered by step parity, so a fast rank's next push cannot overwrite what a
     slow rank's rebuild kernel is still reading (the barrier bounds the skew to one step). The 11 / 10 non-SH floats
-    are reduced IN THE SWITCH by the preprocess-backward kernel itself when the symmetric buffer has a multicast
-    mapping (NVLS): it adds its visible rows into every rank's head with multimem.red (gsr_backward_peer_head), and
-    gsr_peer_consume hands the sum over after the barrier -- a step then contains no NCCL call at all. Without
-    multicast support they are all-reduced by NCCL underneath the rebuild kernel.
+    are reduced IN THE SWITCH when the symmetric buffer has a multicast mapping (NVLS), in two phases whose per-GPU
+    traffic does not grow with the number of ranks (csrc/common.cuh): the preprocess-backward kernel stores its rows
+    into the local replica of a symmetric head (gsr_backward_peer_head); after a barrier every rank sums ITS 1/world
+    share of the rows over all replicas with multimem.ld_reduce and broadcasts the sums with multimem.st
+    (gsr_peer_reduce_shard); after a second barrier the rebuild kernel also hands the summed rows over
+    (gsr_peer_finish) -- a step then contains no NCCL call at all. Without multicast support they are all-reduced by
+    NCCL underneath the rebuild kernel.
+
+    `profile = True` records CUDA events around the phases of finish(); `stage_ms()` returns their mean durations.
 
     Construction is collective. If symmetric memory cannot be set up (no P2P access, a backend without it), `ok` is
     False and the object behaves exactly like FactoredExchange (NCCL all-gather): both are GPU paths of this library."""
@@ -187,6 +192,22 @@ class PeerExchange(FactoredExchange):
         self._side = None
         self.ok = True
         self.why = ""
+        self.profile = False
+        self._events = []
+
+    PHASES = ("wait_push_and_barrier", "head_reduce_shard", "barrier", "sh_rebuild_and_head_consume")
+
+    def stage_ms(self):
+        """Mean CUDA-event duration of each phase of finish() over the steps recorded while `profile` was set (this
+        rank; the barrier phases contain the wait for the slowest rank)."""
+        if not self._events:
+            return None
+        torch.cuda.synchronize()
+        n = len(self._events)
+        out = {name: sum(ev[i].elapsed_time(ev[i + 1]) for ev in self._events) / n for i, name in enumerate(self.PHASES)}
+        out["steps"] = n
+        self._events = []
+        return out
 
     def _setup(self, world, P, dev):
         key = (world, P, str(dev))
@@ -212,7 +233,7 @@ class PeerExchange(FactoredExchange):
             drgb_dst = (C.c_void_p * world)(*[p + 4 * (base + rank * P * 3) for p in ptrs])
             cam_dst = (C.c_void_p * world)(*[p + 4 * (base + n_rgb + rank * 3) for p in ptrs])
             dst.append((drgb_dst, cam_dst))
-            h0 = base + n_rgb + n_cam
+            h0 = base + n_rgb + n_cam                   # multiple of 4 floats: rows are 16-byte aligned
             heads.append((t[h0: h0 + P * 12], (mc + 4 * h0) if mc else 0))
         t.zero_()
         torch.cuda.synchronize(dev)
@@ -252,8 +273,8 @@ class PeerExchange(FactoredExchange):
         cb = _lib.READY_FN(_ready)
         _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
                                                     C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
-        if use_mc:      # the four non-SH gradients are added into every rank's head by the preprocess-backward kernel
-            _lib.check(lib.gsr_backward_peer_head(C.c_void_p(heads[self._parity][1])), "gsr_backward_peer_head")
+        if use_mc:      # the four non-SH gradients go to the local replica of the symmetric head (phase 0 of the switch reduce)
+            _lib.check(lib.gsr_backward_peer_head(C.c_void_p(heads[self._parity][0].data_ptr())), "gsr_backward_peer_head")
         return (cb, campos, drgb_dst, cam_dst), errors
 
     def finish(self, head, means3D, dsh_out, P, M, D):
@@ -269,13 +290,29 @@ class PeerExchange(FactoredExchange):
         dev = dsh_out.device
         main = torch.cuda.current_stream(dev)
         if mc:
+            lib = _lib.lib()
+            st = C.c_void_p(main.cuda_stream)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if self.profile else None
+            mark = (lambda i: ev[i].record(main)) if ev else (lambda i: None)
+            mark(0)
             # push kernel (side stream) and preprocess-backward (this stream) of EVERY rank are complete after this
             main.wait_stream(self._side)
             hdl.barrier(channel=0)
+            mark(1)
             with torch.cuda.device(dev):
-                _lib.check(_lib.lib().gsr_peer_consume(head_sym.data_ptr(), head.data_ptr(), P, int(head.numel() == 10 * P),
-                                                       C.c_void_p(main.cuda_stream)), "gsr_peer_consume")
-            (self.rebuild or _rebuild_cuda)(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
+                # phase 1: this rank's share of the head rows, summed over the replicas by the switch and broadcast
+                _lib.check(lib.gsr_peer_reduce_shard(C.c_void_p(mc), P, dist.get_rank(self.group), world, st),
+                           "gsr_peer_reduce_shard")
+                mark(2)
+                hdl.barrier(channel=1)          # every rank's share has landed in every replica
+                mark(3)
+                # phase 2 + SH rebuild in one launch (one thread per Gaussian does both)
+                _lib.check(lib.gsr_peer_finish(P, M, D, world, means3D.data_ptr(), campos_all.data_ptr(), drgb_all.data_ptr(),
+                                               dsh_out.data_ptr(), head_sym.data_ptr(), head.data_ptr(),
+                                               int(head.numel() == 10 * P), st), "gsr_peer_finish")
+            mark(4)
+            if ev:
+                self._events.append(ev)
             return
         w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         main.wait_stream(self._side)
@@ -292,6 +329,13 @@ def _rebuild_cuda(P, M, D, n_views, means3D, campos_all, drgb_all, dsh_out):
         rc = lib.gsr_sh_grad_from_views(P, M, D, n_views, means3D.data_ptr(), campos_all.data_ptr(), drgb_all.data_ptr(),
                                         dsh_out.data_ptr(), torch.cuda.current_stream(dsh_out.device).cuda_stream)
     _lib.check(rc, "gsr_sh_grad_from_views")
+
+
+def reduce_without_factoring(fx, head: torch.Tensor) -> torch.Tensor:
+    """A backward the installed factored exchange cannot serve (colours precomputed: M == 0, so there is no SH outer
+    product to factor) still has to return gradients summed over ranks: one all_reduce over the contiguous
+    parameter-gradient head, in the exchange's group."""
+    return allreduce_param_grads(head, group=getattr(fx, "group", None))
 
 
 def install_factored_exchange(group=None, enable: bool = True, rebuild=None, peer: bool = False) -> None:

@@ -23,7 +23,7 @@ CONFIGS = {
                desc="large scene: 6M Gaussians, SH3, 1920x1080, 8 views sharded by camera"),
     "C4": dict(P=1_000_000, sh_degree=3, W=1297, H=840, s0=0.012, seed=1004, surfel=True,
                desc="train_2dgs: 1M surfels, SH3, 1297x840, colour + 7-channel map fwd+bwd"),
-    "C5": dict(P=200_000, sh_degree=0, W=512, H=512, s0=0.03, seed=1005, surfel=False, forward_only=True, views_per_rank=16,
+    "C5": dict(P=200_000, sh_degree=0, W=512, H=512, s0=0.03, seed=1005, surfel=False, forward_only=True, sweep_views=128,
                desc="align_3dgs pose sweep: 200k Gaussians, SH0, 512x512, forward only x128 rotations"),
 }
 
@@ -119,7 +119,32 @@ def random_rotations(n, seed=128):
 
 
 def make_scene(name="C1", P=None, n_views=1, W=None, H=None, sh_degree=None, seed=None, random_bg=False,
-               rotations_npz=None):
+               rotations_npz=None, cameras=None):
+    """Seeded scene. Generated with ONE intra-op thread: torch's vectorised CPU kernels (exp, sigmoid, norm) take a
+    SIMD path for the body of a thread's chunk and a scalar path for its tail, and the two may differ in the last bit,
+    so with N threads the values at the N-1 chunk boundaries depend on N. One thread makes the bits a function of the
+    seed alone, on any host; bench.py prints a hash of the device-resident inputs (config.inputs_sha) to prove it."""
+    nthreads = torch.get_num_threads()
+    torch.set_num_threads(1)
+    try:
+        return _make_scene(name, P, n_views, W, H, sh_degree, seed, random_bg, rotations_npz, cameras)
+    finally:
+        torch.set_num_threads(nthreads)
+
+
+def stress_camera(W, H, k):
+    """Camera INSIDE the point cloud (at CENTER, looking along a direction that depends on k): about half of the
+    Gaussians are behind it, many sit near the z = 0.2 cull plane with radii of tens of pixels, and most of the rest
+    lie outside the frustum, i.e. on the +-1.3*tanfov clamp of computeCov2D (forward.cu:82-87)."""
+    a, b = math.radians(37.0 * k), math.radians(11.0 * k)
+    pitch = np.array([[1, 0, 0], [0, math.cos(b), -math.sin(b)], [0, math.sin(b), math.cos(b)]])
+    Robj = pitch @ yaw(math.degrees(a))
+    c = np.asarray(CENTER)
+    # view = Robj (x - c): the camera sits at the cloud's centre
+    return make_camera(W, H, R=Robj.T, T=-Robj @ c)
+
+
+def _make_scene(name, P, n_views, W, H, sh_degree, seed, random_bg, rotations_npz, cameras):
     cfg = dict(CONFIGS[name])
     P = cfg["P"] if P is None else P
     W = cfg["W"] if W is None else W
@@ -140,8 +165,8 @@ def make_scene(name="C1", P=None, n_views=1, W=None, H=None, sh_degree=None, see
     if M > 1:
         shs[:, 1:, :] = 0.1 * torch.randn(P, M - 1, 3, generator=g)
     bg = torch.rand(3, generator=g) if random_bg else torch.zeros(3)
-    cams = []
-    for v in range(n_views):
+    cams = list(cameras) if cameras is not None else []
+    for v in range(n_views if cameras is None else 0):
         if v == 0:
             cams.append(make_camera(W, H))
         elif rotations_npz is not None:

@@ -26,11 +26,21 @@ def main():
         grads = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 5 + rank, channels=(3, 7) if surfel else (3, 1, 1))]
         fo = fwd_f(sc, cam)
         keys = ("means3D", "sh", "opacity", "scales", "rotations")
-        # reference: plain backward + one all_reduce per tensor
-        ref = bwd_f(sc, cam, fo, grads)
-        ref = {k: ref[k].clone() for k in keys}
+        # reference: plain backward + one all_reduce per tensor, four times: the mean is the comparison value and the
+        # spread (float atomics in the blend backward) widens the tolerance, as tests/test_gpu_dgr_parity.py:_grad_ok does
+        runs = []
+        for _ in range(4):
+            r = bwd_f(sc, cam, fo, grads)
+            r = {k: r[k].clone() for k in keys}
+            for k in keys:
+                dist.all_reduce(r[k])
+            runs.append(r)
+        ref, tol = {}, {}
         for k in keys:
-            dist.all_reduce(ref[k])
+            st = torch.stack([r[k].double().reshape(-1) for r in runs])
+            ref[k] = st.mean(0)
+            spread = float((st.max(0).values - st.min(0).values).max())
+            tol[k] = 1e-6 * float(ref[k].abs().max()) + 2.0 * spread + 1e-4 * ref[k].abs()      # north_star: rtol 1e-4
         for mode in ("factored", "peer"):
             mv.install_factored_exchange(enable=True, peer=(mode == "peer"))
             try:
@@ -38,19 +48,37 @@ def main():
                     out = bwd_f(sc, cam, fo, grads)
                     torch.cuda.synchronize()
                     for k in keys:
-                        good, worst = h.close(out[k], ref[k], rtol=1e-3, atol_scale=1e-5)
-                        if not good:
+                        worst = float(((out[k].double().reshape(-1) - ref[k]).abs() / tol[k].clamp_min(1e-300)).max())
+                        if not worst <= 1.0:
                             ok = False
                             print(f"rank {rank} surfel={surfel} {mode} step {step} {k}: worst ratio {worst}", flush=True)
                 if mode == "peer":
                     from scorp_b200.diff_gaussian_rasterization import _C as c3
                     fx = c3._factored[0]
                     if rank == 0:
-                        print(f"peer exchange active: {fx.ok} multicast={getattr(fx, 'multicast', None)} {fx.why}", flush=True)
+                        print(f"peer exchange active: {fx.ok} multicast={getattr(fx, 'multicast', None)} world={world} {fx.why}", flush=True)
                     if not fx.ok:
                         ok = False
             finally:
                 mv.install_factored_exchange(enable=False)
+        # precomputed colours (M == 0) under an installed factored exchange: still summed over ranks (one all_reduce)
+        gcol = torch.Generator().manual_seed(11)
+        colors = torch.rand(sc.P, 3, generator=gcol).cuda()
+        fo_c = fwd_f(sc, cam, colors_precomp=colors)
+        plain = bwd_f(sc, cam, fo_c, grads)
+        want = {k: plain[k].clone() for k in ("means3D", "opacity", "scales", "rotations")}
+        for k in want:
+            dist.all_reduce(want[k])
+        mv.install_factored_exchange(enable=True, peer=True)
+        try:
+            out = bwd_f(sc, cam, fo_c, grads)
+            for k in want:
+                good, worst = h.close(out[k], want[k], rtol=1e-3, atol_scale=1e-5)     # two backward runs: atomics noise
+                if not good:
+                    ok = False
+                    print(f"rank {rank} surfel={surfel} precomputed colours {k}: worst ratio {worst}", flush=True)
+        finally:
+            mv.install_factored_exchange(enable=False)
     t = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:

@@ -114,6 +114,39 @@ def test_full_size_c2_bit_exact():
     rg = io["ranges"].long()
     assert int((rg[:, 1] - rg[:, 0]).sum()) == fo["num_rendered"]
     assert int(io["tiles_touched"].long().sum()) == fo["num_rendered"]
+    # and the gradients at full size (rtol 1e-4 + the reference's own atomics spread)
+    _full_size_gradients(sc, cam, fo, fr)
+
+
+def _full_size_gradients(sc, cam, fo, fr):
+    grads = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 5)]
+    go = h.ours_backward(sc, cam, fo, grads)
+    runs = [h.ref_backward(sc, cam, fr, grads) for _ in range(4)]
+    for k in ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations"):
+        _grad_ok("dL_d" + k, go[k], [r[k] for r in runs])
+    # invisible Gaussians get exact zeros, as the reference's zero-filled tensors keep
+    inv = fr["radii"] == 0
+    for k in ("means3D", "sh", "opacity", "scales", "rotations", "means2D"):
+        assert float(go[k][inv].abs().max()) == 0.0, k
+
+
+def test_full_size_c3_shape_bit_exact_and_gradients():
+    """BASELINE.json config[2]'s shape on one GPU: 6M Gaussians, SH3, 1920x1080 (one view of the 8)."""
+    ref_cuda = _need_ref()
+    sc = h.make("C3"); cam = sc.cameras[0]
+    fo = h.ours_forward(sc, cam); fr = h.ref_forward(sc, cam)
+    assert fo["num_rendered"] == fr["num_rendered"]
+    io, ir = h.ours_intermediates(fo), ref_cuda.dgr_intermediates(fr)
+    _assert_exact("radii", fo["radii"], fr["radii"])
+    _assert_exact("point_list_keys", io["point_list_keys"], ir["point_list_keys"])
+    _assert_exact("point_list", io["point_list"], ir["point_list"])
+    _assert_exact("ranges", io["ranges"], ir["ranges"])
+    _assert_exact("n_contrib", io["n_contrib"], ir["n_contrib"])
+    for k in ("color", "depth", "alpha"):
+        _assert_exact(k, fo[k], fr[k])
+    rg = io["ranges"].long()
+    assert int((rg[:, 1] - rg[:, 0]).max()) > 1024          # the crowded-tile sort path is the one exercised here
+    _full_size_gradients(sc, cam, fo, fr)
 
 
 def test_precomputed_colors_and_covariance():

@@ -93,6 +93,11 @@ def _factored_worker(rank, world, port, P, M, D, q):
         h.sh_grad_from_views_torch(P, M, D, 1, means, campos.view(1, 3), drgb.view(1, P, 3), mine)
         dist.all_reduce(mine)
         ok = ok and torch.allclose(mine, dsh, rtol=1e-4, atol=1e-5)
+        # precomputed colours (M == 0): the installed exchange cannot factor anything, the `_C` level then reduces the
+        # whole head with one all_reduce (multiview.reduce_without_factoring) instead of returning rank-local gradients
+        head0 = per_rank[rank][0][: P * 11].clone()
+        mv.reduce_without_factoring(fx, head0)
+        ok = ok and torch.allclose(head0.double(), want_head, rtol=1e-5, atol=1e-5)
         q.put((rank, bool(ok)))
     finally:
         dist.destroy_process_group()
