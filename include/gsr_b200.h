@@ -244,19 +244,22 @@ int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const
 /* Sum of the four non-SH parameter gradients over ranks, done in the NVSwitch (NVLS) in two phases so that the bytes a GPU
  * moves do not grow with the number of ranks. `head` is a symmetric buffer (same offset on every rank, with a multicast
  * mapping) of P rows of 12 floats (means3D xyz, opacity | scales, rotations, padding), 16-byte aligned.
- *   gsr_backward_peer_head(local replica)  arms the NEXT gsr_rasterize_backward / gsr_surfel_backward of this thread (SH
- *       colours only): its preprocess-backward kernel stores every Gaussian's row (zeros when invisible) into the local
- *       replica; dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations are then NOT written by that call. NULL disarms.
+ *   gsr_backward_peer_head(local replica, chunks, chunk_done, user)  arms the NEXT gsr_rasterize_backward /
+ *       gsr_surfel_backward of this thread (SH colours only): its preprocess-backward kernel stores every Gaussian's row
+ *       (zeros when invisible) into the local replica; dL_dmeans3D / dL_dopacity / dL_dscales / dL_drotations are then NOT
+ *       written by that call. The kernel runs as `chunks` launches over consecutive row ranges and chunk_done(user, k,
+ *       row0, rows) is called on the host right after launch k is enqueued, so the caller can reduce range k on another
+ *       stream while range k+1 is being computed. NULL disarms.
  *   -- cross-rank barrier --
- *   gsr_peer_reduce_shard(multicast address, P, rank, world)  rank r sums rows [r*P/world, (r+1)*P/world) over all
- *       replicas with multimem.ld_reduce and stores the sums into all replicas with multimem.st.
+ *   gsr_peer_reduce_shard(multicast address, row0, rows, rank, world)  rank r sums its 1/world share of rows
+ *       [row0, row0 + rows) over all replicas with multimem.ld_reduce and stores the sums into all replicas with multimem.st.
  *   -- cross-rank barrier --
- *   gsr_peer_consume(local replica, dst)  un-interleaves the summed rows into dst = the planar head [means3D 3P |
- *       opacity P | scales 3P (2P surfels) | rotations 4P]; gsr_peer_finish does that inside the SH rebuild kernel
- *       (gsr_sh_grad_from_views with the same first nine arguments), one launch for both. */
-int gsr_backward_peer_head(float* symmetric_head);
-int gsr_peer_reduce_shard(float* multicast_head, int P, int rank, int world, void* stream);
-int gsr_peer_consume(const float* symmetric_src, float* dst, int P, int surfel, void* stream);
+ *   gsr_peer_consume(local replica, dst, P, row0, rows)  un-interleaves the summed rows into dst = the planar head
+ *       [means3D 3P | opacity P | scales 3P (2P surfels) | rotations 4P]; gsr_peer_finish does that for all P rows inside
+ *       the SH rebuild kernel (gsr_sh_grad_from_views with the same first nine arguments), one launch for both. */
+int gsr_backward_peer_head(float* symmetric_head, int chunks, void (*chunk_done)(void* user, int k, int row0, int rows), void* user);
+int gsr_peer_reduce_shard(float* multicast_head, int row0, int rows, int rank, int world, void* stream);
+int gsr_peer_consume(const float* symmetric_src, float* dst, int P, int row0, int rows, int surfel, void* stream);
 int gsr_peer_finish(int P, int M, int D, int n_views, const float* means3D, const float* campos, const float* drgb,
                     float* dL_dsh, const float* head_rows, float* head_dst, int surfel, void* stream);
 int gsr_sh_grad_from_views(int P, int M, int D, int n_views, const float* means3D, const float* campos,

@@ -15,6 +15,7 @@ LIB_PATH = HERE / "libgsr_b200.so"
 c_void_p, c_int, c_size_t, c_float = C.c_void_p, C.c_int, C.c_size_t, C.c_float
 
 READY_FN = C.CFUNCTYPE(None, C.c_void_p)          # gsr_backward_early_rgb callback
+CHUNK_FN = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_int)     # gsr_backward_peer_head: chunk_done(user, k, row0, rows)
 ALLOC_FN = C.CFUNCTYPE(c_void_p, c_void_p, c_int, c_size_t)
 
 GSR_BUF_GEOM, GSR_BUF_BINNING, GSR_BUF_IMAGE = 0, 1, 2
@@ -109,9 +110,9 @@ SIGNATURES = {
     "gsr_clamped_color_grad": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "gsr_backward_early_rgb": (c_int, [_P, _P, _P]),
     "gsr_backward_early_rgb_peers": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), _P, _P, _P, _P]),
-    "gsr_backward_peer_head": (c_int, [_P]),
-    "gsr_peer_consume": (c_int, [_P, _P, c_int, c_int, _P]),
-    "gsr_peer_reduce_shard": (c_int, [_P, c_int, c_int, c_int, _P]),
+    "gsr_backward_peer_head": (c_int, [_P, c_int, _P, _P]),
+    "gsr_peer_consume": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
+    "gsr_peer_reduce_shard": (c_int, [_P, c_int, c_int, c_int, c_int, _P]),
     "gsr_peer_finish": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P, _P, c_int, _P]),
     "gsr_sh_grad_from_views": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P, _P]),
 }

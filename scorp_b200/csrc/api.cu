@@ -56,8 +56,8 @@ uint32_t* readback_pad() {
 }
 
 thread_local EarlyRgb g_early = { nullptr, nullptr, nullptr, false, {} };
-thread_local float* g_peer_head = nullptr;
-float* take_peer_head() { float* h = g_peer_head; g_peer_head = nullptr; return h; }
+thread_local PeerHead g_peer_head;
+PeerHead take_peer_head() { const PeerHead h = g_peer_head; g_peer_head = PeerHead{}; return h; }
 EarlyRgb take_early_rgb() { const EarlyRgb e = g_early; g_early.armed = false; return e; }
 
 }  // namespace gsr
@@ -287,7 +287,7 @@ static int backward_impl(
     // whatever was armed for "the next backward of this thread" is consumed by THIS call, also when it returns early:
     // the armed state holds raw pointers into a caller-owned gradient arena and into peer buffers
     const EarlyRgb e = take_early_rgb();
-    float* const peer_head = take_peer_head();
+    const PeerHead peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
     if (P == 0) return GSR_OK;
     const int W = s->image_width, H = s->image_height;
@@ -335,8 +335,12 @@ static int backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dcov3D = dL_dcov3D; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
-    b.peer_head = peer_head;
-    if ((rc = check_cuda(launch_preprocess_backward(b, st), "preprocess backward launch"))) return rc;
+    b.peer_head = (shs && !raw) ? peer_head.head : nullptr;
+    // multi-GPU: with an armed head the kernel runs as several launches over consecutive row ranges and the caller is told
+    // after each one, so the cross-rank reduction of a range overlaps the computation of the next (gsr_backward_peer_head)
+    PeerHead ph = peer_head; ph.head = b.peer_head;
+    if ((rc = check_cuda(launch_in_row_chunks(P, 128, ph, [&](int r0, int r1) {
+            b.row_begin = r0; b.row_end = r1; return launch_preprocess_backward(b, st); }), "preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "preprocess backward");
 }
@@ -347,15 +351,18 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void*), void* user) {
     return GSR_OK;
 }
 
-int gsr_backward_peer_head(float* symmetric_head) {
+int gsr_backward_peer_head(float* symmetric_head, int chunks, void (*chunk_done)(void*, int, int, int), void* user) {
     if ((uintptr_t)symmetric_head & 15) { set_error("gsr_backward_peer_head: the head must be 16-byte aligned"); return GSR_EINVAL; }
-    gsr::g_peer_head = symmetric_head; return GSR_OK;
+    if (symmetric_head && (chunks < 1 || chunks > 64)) { set_error("gsr_backward_peer_head: 1..64 chunks"); return GSR_EINVAL; }
+    gsr::PeerHead h; h.head = symmetric_head; h.chunks = chunks; h.chunk_done = chunk_done; h.user = user;
+    gsr::g_peer_head = symmetric_head ? h : gsr::PeerHead{};
+    return GSR_OK;
 }
 
-int gsr_peer_consume(const float* symmetric_src, float* dst, int P, int surfel, void* stream) {
-    if (P == 0) return GSR_OK;
-    if (P < 0 || !symmetric_src || !dst) { set_error("gsr_peer_consume: bad argument"); return GSR_EINVAL; }
-    return check_cuda(gsr::launch_peer_consume(symmetric_src, dst, P, surfel != 0, (cudaStream_t)stream), "peer consume launch");
+int gsr_peer_consume(const float* symmetric_src, float* dst, int P, int row0, int rows, int surfel, void* stream) {
+    if (P == 0 || rows == 0) return GSR_OK;
+    if (P < 0 || row0 < 0 || rows < 0 || row0 + rows > P || !symmetric_src || !dst) { set_error("gsr_peer_consume: bad argument"); return GSR_EINVAL; }
+    return check_cuda(gsr::launch_peer_consume(symmetric_src, dst, P, row0, rows, surfel != 0, (cudaStream_t)stream), "peer consume launch");
 }
 
 int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,

@@ -111,12 +111,32 @@ EarlyRgb take_early_rgb();          // returns the armed request (armed == false
 cudaError_t launch_clamped_rgb_from_acc(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                         int rgb_off, float* drgb, cudaStream_t st);
 // head rows [P][12] -> the planar arena head [means3D 3P | opacity P | scales 3P (2P) | rotations 4P]
-cudaError_t launch_peer_consume(const float* src, float* dst, int P, bool surfel, cudaStream_t st);
+cudaError_t launch_peer_consume(const float* src, float* dst, int P, int row0, int rows, bool surfel, cudaStream_t st);
 // the same values written straight into every rank's gather buffer through peer pointers (all-gather by stores)
 cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                     int rgb_off, const PeerDst& dst, cudaStream_t main);
 
-float* take_peer_head();            // api.cu: symmetric head (local replica) armed for the next backward of this thread (NULL if none); disarms
+// gsr_backward_peer_head (api.cu): armed per thread for the next backward call; take_peer_head returns it and disarms
+struct PeerHead {
+    float* head = nullptr;              // local replica of the symmetric head rows (NULL: not armed)
+    int chunks = 1;                     // the preprocess-backward runs as this many launches over consecutive row ranges ...
+    void (*chunk_done)(void*, int, int, int) = nullptr;     // ... and this is called (user, k, row0, rows) after each is enqueued
+    void* user = nullptr;
+};
+PeerHead take_peer_head();
+// shared by api.cu / surfel_api.cu: runs launch(row_begin, row_end) over the armed chunking (one launch when not armed)
+template <class Launch>
+inline cudaError_t launch_in_row_chunks(int P, int tile, const PeerHead& ph, Launch&& launch) {
+    const int chunks = (ph.head && ph.chunks > 1) ? ph.chunks : 1;
+    const int per = ((P + chunks - 1) / chunks + tile - 1) / tile * tile;      // chunk starts stay multiples of the kernel's tile
+    for (int k = 0, r0 = 0; r0 < P; ++k, r0 += per) {
+        const int r1 = r0 + per < P ? r0 + per : P;
+        cudaError_t e = launch(r0, r1);
+        if (e != cudaSuccess) return e;
+        if (ph.head && ph.chunk_done) ph.chunk_done(ph.user, k, r0, r1 - r0);
+    }
+    return cudaSuccess;
+}
 uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
 
 // error plumbing (api.cu)
@@ -278,6 +298,7 @@ struct BwdArgs {
     // gsr_backward_peer_head: this rank's replica of the symmetric head [P][12] = (means3D xyz, opacity | scales xyz,
     // rot r | rot xyz, 0); the four parameter gradients are stored there (every row) instead of into the arena
     float* peer_head = nullptr;
+    int row_begin = 0, row_end = 0;     // Gaussians this launch covers (row_begin a multiple of SH_TILE); set by the caller
 };
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st);
 

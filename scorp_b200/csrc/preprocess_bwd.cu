@@ -10,6 +10,8 @@
 
 namespace gsr {
 
+static_assert(SH_TILE == 128, "api.cu / surfel_api.cu align the row-range launches (launch_in_row_chunks) to 128 rows");
+
 // M3: 3 * SH coefficients per Gaussian (0: colours were precomputed). RAW: model-space variant -- SH rows split into
 // features_dc / features_rest, and the gradients are taken through sigmoid / exp / normalize to the stored parameters.
 template <int M3, bool RAW>
@@ -18,10 +20,10 @@ preprocess_backward_kernel(BwdArgs a) {
     constexpr int TILE_FLOATS = M3 ? SH_TILE * ShTile<M3>::STRIDE : 4;
     __shared__ __align__(16) float s_sh[TILE_FLOATS];
     __shared__ uint8_t s_vis[SH_TILE];
-    const size_t row0 = (size_t)blockIdx.x * SH_TILE;
-    const int nrows = min(SH_TILE, a.P - (int)row0);
+    const size_t row0 = (size_t)a.row_begin + (size_t)blockIdx.x * SH_TILE;     // this launch covers rows [row_begin, row_end)
+    const int nrows = min(SH_TILE, a.row_end - (int)row0);
     const int idx = (int)row0 + threadIdx.x;
-    const bool valid = idx < a.P;
+    const bool valid = idx < a.row_end;
     const bool vis = valid && a.radii[idx] > 0;
     if constexpr (M3 != 0) {
         s_vis[threadIdx.x] = vis;
@@ -197,7 +199,8 @@ preprocess_backward_kernel(BwdArgs a) {
 }
 
 cudaError_t launch_preprocess_backward(const BwdArgs& a, cudaStream_t st) {
-    const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    const int blocks = (a.row_end - a.row_begin + SH_TILE - 1) / SH_TILE;
+    if (blocks <= 0) return cudaSuccess;
     if (a.raw) {
         switch (3 * a.M) {
         case 3:  preprocess_backward_kernel<3, true><<<blocks, SH_TILE, 0, st>>>(a); break;

@@ -87,26 +87,33 @@ __device__ __forceinline__ void head_row_to_planar(const float* __restrict__ src
     }
 }
 __global__ void __launch_bounds__(256)
-peer_consume_kernel(const float* __restrict__ src, float* __restrict__ dst, int P, bool surfel) {
+peer_consume_kernel(const float* __restrict__ src, float* __restrict__ dst, int P, int row0, int rows, bool surfel) {
     const int g = blockIdx.x * 256 + threadIdx.x;
-    if (g < P) head_row_to_planar(src, dst, P, g, surfel);
+    if (g < rows) head_row_to_planar(src, dst, P, row0 + g, surfel);
 }
-cudaError_t launch_peer_consume(const float* src, float* dst, int P, bool surfel, cudaStream_t st) {
-    peer_consume_kernel<<<(P + 255) / 256, 256, 0, st>>>(src, dst, P, surfel);
+cudaError_t launch_peer_consume(const float* src, float* dst, int P, int row0, int rows, bool surfel, cudaStream_t st) {
+    peer_consume_kernel<<<(rows + 255) / 256, 256, 0, st>>>(src, dst, P, row0, rows, surfel);
     return cudaGetLastError();
 }
 
 // Phase 1 of the head reduce (common.cuh): this rank's share of the 16-byte groups, [q0, q1), summed over all replicas by
-// the switch (multimem.ld_reduce) and stored back into all replicas (multimem.st). One group per thread per round,
-// consecutive lanes on consecutive groups (a warp instruction covers 512 contiguous bytes).
+// the switch (multimem.ld_reduce) and stored back into all replicas (multimem.st). A ld_reduce is a round trip through
+// the switch (microseconds), so the kernel is bound by bytes in flight: every thread issues U independent 16-byte
+// reductions (consecutive lanes on consecutive groups: a warp instruction covers 512 contiguous bytes) before the
+// first dependent store. Measured at 2 GPUs, 24 MB share: U = 1 0.150 ms.
+template <int U>
 __global__ void __launch_bounds__(256)
 peer_reduce_shard_kernel(float4* __restrict__ mc, size_t q0, size_t q1) {
-    for (size_t q = q0 + (size_t)blockIdx.x * 256 + threadIdx.x; q < q1; q += (size_t)gridDim.x * 256)
-        mc_st4(mc + q, mc_ld_reduce4(mc + q));
+    const size_t step = (size_t)gridDim.x * 256 * U;
+    for (size_t base = q0 + (size_t)blockIdx.x * 256 * U + threadIdx.x; base < q1; base += step) {
+        float4 v[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (base + (size_t)u * 256 < q1) v[u] = mc_ld_reduce4(mc + base + (size_t)u * 256);
+#pragma unroll
+        for (int u = 0; u < U; ++u) if (base + (size_t)u * 256 < q1) mc_st4(mc + base + (size_t)u * 256, v[u]);
+    }
 }
 
-// One thread per Gaussian, SH_TILE Gaussians per CTA: the basis is evaluated once per (Gaussian, view) and the 3M
-// sums stay in registers; rows leave through the shared tile of sh.cuh so the stores are unit-stride.
 // head != NULL: also hands over the switch-reduced head rows of the same Gaussians (phase 2 of the head reduce).
 template <int M3>
 __global__ void __launch_bounds__(SH_TILE)
@@ -198,16 +205,21 @@ extern "C" int gsr_peer_finish(int P, int M, int D, int n_views, const float* me
     return sh_from_views_impl(P, M, D, n_views, means3D, campos, drgb, dL_dsh, head_rows, head_dst, surfel != 0, stream);
 }
 
-extern "C" int gsr_peer_reduce_shard(float* multicast_head, int P, int rank, int world, void* stream) {
-    if (P == 0) return GSR_OK;
-    if (P < 0 || !multicast_head || world < 1 || rank < 0 || rank >= world || ((uintptr_t)multicast_head & 15)) {
+extern "C" int gsr_peer_reduce_shard(float* multicast_head, int row0, int rows, int rank, int world, void* stream) {
+    if (rows == 0) return GSR_OK;
+    if (row0 < 0 || rows < 0 || !multicast_head || world < 1 || rank < 0 || rank >= world || ((uintptr_t)multicast_head & 15)) {
         set_error("gsr_peer_reduce_shard: bad argument"); return GSR_EINVAL;
     }
-    const size_t groups = (size_t)P * (PEER_HEAD_STRIDE / 4), per = (groups + world - 1) / world;
-    const size_t q0 = per * (size_t)rank, q1 = q0 + per < groups ? q0 + per : groups;
+    // this rank's share of the 16-byte groups of rows [row0, row0 + rows)
+    const size_t g0 = (size_t)row0 * (PEER_HEAD_STRIDE / 4), groups = (size_t)rows * (PEER_HEAD_STRIDE / 4);
+    const size_t per = (groups + world - 1) / world;
+    const size_t q0 = g0 + per * (size_t)rank, q1 = (per * (size_t)(rank + 1) < groups ? g0 + per * (size_t)(rank + 1) : g0 + groups);
     if (q0 >= q1) return GSR_OK;
-    const size_t want = (q1 - q0 + 255) / 256;
-    const int blocks = (int)(want < 148 * 16 ? want : 148 * 16);        // grid-stride; 16 CTAs of 256 per SM keep the switch busy
-    peer_reduce_shard_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_head), q0, q1);
+    constexpr int U = 8;
+    const size_t want = (q1 - q0 + 256 * U - 1) / (256 * U);
+    // grid-stride, one CTA of 256 threads per SM, 8 groups per thread: 4.8 MB in flight (the link's bandwidth x the
+    // round trip through the switch), and a footprint small enough to co-reside with the kernel it is pipelined with
+    const int blocks = (int)(want < 148 ? want : 148);
+    peer_reduce_shard_kernel<U><<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_head), q0, q1);
     return check_cuda(cudaGetLastError(), "peer head reduce launch");
 }

@@ -113,6 +113,7 @@ struct SurfelBwdArgs {
     const float* opacities = nullptr;
     float* dL_dsh_rest = nullptr;
     bool raw = false;
+    int row_begin = 0, row_end = 0;     // as BwdArgs
     float* peer_head = nullptr;    // as BwdArgs::peer_head: [P][12] = (means3D xyz, opacity | scales xy, rot rx | rot yz, 0, 0)
 };
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st);

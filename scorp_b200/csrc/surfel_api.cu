@@ -177,7 +177,7 @@ static int surfel_backward_impl(
 {
     cudaStream_t st = (cudaStream_t)stream;
     const EarlyRgb e = take_early_rgb();         // consumed by THIS call, also when it returns early (see api.cu)
-    float* const peer_head = take_peer_head();
+    const PeerHead peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
     if (P == 0) return GSR_OK;
     const int W = s->image_width, H = s->image_height;
@@ -224,8 +224,10 @@ static int surfel_backward_impl(
     b.dL_dmeans2D = dL_dmeans2D; b.dL_dcolors = dL_dcolors; b.dL_dopacity = dL_dopacity; b.dL_dmeans3D = dL_dmeans3D;
     b.dL_dtransMat = dL_dtransMat; b.dL_dsh = shs ? dL_dsh : nullptr; b.dL_dscales = dL_dscales; b.dL_drotations = dL_drotations;
     if (raw) { b.raw = true; b.shs_rest = raw->shs_rest; b.opacities = raw->opacities; b.dL_dsh_rest = raw->dL_dsh_rest; }
-    b.peer_head = peer_head;
-    if ((rc = check_cuda(launch_surfel_preprocess_backward(b, st), "surfel preprocess backward launch"))) return rc;
+    b.peer_head = (shs && !raw) ? peer_head.head : nullptr;
+    PeerHead ph = peer_head; ph.head = b.peer_head;             // multi-GPU: row-range launches, see gsr_rasterize_backward
+    if ((rc = check_cuda(launch_in_row_chunks(P, 128, ph, [&](int r0, int r1) {
+            b.row_begin = r0; b.row_end = r1; return launch_surfel_preprocess_backward(b, st); }), "surfel preprocess backward launch"))) return rc;
     prof_mark(6, st);
     return stage_check(s, st, "surfel preprocess backward");
 }

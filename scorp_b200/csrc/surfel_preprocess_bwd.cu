@@ -19,10 +19,10 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
     constexpr int TILE_FLOATS = M3 ? SH_TILE * ShTile<M3>::STRIDE : 4;
     __shared__ __align__(16) float s_sh[TILE_FLOATS];
     __shared__ uint8_t s_vis[SH_TILE];
-    const size_t row0 = (size_t)blockIdx.x * SH_TILE;
-    const int nrows = min(SH_TILE, a.P - (int)row0);
+    const size_t row0 = (size_t)a.row_begin + (size_t)blockIdx.x * SH_TILE;     // this launch covers rows [row_begin, row_end)
+    const int nrows = min(SH_TILE, a.row_end - (int)row0);
     const int idx = (int)row0 + threadIdx.x;
-    const bool valid = idx < a.P;
+    const bool valid = idx < a.row_end;
     const bool vis = valid && a.radii[idx] > 0;
     if constexpr (M3 != 0) {
         s_vis[threadIdx.x] = vis;
@@ -236,7 +236,8 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
 }
 
 cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream_t st) {
-    const int blocks = (a.P + SH_TILE - 1) / SH_TILE;
+    const int blocks = (a.row_end - a.row_begin + SH_TILE - 1) / SH_TILE;
+    if (blocks <= 0) return cudaSuccess;
     if (a.raw) {
         switch (3 * a.M) {
         case 3:  surfel_preprocess_backward_kernel<3, true><<<blocks, SH_TILE, 0, st>>>(a); break;

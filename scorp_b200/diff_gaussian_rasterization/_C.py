@@ -64,13 +64,13 @@ class _Arena:
         return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
 
 
-def _arm_early(lib, fx, g_drgb, campos, P):
+def _arm_early(lib, fx, g_drgb, campos, P, rebuild_args=None):
     """Factored multi-GPU exchange: ask the next backward call to hand out the clamped colour gradient right after
     its blend kernel and start gathering it there (gsr_backward_early_rgb). Returns (callback to keep alive until the
     backward returned, list that receives an exception raised inside it); no reference cycle: the closure does not
     see the callback object."""
     if hasattr(fx, "arm"):             # multiview.PeerExchange: the backward pushes drgb into peer memory itself
-        armed = fx.arm(lib, campos, P, g_drgb.device)
+        armed = fx.arm(lib, campos, P, g_drgb.device, rebuild_args)     # rebuild_args = (means3D, g_sh, M, degree, head)
         if armed is not None:
             return armed
     errors = []
@@ -224,7 +224,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
                       degree, False, debug)
-        early = _arm_early(lib, fx, g_drgb, campos, P) if fx is not None else None
+        early = _arm_early(lib, fx, g_drgb, campos, P, (means3D, g_sh, M, int(degree), flat[: P * 11])) if fx is not None else None
         with torch.cuda.device(dev):
             rc = lib.gsr_rasterize_backward(
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),

@@ -92,7 +92,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
                       degree, False, debug)
-        early = _arm_early(lib, fx, g_drgb, campos, P) if fx is not None else None
+        early = _arm_early(lib, fx, g_drgb, campos, P, (means3D, g_sh, M, int(degree), flat[: P * 10])) if fx is not None else None
         with torch.cuda.device(dev):
             rc = lib.gsr_surfel_backward(
                 C.byref(s), P, M, int(R), ptr(means3D), ptr(sh), ptr(colors), ptr(scales), ptr(rotations),

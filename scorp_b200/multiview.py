@@ -176,8 +176,10 @@ class PeerExchange(FactoredExchange):
     traffic does not grow with the number of ranks (csrc/common.cuh): the preprocess-backward kernel stores its rows
     into the local replica of a symmetric head (gsr_backward_peer_head); after a barrier every rank sums ITS 1/world
     share of the rows over all replicas with multimem.ld_reduce and broadcasts the sums with multimem.st
-    (gsr_peer_reduce_shard); after a second barrier the rebuild kernel also hands the summed rows over
-    (gsr_peer_finish) -- a step then contains no NCCL call at all. Without multicast support they are all-reduced by
+    (gsr_peer_reduce_shard); after a second barrier gsr_peer_consume hands the summed rows over. That sequence is
+    pipelined with the preprocess-backward kernel row range by row range (the library runs it as CHUNKS launches and
+    calls back after each), and the SH rebuild runs on the side stream right behind the push and a barrier of its own,
+    so both travel underneath the preprocess-backward kernel -- a step contains no NCCL call at all. Without multicast support they are all-reduced by
     NCCL underneath the rebuild kernel.
 
     `profile = True` records CUDA events around the phases of finish(); `stage_ms()` returns their mean durations.
@@ -195,16 +197,30 @@ class PeerExchange(FactoredExchange):
         self.profile = False
         self._events = []
 
-    PHASES = ("wait_push_and_barrier", "head_reduce_shard", "barrier", "sh_rebuild_and_head_consume")
+    # row ranges the preprocess-backward kernel is split into for the pipelined head reduce (GSR_PEER_CHUNKS overrides).
+    # Measured at C2 on 2 GPUs (profiles/r02_mg2_chunks.md): 1 range 1.750 ms/step, 2 ranges 1.743, 4 ranges 1.792 -- what
+    # the pipelining takes off the tail comes back as a slower preprocess-backward stage, so the default is one range.
+    CHUNKS = int(os.environ.get("GSR_PEER_CHUNKS", "1"))
 
     def stage_ms(self):
-        """Mean CUDA-event duration of each phase of finish() over the steps recorded while `profile` was set (this
-        rank; the barrier phases contain the wait for the slowest rank)."""
+        """Mean CUDA-event durations over the steps recorded while `profile` was set (this rank): `exposed_tail` is what
+        the step pays after its last preprocess-backward launch (join of the reduce and side streams); per row range,
+        the time from the end of its preprocess-backward launch to its summed rows sitting in the arena (two barriers,
+        which include waiting for the slowest rank, the switch reduce and the hand-over); and the side stream's barrier
+        and SH rebuild, which run underneath the preprocess-backward kernel."""
         if not self._events:
             return None
         torch.cuda.synchronize()
         n = len(self._events)
-        out = {name: sum(ev[i].elapsed_time(ev[i + 1]) for ev in self._events) / n for i, name in enumerate(self.PHASES)}
+        out = {"exposed_tail": sum(ev[0].elapsed_time(ev[1]) for ev, _, _ in self._events) / n}
+        side = [m for _, m, _ in self._events if len(m) == 3]
+        if side:
+            out["side:barrier_after_push"] = sum(m[0].elapsed_time(m[1]) for m in side) / len(side)
+            out["side:sh_rebuild"] = sum(m[1].elapsed_time(m[2]) for m in side) / len(side)
+        chunks = [c for _, _, c in self._events if c]
+        if chunks:
+            k = min(len(c) for c in chunks)
+            out["range_reduce_ms"] = [sum(c[i][0].elapsed_time(c[i][1]) for c in chunks) / len(chunks) for i in range(k)]
         out["steps"] = n
         self._events = []
         return out
@@ -240,11 +256,18 @@ class PeerExchange(FactoredExchange):
         dist.barrier(group=grp)
         self._symm = {key: (t, hdl, views, dst, heads)}
         self._side = torch.cuda.Stream(dev)
+        # high priority: the reduce kernels and barriers of range k get SM slots as soon as blocks of the
+        # preprocess-backward launch of range k+1 (main stream, normal priority, fills every SM) retire
+        self._red = torch.cuda.Stream(dev, priority=-1)
         self.multicast = bool(mc)
         return self._symm[key]
 
-    def arm(self, lib, campos, P, dev):
+    def arm(self, lib, campos, P, dev, rebuild_args=None):
         """Arm the next backward of this thread (called by the `_C` level in place of gsr_backward_early_rgb).
+        rebuild_args = (means3D, dsh_out, M, D, head_dst): with a multicast mapping the SH rebuild is enqueued on the side
+        stream right behind the push and its barrier, i.e. it runs underneath the preprocess-backward kernel of the main
+        stream, and the switch reduce of the head rows is pipelined with that kernel row range by row range (CHUNKS
+        launches; range k is reduced on the reduce stream while range k+1 is computed).
         Returns (objects to keep alive until the backward returned, list receiving an exception of the callback)."""
         from . import _lib
         world = self._world()
@@ -259,11 +282,32 @@ class PeerExchange(FactoredExchange):
         drgb_dst, cam_dst = dst[self._parity]
         campos = campos.reshape(3).contiguous()
         side = self._side
-        use_mc = heads[self._parity][1] != 0
+        use_mc = heads[self._parity][1] != 0 and rebuild_args is not None
+        drgb_all, campos_all = views[self._parity]
+        profile, marks = self.profile, []
+        self._marks = marks
+        rebuild = self.rebuild or _rebuild_cuda
 
         def _ready(_user):
             if use_mc:
-                return                             # one barrier on the main stream in finish() covers push and head
+                # the push kernel is enqueued on the side stream; behind it, on the same stream: a barrier (all ranks'
+                # colour gradients have landed) and the SH rebuild, which then overlaps the preprocess-backward kernel the
+                # library enqueues on the main stream right after this callback returns
+                try:
+                    means3D, dsh_out, M, D, _ = rebuild_args
+                    with torch.cuda.stream(side):
+                        if profile:
+                            marks.extend(torch.cuda.Event(enable_timing=True) for _ in range(3))
+                            marks[0].record(side)
+                        hdl.barrier(channel=2)
+                        if profile:
+                            marks[1].record(side)
+                        rebuild(P, M, D, world, means3D, campos_all, drgb_all, dsh_out)
+                        if profile:
+                            marks[2].record(side)
+                except Exception as ex:
+                    errors.append(ex)
+                return
             try:
                 with torch.cuda.stream(side):      # after the push kernel: all ranks' stores have landed once this passes
                     hdl.barrier(channel=0)
@@ -273,9 +317,42 @@ class PeerExchange(FactoredExchange):
         cb = _lib.READY_FN(_ready)
         _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
                                                     C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
+        self._armed_mc = use_mc
+        keep = [cb, campos, drgb_dst, cam_dst]
         if use_mc:      # the four non-SH gradients go to the local replica of the symmetric head (phase 0 of the switch reduce)
-            _lib.check(lib.gsr_backward_peer_head(C.c_void_p(heads[self._parity][0].data_ptr())), "gsr_backward_peer_head")
-        return (cb, campos, drgb_dst, cam_dst), errors
+            head_sym, mc = heads[self._parity]
+            head_dst = rebuild_args[4]
+            surfel = int(head_dst.numel() == 10 * P)
+            red, rank = self._red, dist.get_rank(self.group)
+            red_st = C.c_void_p(red.cuda_stream)
+            main = torch.cuda.current_stream(dev)
+            cmarks = []
+            self._cmarks = cmarks
+
+            def _chunk(_user, k, row0, rows):
+                # launch k of the preprocess-backward kernel (rows [row0, row0 + rows)) is enqueued on the main stream:
+                # behind it, on the reduce stream, barrier -> this rank's share summed in the switch and broadcast ->
+                # barrier -> the summed rows handed to the arena, while the main stream computes the next range
+                try:
+                    e = torch.cuda.Event(enable_timing=profile)
+                    e.record(main)
+                    red.wait_event(e)
+                    with torch.cuda.stream(red):
+                        hdl.barrier(channel=0)              # every rank has stored these rows
+                        _lib.check(lib.gsr_peer_reduce_shard(C.c_void_p(mc), row0, rows, rank, world, red_st), "gsr_peer_reduce_shard")
+                        hdl.barrier(channel=1)              # every rank's share has landed in every replica
+                        _lib.check(lib.gsr_peer_consume(head_sym.data_ptr(), head_dst.data_ptr(), P, row0, rows, surfel, red_st),
+                                   "gsr_peer_consume")
+                        if profile:
+                            e2 = torch.cuda.Event(enable_timing=True); e2.record(red)
+                            cmarks.append((e, e2))
+                except Exception as ex:                     # never let an exception cross the C ABI
+                    errors.append(ex)
+
+            ccb = _lib.CHUNK_FN(_chunk)
+            keep.append(ccb)
+            _lib.check(lib.gsr_backward_peer_head(C.c_void_p(head_sym.data_ptr()), self.CHUNKS, ccb, None), "gsr_backward_peer_head")
+        return tuple(keep), errors
 
     def finish(self, head, means3D, dsh_out, P, M, D):
         world = self._world()
@@ -289,30 +366,17 @@ class PeerExchange(FactoredExchange):
         self._parity ^= 1
         dev = dsh_out.device
         main = torch.cuda.current_stream(dev)
-        if mc:
-            lib = _lib.lib()
-            st = C.c_void_p(main.cuda_stream)
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)] if self.profile else None
-            mark = (lambda i: ev[i].record(main)) if ev else (lambda i: None)
-            mark(0)
-            # push kernel (side stream) and preprocess-backward (this stream) of EVERY rank are complete after this
-            main.wait_stream(self._side)
-            hdl.barrier(channel=0)
-            mark(1)
-            with torch.cuda.device(dev):
-                # phase 1: this rank's share of the head rows, summed over the replicas by the switch and broadcast
-                _lib.check(lib.gsr_peer_reduce_shard(C.c_void_p(mc), P, dist.get_rank(self.group), world, st),
-                           "gsr_peer_reduce_shard")
-                mark(2)
-                hdl.barrier(channel=1)          # every rank's share has landed in every replica
-                mark(3)
-                # phase 2 + SH rebuild in one launch (one thread per Gaussian does both)
-                _lib.check(lib.gsr_peer_finish(P, M, D, world, means3D.data_ptr(), campos_all.data_ptr(), drgb_all.data_ptr(),
-                                               dsh_out.data_ptr(), head_sym.data_ptr(), head.data_ptr(),
-                                               int(head.numel() == 10 * P), st), "gsr_peer_finish")
-            mark(4)
+        if mc and getattr(self, "_armed_mc", False):
+            # everything was enqueued from inside the backward call (arm()'s callbacks): the head reduce on the reduce
+            # stream, row range by row range, and the SH rebuild on the side stream; the main stream only joins them
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)] if self.profile else None
             if ev:
-                self._events.append(ev)
+                ev[0].record(main)
+            main.wait_stream(self._red)
+            main.wait_stream(self._side)
+            if ev:
+                ev[1].record(main)
+                self._events.append((ev, list(getattr(self, "_marks", [])), list(getattr(self, "_cmarks", []))))
             return
         w_r = dist.all_reduce(head, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
         main.wait_stream(self._side)

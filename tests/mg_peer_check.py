@@ -41,8 +41,9 @@ def main():
             ref[k] = st.mean(0)
             spread = float((st.max(0).values - st.min(0).values).max())
             tol[k] = 1e-6 * float(ref[k].abs().max()) + 2.0 * spread + 1e-4 * ref[k].abs()      # north_star: rtol 1e-4
-        for mode in ("factored", "peer"):
-            mv.install_factored_exchange(enable=True, peer=(mode == "peer"))
+        for mode in ("factored", "peer", "peer3"):       # peer3: the head reduce pipelined over 3 row ranges
+            mv.PeerExchange.CHUNKS = 3 if mode == "peer3" else 1
+            mv.install_factored_exchange(enable=True, peer=mode.startswith("peer"))
             try:
                 for step in range(3):       # three steps: both parities of the double buffer, and reuse
                     out = bwd_f(sc, cam, fo, grads)
@@ -52,7 +53,7 @@ def main():
                         if not worst <= 1.0:
                             ok = False
                             print(f"rank {rank} surfel={surfel} {mode} step {step} {k}: worst ratio {worst}", flush=True)
-                if mode == "peer":
+                if mode.startswith("peer"):
                     from scorp_b200.diff_gaussian_rasterization import _C as c3
                     fx = c3._factored[0]
                     if rank == 0:
@@ -61,6 +62,7 @@ def main():
                         ok = False
             finally:
                 mv.install_factored_exchange(enable=False)
+                mv.PeerExchange.CHUNKS = 1
         # precomputed colours (M == 0) under an installed factored exchange: still summed over ranks (one all_reduce)
         gcol = torch.Generator().manual_seed(11)
         colors = torch.rand(sc.P, 3, generator=gcol).cuda()

@@ -58,3 +58,33 @@ def test_rebuild_kernel_matches_torch_for_several_views():
     assert torch.equal(out2.view(P, M, 3)[:, 4:], torch.zeros(P, M - 4, 3, device="cuda"))
     with pytest.raises(_lib.GsrError):
         mv._rebuild_cuda(P, 3, 3, V, means, campos, drgb, out)   # (D+1)^2 > M
+
+
+@pytest.mark.parametrize("surfel", [False, True])
+def test_peer_consume_and_fused_finish_agree(surfel):
+    """Phase 2 of the switch reduce on one GPU: gsr_peer_consume (head rows [P][12] -> planar head) and gsr_peer_finish
+    (the same inside the SH rebuild kernel) must give identical results, and the planar head must hold the rows' fields
+    in the arena order means3D | opacity | scales | rotations."""
+    import ctypes as C
+    torch.manual_seed(5)
+    P, M, D, V = 7001, 16, 3, 3
+    lib = _lib.lib()
+    st = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rows = torch.randn(P, 12, device="cuda")
+    means = torch.randn(P, 3, device="cuda"); campos = torch.randn(V, 3, device="cuda") * 4
+    drgb = torch.randn(V, P, 3, device="cuda")
+    nh = 10 if surfel else 11
+    head_a = torch.empty(P * nh, device="cuda"); head_b = torch.empty_like(head_a)
+    dsh_a = torch.empty(P * M * 3, device="cuda"); dsh_b = torch.empty_like(dsh_a)
+    # handed over in three row ranges, as the pipelined reduce does
+    for r0, n in ((0, 3072), (3072, 3072), (6144, P - 6144)):
+        assert lib.gsr_peer_consume(rows.data_ptr(), head_a.data_ptr(), P, r0, n, int(surfel), st) == 0
+    mv._rebuild_cuda(P, M, D, V, means, campos, drgb, dsh_a)
+    assert lib.gsr_peer_finish(P, M, D, V, means.data_ptr(), campos.data_ptr(), drgb.data_ptr(), dsh_b.data_ptr(),
+                               rows.data_ptr(), head_b.data_ptr(), int(surfel), st) == 0
+    assert torch.equal(head_a, head_b) and torch.equal(dsh_a, dsh_b)
+    ns = 2 if surfel else 3
+    want = torch.cat([rows[:, 0:3].reshape(-1), rows[:, 3], rows[:, 4:4 + ns].reshape(-1), rows[:, 4 + ns:8 + ns].reshape(-1)])
+    assert torch.equal(head_a, want)
+    assert lib.gsr_peer_reduce_shard(None, 0, P, 0, 1, st) != 0       # a NULL multicast address is rejected
+    assert lib.gsr_peer_consume(rows.data_ptr(), head_a.data_ptr(), P, P - 5, 10, int(surfel), st) != 0      # range beyond P
