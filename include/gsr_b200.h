@@ -241,6 +241,12 @@ int gsr_backward_early_rgb(float* drgb, void (*ready)(void* user), void* user);
  * n_dst <= 0 disarms. */
 int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const* campos_dst, const float* campos_src,
                                  void* side_stream, void (*ready)(void* user), void* user);
+/* Multicast variant of gsr_backward_early_rgb_peers: mc_drgb_slot / mc_campos_slot are the MULTICAST (NVLS) addresses of
+ * this rank's slot ([P*3] floats, [3] floats) in a symmetric gather buffer; the push kernel issues one multimem.st per 16
+ * bytes and the NVSwitch replicates it into every rank's buffer, so the SMs and the outbound link carry the colour
+ * gradient once instead of once per rank. NULL disarms. */
+int gsr_backward_early_rgb_multicast(float* mc_drgb_slot, float* mc_campos_slot, const float* campos_src,
+                                     void* side_stream, void (*ready)(void* user), void* user);
 /* Sum of the four non-SH parameter gradients over ranks, done in the NVSwitch (NVLS) in two phases so that the bytes a GPU
  * moves do not grow with the number of ranks. `head` is a symmetric buffer (same offset on every rank, with a multicast
  * mapping) of P rows of 12 floats (means3D xyz, opacity | scales, rotations, padding), 16-byte aligned.

@@ -110,6 +110,7 @@ SIGNATURES = {
     "gsr_clamped_color_grad": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "gsr_backward_early_rgb": (c_int, [_P, _P, _P]),
     "gsr_backward_early_rgb_peers": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), _P, _P, _P, _P]),
+    "gsr_backward_early_rgb_multicast": (c_int, [_P, _P, _P, _P, _P, _P]),
     "gsr_backward_peer_head": (c_int, [_P, c_int, _P, _P]),
     "gsr_peer_consume": (c_int, [_P, _P, c_int, c_int, c_int, c_int, _P]),
     "gsr_peer_reduce_shard": (c_int, [_P, c_int, c_int, c_int, c_int, _P]),

@@ -314,7 +314,7 @@ static int backward_impl(
     prof_mark(5, st);
     {   // multi-GPU: the colour gradient is final here; hand it out so its all-gather overlaps the next kernel
         if (e.armed && shs) {
-            if (e.peers.n > 0) {
+            if (e.peers.n > 0 || e.peers.mc_drgb) {
                 if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.peers, st),
                                      "peer colour gradient push"))) return rc;
             } else if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, ACC_STRIDE, ACC_R, e.drgb, st),
@@ -378,6 +378,20 @@ int gsr_backward_early_rgb_peers(int n_dst, float* const* drgb_dst, float* const
         if (!drgb_dst[k] || !campos_dst[k]) { set_error("gsr_backward_early_rgb_peers: null destination %d", k); return GSR_EINVAL; }
         e.peers.drgb[k] = drgb_dst[k]; e.peers.campos[k] = campos_dst[k];
     }
+    gsr::g_early = e;
+    return GSR_OK;
+}
+
+int gsr_backward_early_rgb_multicast(float* mc_drgb_slot, float* mc_campos_slot, const float* campos_src,
+                                     void* side_stream, void (*ready)(void*), void* user) {
+    if (!mc_drgb_slot) { gsr::g_early = gsr::EarlyRgb{nullptr, nullptr, nullptr, false, {}}; return GSR_OK; }
+    if (!mc_campos_slot || !campos_src || !side_stream || ((uintptr_t)mc_drgb_slot & 3) || ((uintptr_t)mc_campos_slot & 3)) {
+        set_error("gsr_backward_early_rgb_multicast: bad argument (4-byte aligned multicast slots and a side stream are required)");
+        return GSR_EINVAL;
+    }
+    gsr::EarlyRgb e{nullptr, ready, user, true, {}};
+    e.peers.n = 0; e.peers.campos_src = campos_src; e.peers.side = (cudaStream_t)side_stream;
+    e.peers.mc_drgb = mc_drgb_slot; e.peers.mc_campos = mc_campos_slot;
     gsr::g_early = e;
     return GSR_OK;
 }

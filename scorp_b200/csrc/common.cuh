@@ -105,6 +105,10 @@ struct PeerDst {                    // gsr_backward_early_rgb_peers: one destina
     float* campos[PEER_MAX] = {};
     const float* campos_src = nullptr;
     cudaStream_t side = nullptr;    // the push kernel runs here, ordered after the blend backward by an event
+    // gsr_backward_early_rgb_multicast: ONE multicast (NVLS) address of this rank's slot instead of n peer pointers; the
+    // switch replicates every store into all replicas (n = 0 then)
+    float* mc_drgb = nullptr;
+    float* mc_campos = nullptr;
 };
 struct EarlyRgb { float* drgb; void (*ready)(void*); void* user; bool armed; PeerDst peers; };
 EarlyRgb take_early_rgb();          // returns the armed request (armed == false if none) and disarms it
@@ -230,6 +234,9 @@ __device__ __forceinline__ float4 mc_ld_reduce4(const float4* mc) {
     asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
     return v;
+}
+__device__ __forceinline__ void mc_st1(float* mc, float v) {
+    asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" :: "l"(mc), "f"(v) : "memory");
 }
 __device__ __forceinline__ void mc_st4(float4* mc, float4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};"

@@ -60,6 +60,31 @@ clamped_rgb_push_kernel(int P, const int32_t* __restrict__ radii, const uint8_t*
 #pragma unroll 4
     for (int k = 0; k < d.n; ++k) d.drgb[k][i] = v;
 }
+// Multicast variant: one multimem.st per 16 bytes, replicated into every rank's gather buffer by the switch -- the SMs
+// issue 1/n of the stores and the link carries the 12 B x P once outbound instead of n times. The slot starts at an
+// arbitrary float offset of the symmetric buffer (rank * 3P), so the floats before the first and after the last
+// 16-byte-aligned group go out as scalar multimem.st.
+__global__ void __launch_bounds__(256)
+clamped_rgb_push_mc_kernel(int P, const int32_t* __restrict__ radii, const uint8_t* __restrict__ clamped,
+                           const float* __restrict__ acc, int stride, int rgb_off, float* __restrict__ mc_drgb,
+                           float* __restrict__ mc_campos, const float* __restrict__ campos_src) {
+    if (blockIdx.x == 0 && threadIdx.x < 3) mc_st1(mc_campos + threadIdx.x, campos_src[threadIdx.x]);
+    const int n = 3 * P;
+    auto value = [&](int i) {
+        const int g = i / 3, c = i - 3 * g;
+        return (radii[g] > 0 && !((clamped[g] >> c) & 1)) ? acc[(size_t)g * stride + rgb_off + c] : 0.0f;
+    };
+    const int lead = (int)((16 - ((uintptr_t)mc_drgb & 15)) & 15) / 4;     // floats before the first aligned group (0..3)
+    const int q = blockIdx.x * 256 + threadIdx.x;                          // aligned group index
+    const int i0 = lead + 4 * q;
+    if (q == 0) for (int i = 0; i < lead && i < n; ++i) mc_st1(mc_drgb + i, value(i));
+    if (i0 + 3 < n) {
+        mc_st4(reinterpret_cast<float4*>(mc_drgb + i0), make_float4(value(i0), value(i0 + 1), value(i0 + 2), value(i0 + 3)));
+    } else {
+        for (int i = i0; i < n; ++i) mc_st1(mc_drgb + i, value(i));        // the last, partial group
+    }
+}
+
 cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                     int rgb_off, const PeerDst& dst, cudaStream_t main) {
     static thread_local cudaEvent_t ev = nullptr;
@@ -67,7 +92,13 @@ cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* 
     if (!ev && (e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
     if ((e = cudaEventRecord(ev, main)) != cudaSuccess) return e;
     if ((e = cudaStreamWaitEvent(dst.side, ev, 0)) != cudaSuccess) return e;
-    if (P > 0) clamped_rgb_push_kernel<<<(3 * P + 255) / 256, 256, 0, dst.side>>>(P, radii, clamped, acc, stride, rgb_off, dst);
+    if (P > 0 && dst.mc_drgb) {
+        const int groups = (3 * P + 3) / 4 + 1;
+        clamped_rgb_push_mc_kernel<<<(groups + 255) / 256, 256, 0, dst.side>>>(P, radii, clamped, acc, stride, rgb_off, dst.mc_drgb,
+                                                                               dst.mc_campos, dst.campos_src);
+    } else if (P > 0) {
+        clamped_rgb_push_kernel<<<(3 * P + 255) / 256, 256, 0, dst.side>>>(P, radii, clamped, acc, stride, rgb_off, dst);
+    }
     return cudaGetLastError();
 }
 

@@ -205,7 +205,7 @@ static int surfel_backward_impl(
     prof_mark(5, st);
     {   // multi-GPU: see gsr_rasterize_backward
         if (e.armed && shs) {
-            if (e.peers.n > 0) {
+            if (e.peers.n > 0 || e.peers.mc_drgb) {
                 if ((rc = check_cuda(launch_clamped_rgb_push(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.peers, st),
                                      "peer colour gradient push"))) return rc;
             } else if ((rc = check_cuda(launch_clamped_rgb_from_acc(P, radii, g.clamped, acc, SACC_STRIDE, SACC_R, e.drgb, st),

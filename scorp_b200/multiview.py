@@ -199,8 +199,9 @@ class PeerExchange(FactoredExchange):
 
     # row ranges the preprocess-backward kernel is split into for the pipelined head reduce (GSR_PEER_CHUNKS overrides).
     # Measured at C2 on 2 GPUs (profiles/r02_mg2_chunks.md): 1 range 1.750 ms/step, 2 ranges 1.743, 4 ranges 1.792 -- what
-    # the pipelining takes off the tail comes back as a slower preprocess-backward stage, so the default is one range.
-    CHUNKS = int(os.environ.get("GSR_PEER_CHUNKS", "1"))
+    # the pipelining takes off the tail mostly comes back as a slower preprocess-backward stage; at 8 GPUs 1 range 1.925,
+    # 2 ranges 1.853 (profiles/r02_mg8_chunks.md). Default: 2.
+    CHUNKS = int(os.environ.get("GSR_PEER_CHUNKS", "2"))
 
     def stage_ms(self):
         """Mean CUDA-event durations over the steps recorded while `profile` was set (this rank): `exposed_tail` is what
@@ -241,7 +242,7 @@ class PeerExchange(FactoredExchange):
         mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
         if os.environ.get("GSR_PEER_NO_MULTICAST"):
             mc = 0
-        views, dst, heads = [], [], []
+        views, dst, heads, mc_slots = [], [], [], []
         for b in range(2):
             base = b * half
             views.append((t[base: base + world * P * 3].view(world, P, 3),
@@ -251,9 +252,11 @@ class PeerExchange(FactoredExchange):
             dst.append((drgb_dst, cam_dst))
             h0 = base + n_rgb + n_cam                   # multiple of 4 floats: rows are 16-byte aligned
             heads.append((t[h0: h0 + P * 12], (mc + 4 * h0) if mc else 0))
+            mc_slots.append(((mc + 4 * (base + rank * P * 3)), (mc + 4 * (base + n_rgb + rank * 3))) if mc else None)
         t.zero_()
         torch.cuda.synchronize(dev)
         dist.barrier(group=grp)
+        self._mc_slots = mc_slots
         self._symm = {key: (t, hdl, views, dst, heads)}
         self._side = torch.cuda.Stream(dev)
         # high priority: the reduce kernels and barriers of range k get SM slots as soon as blocks of the
@@ -315,8 +318,14 @@ class PeerExchange(FactoredExchange):
                 errors.append(ex)
 
         cb = _lib.READY_FN(_ready)
-        _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
-                                                    C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
+        if use_mc and not os.environ.get("GSR_PEER_PUSH_P2P"):
+            # the switch replicates the colour gradient into every rank's gather buffer (one multimem.st per 16 bytes)
+            mc_drgb, mc_cam = self._mc_slots[self._parity]
+            _lib.check(lib.gsr_backward_early_rgb_multicast(C.c_void_p(mc_drgb), C.c_void_p(mc_cam), campos.data_ptr(),
+                                                            C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_multicast")
+        else:
+            _lib.check(lib.gsr_backward_early_rgb_peers(world, drgb_dst, cam_dst, campos.data_ptr(),
+                                                        C.c_void_p(side.cuda_stream), cb, None), "gsr_backward_early_rgb_peers")
         self._armed_mc = use_mc
         keep = [cb, campos, drgb_dst, cam_dst]
         if use_mc:      # the four non-SH gradients go to the local replica of the symmetric head (phase 0 of the switch reduce)

@@ -14,6 +14,9 @@ import helpers as h  # noqa: E402
 from scorp_b200 import multiview as mv, synth  # noqa: E402
 
 
+DEFAULT_CHUNKS = mv.PeerExchange.CHUNKS
+
+
 def main():
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
@@ -42,7 +45,7 @@ def main():
             spread = float((st.max(0).values - st.min(0).values).max())
             tol[k] = 1e-6 * float(ref[k].abs().max()) + 2.0 * spread + 1e-4 * ref[k].abs()      # north_star: rtol 1e-4
         for mode in ("factored", "peer", "peer3"):       # peer3: the head reduce pipelined over 3 row ranges
-            mv.PeerExchange.CHUNKS = 3 if mode == "peer3" else 1
+            mv.PeerExchange.CHUNKS = 3 if mode == "peer3" else DEFAULT_CHUNKS
             mv.install_factored_exchange(enable=True, peer=mode.startswith("peer"))
             try:
                 for step in range(3):       # three steps: both parities of the double buffer, and reuse
@@ -62,7 +65,7 @@ def main():
                         ok = False
             finally:
                 mv.install_factored_exchange(enable=False)
-                mv.PeerExchange.CHUNKS = 1
+                mv.PeerExchange.CHUNKS = DEFAULT_CHUNKS
         # precomputed colours (M == 0) under an installed factored exchange: still summed over ranks (one all_reduce)
         gcol = torch.Generator().manual_seed(11)
         colors = torch.rand(sc.P, 3, generator=gcol).cuda()
