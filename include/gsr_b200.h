@@ -214,6 +214,17 @@ void gsr_surfel_image_layout(int W, int H, size_t off[4], size_t* total);
  * gsr_knn_workspace_bytes(P) bytes. */
 size_t gsr_knn_workspace_bytes(int P);
 int gsr_knn_dist2(int P, const float* xyz, float* out, void* tmp, size_t tmp_bytes, void* stream);
+/* Allocation-free variant of gsr_knn_dist2. NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).
+ * Same result as gsr_knn_dist2, bit for bit, with the scratch in a static __device__ array inside the library instead of
+ * `tmp`: the caller passes only xyz[P*3] and out[P]; the call performs no cudaMalloc / cudaFree and calls no allocating
+ * library routine. Limit: P <= GSR_KNN_STATIC_MAX_POINTS (gsr_knn_static_max_points()); a larger P is rejected with
+ * GSR_EINVAL and a message naming the limit. The array (about 6.3 MB) is held by every GPU that loads the library until
+ * the process exits. All calls on a device share it: the call re-initialises what must start clean, so results do not
+ * depend on the previous call, but calls that OVERLAP on the GPU (two streams, two host threads) race -- serialise them. */
+#define GSR_KNN_STATIC_MAX_POINTS 262144
+int gsr_knn_static_max_points(void);
+int gsr_knn_dist2_static(int P, const float* xyz, float* out, void* stream);
 
 /* ---- view-sharded multi-GPU helpers (no reference counterpart; the reference is single-GPU) ----
  * The SH gradient of ONE view is an outer product, dL_dsh[k] = b_k(dir) * dL_dRGB with dir = normalize(mean - campos)

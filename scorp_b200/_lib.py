@@ -107,6 +107,8 @@ SIGNATURES = {
     "gsr_surfel_image_layout": (None, [c_int, c_int, C.POINTER(c_size_t), C.POINTER(c_size_t)]),
     "gsr_knn_workspace_bytes": (c_size_t, [c_int]),
     "gsr_knn_dist2": (c_int, [c_int, _P, _P, _P, c_size_t, _P]),
+    "gsr_knn_static_max_points": (c_int, []),
+    "gsr_knn_dist2_static": (c_int, [c_int, _P, _P, _P]),
     "gsr_clamped_color_grad": (c_int, [c_int, c_int, c_int, c_int, _P, _P, _P, _P]),
     "gsr_backward_early_rgb": (c_int, [_P, _P, _P]),
     "gsr_backward_early_rgb_peers": (c_int, [c_int, C.POINTER(c_void_p), C.POINTER(c_void_p), _P, _P, _P, _P]),

@@ -212,3 +212,63 @@ cudaError_t launch_knn(int P, const float* xyz, float* out, void* tmp, size_t, c
 }
 
 }  // namespace gsr
+
+// ---- gsr_knn_dist2_static: the same computation with NO caller scratch and NO allocation ---------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA-graph capture regions, tight serving loops, harnesses that forbid it). The workspace launch_knn needs lives in a
+// file-scope __device__ array sized for GSR_KNN_STATIC_MAX_POINTS points (about 6.3 MB, held by every GPU that loads the
+// library until the process exits). In host code `g_knn_static_scratch` is only a host-side stand-in for the symbol, not
+// a device address: the address a kernel may use comes from cudaGetSymbolAddress, queried once per device with that
+// device current, below. Every call shares the array; launch_knn re-initialises the parts that must start clean (the
+// bounding box and the per-cell counters are memset, every other sub-array is written before it is read), so the
+// previous call's contents do not matter -- but two calls that overlap on the GPU (different streams, or different host
+// threads) race on it.
+#include <mutex>
+
+namespace {
+
+constexpr int KNN_STATIC_MAX_P = GSR_KNN_STATIC_MAX_POINTS;
+constexpr size_t cexpr_align(size_t v) { return (v + 255) / 256 * 256; }
+constexpr size_t cexpr_cells(size_t P) { return P / 2 + 1024; }
+// == knn_workspace_bytes(KNN_STATIC_MAX_P), restated as a constant expression (checked at run time below)
+constexpr size_t KNN_STATIC_BYTES = 256 + cexpr_align((size_t)KNN_STATIC_MAX_P * 4) + cexpr_align((size_t)KNN_STATIC_MAX_P * 16) +
+                                    cexpr_align(cexpr_cells(KNN_STATIC_MAX_P) * 4) + cexpr_align((cexpr_cells(KNN_STATIC_MAX_P) + 1) * 4);
+
+static __device__ __align__(256) unsigned char g_knn_static_scratch[KNN_STATIC_BYTES];
+
+constexpr int MAX_DEVICES = 64;
+std::mutex g_knn_static_mu;
+void* g_knn_static_ptr[MAX_DEVICES] = {};
+
+// device address of the scratch array on the CURRENT device (cached per device); nullptr + error text on failure
+void* knn_static_scratch_ptr() {
+    int dev = -1;
+    if (gsr::check_cuda(cudaGetDevice(&dev), "cudaGetDevice")) return nullptr;
+    if (dev < 0 || dev >= MAX_DEVICES) { gsr::set_error("gsr_knn_dist2_static: device ordinal %d not supported", dev); return nullptr; }
+    std::lock_guard<std::mutex> lock(g_knn_static_mu);
+    if (!g_knn_static_ptr[dev]) {
+        void* p = nullptr;
+        if (gsr::check_cuda(cudaGetSymbolAddress(&p, g_knn_static_scratch), "cudaGetSymbolAddress(knn scratch)")) return nullptr;
+        g_knn_static_ptr[dev] = p;
+    }
+    return g_knn_static_ptr[dev];
+}
+
+}  // namespace
+
+extern "C" int gsr_knn_static_max_points(void) { return KNN_STATIC_MAX_P; }
+
+extern "C" int gsr_knn_dist2_static(int P, const float* xyz, float* out, void* stream) {
+    if (P == 0) return GSR_OK;
+    if (P < 0 || !xyz || !out) { gsr::set_error("bad argument to gsr_knn_dist2_static"); return GSR_EINVAL; }
+    if (P > KNN_STATIC_MAX_P) {
+        gsr::set_error("gsr_knn_dist2_static: %d points exceed the built-in scratch (at most %d); use gsr_knn_dist2 with caller scratch",
+                       P, KNN_STATIC_MAX_P);
+        return GSR_EINVAL;
+    }
+    if (gsr::knn_workspace_bytes(P) > KNN_STATIC_BYTES) { gsr::set_error("gsr_knn_dist2_static: scratch size mismatch"); return GSR_EINVAL; }
+    void* tmp = knn_static_scratch_ptr();
+    if (!tmp) return GSR_ECUDA;
+    return gsr::check_cuda(gsr::launch_knn(P, xyz, out, tmp, KNN_STATIC_BYTES, (cudaStream_t)stream), "knn launch (static scratch)");
+}
+
