@@ -582,7 +582,11 @@ def run(arm, args, rank, world, local):
     if batched:
         h_all = torch.stack(h_cams).pin_memory()
 
-    def step_e2e():
+    from scorp_b200 import capacity
+
+    def enqueue_e2e():
+        """everything of one end-to-end step that is enqueued: H2D of the step's inputs, forward, backward, the scalar and
+        its D2H copy; returns without waiting (so it can also be captured in a CUDA graph)"""
         main = torch.cuda.current_stream(dev)
         acc = None
         if batched:     # one H2D of the V cameras, one forward_views call, one scalar back
@@ -594,7 +598,6 @@ def run(arm, args, rank, world, local):
                 d[:, 0:16].reshape(-1, 4, 4), d[:, 16:32].reshape(-1, 4, 4), d[:, 32:35], params[0], params[2],
                 shs=params[1], scales=params[3], rotations=params[4])
             h_out.copy_(color.sum().view(1), non_blocking=True)
-            torch.cuda.current_stream().synchronize()
             return
         for cam, h_cam, h_gr in zip(cams, h_cams, h_grads):
             d_cam = h_cam.to(dev, non_blocking=True)
@@ -612,10 +615,60 @@ def run(arm, args, rank, world, local):
             s = color.detach().sum().view(1)      # the scalar that goes to the host (loss.item()); no graph hangs off it
             acc = s if acc is None else acc + s
         h_out.copy_(acc, non_blocking=True)
+
+    redone = [0]
+
+    def step_e2e():
+        enqueue_e2e()
         torch.cuda.current_stream().synchronize()     # the step's result is on the host (loss.item() in train_3dgs.py)
+        # no-sync mode (scorp_b200.capacity): the instance-capacity check sits at the step's own synchronisation point;
+        # a step that overflowed is repeated with the raised capacity, inside the timed region
+        while capacity.enabled() and capacity.overflowed(synchronize=False):
+            redone[0] += 1
+            enqueue_e2e()
+            torch.cuda.current_stream().synchronize()
 
     prime(step_e2e, world)                 # setup, not warm-up: caching-allocator growth for the autograd path
     ms_e2e_total, _, per_e2e = time_steps(step_e2e, args.steps, args.warmup, world)
+    e2e_modes = {"stock": {"ms_per_step": ms_e2e_total / args.steps, "spread": per_e2e,
+                           "what": "drop-in API as the reference uses it: one host synchronisation inside every forward (num_rendered)"}}
+    if arm.name == "ours" and not batched:
+        # (1) scorp_b200.capacity.enable(): the forward no longer waits for num_rendered; the check moves to the step's sync
+        capacity.reset(); capacity.enable()
+        try:
+            prime(step_e2e, world)
+            t_ns, _, per_ns = time_steps(step_e2e, args.steps, args.warmup, world)
+            e2e_modes["nosync"] = {"ms_per_step": t_ns / args.steps, "spread": per_ns, "steps_repeated_for_capacity": redone[0],
+                                   "what": "same calls after scorp_b200.capacity.enable(): no host round trip in the forward, capacity checked at the step's own synchronisation"}
+            # (2) the whole step (H2D copies, forward, backward, scalar D2H) captured in ONE CUDA graph and replayed
+            if world == 1 and len(cams) == 1:
+                try:
+                    for p_ in params:
+                        p_.grad = None
+                    graph = torch.cuda.CUDAGraph()
+                    capacity.forget_captured()
+                    with torch.cuda.graph(graph):
+                        enqueue_e2e()
+
+                    def step_graph():
+                        graph.replay()
+                        torch.cuda.current_stream().synchronize()
+                        if capacity.overflowed(synchronize=False):
+                            raise RuntimeError("captured step exceeded its instance capacity (re-capture needed)")
+                    prime(step_graph, world)
+                    ref_val = float(h_out)
+                    t_g, _, per_g = time_steps(step_graph, args.steps, args.warmup, world)
+                    step_e2e()
+                    e2e_modes["graph"] = {"ms_per_step": t_g / args.steps, "spread": per_g,
+                                          "result_equals_eager": bool(abs(float(h_out) - ref_val) <= 1e-5 * abs(ref_val) + 1e-12),
+                                          "what": "the same step captured once with torch.cuda.graph (possible because nothing in it synchronises) and replayed"}
+                    del graph
+                except Exception as ex:
+                    e2e_modes["graph"] = {"error": repr(ex)[:300]}
+        finally:
+            capacity.disable(); capacity.reset(); capacity.forget_captured()
+    best = min((m for m in e2e_modes if "ms_per_step" in e2e_modes[m]), key=lambda m: e2e_modes[m]["ms_per_step"])
+    ms_e2e_total, per_e2e = e2e_modes[best]["ms_per_step"] * args.steps, e2e_modes[best]["spread"]
     exch, xcheck = None, None
     if world > 1 and not fwd_only:
         exch = time_exchange(arm, P, M, surfel, world, dev)
@@ -652,7 +705,7 @@ def run(arm, args, rank, world, local):
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
                 d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched,
-                inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck)
+                inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck, e2e_modes=e2e_modes, e2e_mode=best)
 
 
 def main():
@@ -699,7 +752,7 @@ def main():
                    "l2": "per-step inputs (236 B x P parameters + 24 B x N lists) exceed the 126 MB L2; no explicit flush"
                          if r["P"] * (44 + 12 * r["M"]) > 126e6 else "working set below the 126 MB L2: numbers are L2-warm, as in the reference's own loop"},
         "e2e": {"value": e2e_v, "unit": UNIT, "ms_per_step": r["ms_e2e"], "ms_per_step_spread": r["per_e2e"], "h2d_bytes_per_step": r["h2d"],
-                "d2h_bytes_per_step": r["d2h"],
+                "d2h_bytes_per_step": r["d2h"], "mode": r["e2e_mode"], "modes": r["e2e_modes"],
                 "note": "public API + autograd; per view the camera and the upstream-gradient maps are copied from pinned host memory (the gradient maps on a copy stream under the forward), scalar result read back; Gaussian parameters are model state resident in HBM as in train_3dgs.py"},
         "gpu_launches": r["launches"], "clocks": r["clocks"],
         # the contract's value/ms_per_step are MEANS over the K steps; the medians say what a typical step costs, and

@@ -209,6 +209,30 @@ int gsr_surfel_backward(
 void gsr_surfel_geom_layout(int P, int tiles, size_t off[6], size_t* total);
 void gsr_surfel_image_layout(int W, int H, size_t off[4], size_t* total);
 
+/* ---- forward without the host round trip ------------------------------------------------------------------------
+ * The reference reads the number of (Gaussian, tile) instances back to the host in the middle of every forward because it
+ * sizes the binning buffer from it (cuda_rasterizer/rasterizer_impl.cu:278-286: cudaMemcpy of the scan's last element);
+ * gsr_rasterize_forward / gsr_surfel_forward keep that behaviour. These variants take the size from the CALLER instead:
+ * `capacity` = how many instances the binning buffer may hold (e.g. the largest count seen so far plus a margin). Nothing
+ * in the call synchronises, so the host runs ahead of the GPU and the call can be captured in a CUDA graph.
+ * status_pinned: page-locked host uint32[4]; {num_rendered, longest tile list, overflow flag, -} arrive there behind the
+ * kernels and are valid after the caller's next synchronisation of `stream`. If num_rendered > capacity the overflow flag
+ * is 1, NOTHING was binned or blended (the outputs hold the background) and the call must be repeated with a larger
+ * capacity -- the caller checks the flag at the point where it synchronises anyway (loss.item() in train_3dgs.py:158).
+ * The binning buffer is requested with the size for `capacity`; pass R = capacity to the backward call. */
+int gsr_rasterize_forward_nosync(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int capacity, uint32_t* status_pinned, void* stream);
+int gsr_surfel_forward_nosync(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* transMat_precomp,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int capacity, uint32_t* status_pinned, void* stream);
+
 /* ---- simple_knn.distCUDA2 ---------------------------------------------------------------
  * out[P] = mean squared distance to the 3 nearest other points. tmp: device scratch of
  * gsr_knn_workspace_bytes(P) bytes. */

@@ -68,6 +68,10 @@ SIGNATURES = {
     "gsr_profile_read": (c_int, [C.POINTER(c_float)]),
     "gsr_rasterize_forward": (c_int, [C.POINTER(GsrSettings), c_int, c_int] + [_P] * 7 + [_P] * 4
                               + [ALLOC_FN, _P, C.POINTER(c_int), _P]),
+    "gsr_rasterize_forward_nosync": (c_int, [C.POINTER(GsrSettings), c_int, c_int] + [_P] * 7 + [_P] * 4
+                                     + [ALLOC_FN, _P, c_int, _P, _P]),
+    "gsr_surfel_forward_nosync": (c_int, [C.POINTER(GsrSettings), c_int, c_int] + [_P] * 7 + [_P] * 3
+                                  + [ALLOC_FN, _P, c_int, _P, _P]),
     "gsr_backward_workspace_bytes": (c_size_t, [c_int]),
     "gsr_rasterize_backward": (c_int, [C.POINTER(GsrSettings), c_int, c_int, c_int] + [_P] * 6 + [_P]
                                + [_P] * 3 + [_P] + [_P] * 3 + [_P] * 8 + [_P, c_size_t, _P]),

@@ -105,10 +105,11 @@ static int forward_impl(
     const float* means3D, const float* shs, const float* shs_rest, bool raw, const float* colors_precomp,
     const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
     float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
-    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, int views = 1)
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, int views = 1, const NoSync* nosync = nullptr)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
+    if (nosync && (nosync->capacity < 1 || !nosync->status)) { set_error("no-sync forward needs capacity >= 1 and a pinned status slot"); return GSR_EINVAL; }
     if (views < 1 || (long long)views * P > 0x7fffffffLL) { set_error("bad view count %d for P=%d", views, P); return GSR_EINVAL; }
     *num_rendered = 0;
     const int W = s->image_width, H = s->image_height;
@@ -142,7 +143,7 @@ static int forward_impl(
     carve_image(ibase, W, H, &img, nullptr, views);
 
     // tile_count and counters are adjacent at the end of the geometry buffer: one memset
-    const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + 16;
+    const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + GEOM_COUNTERS * 4;
     if ((rc = check_cuda(cudaMemsetAsync(g.tile_count, 0, zero_bytes, st), "memset tile counters"))) return rc;
 
     prof_mark(0, st);
@@ -163,19 +164,29 @@ static int forward_impl(
     // number of instances -> host (the one blocking point, as rasterizer_impl.cu:282)
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
-    if ((rc = check_cuda(launch_tile_scan(tiles, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
-    uint32_t n_stack[2] = {0, 0};
-    uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
-    if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
-    if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
-    const int N = (int)n_host[0], max_len = (int)n_host[1];
+    if ((rc = check_cuda(launch_tile_scan(tiles, g.tile_count, img.ranges, g.counters, img.tile_order, st,
+                                          nosync ? (uint32_t)nosync->capacity : 0xffffffffu), "tile scan launch"))) return rc;
+    int N, max_len = 0;
+    if (nosync) {
+        // no host round trip (rasterizer_impl.cu:282 has one): the caller sized the binning buffer; N, the longest segment
+        // and the overflow flag travel to its pinned slot behind the kernels and are read after ITS next synchronisation
+        if ((rc = check_cuda(cudaMemcpyAsync(nosync->status, g.counters, 12, cudaMemcpyDeviceToHost, st), "copy status"))) return rc;
+        N = nosync->capacity;
+    } else {
+        uint32_t n_stack[2] = {0, 0};
+        uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
+        if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
+        if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
+        N = (int)n_host[0]; max_len = (int)n_host[1];
+    }
     *num_rendered = N;
 
     char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, tiles));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
     carve_binning(bbase, N, &bin, nullptr, tiles);
 
-    if ((rc = check_cuda(launch_binning(PV, gx, gy, N, max_len, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st, views), "binning launch"))) return rc;
+    if ((rc = check_cuda(launch_binning(PV, gx, gy, N, max_len, g.rec, (int)sizeof(GaussRec), 24, g.tile_count, radii, img.ranges, bin, st, views,
+                                        nosync ? g.counters : nullptr, img.tile_order), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
     if ((rc = check_cuda(cudaMemsetAsync(bin.contrib, 0, contrib_slots(N, tiles) * sizeof(uint4), st), "memset contribution masks"))) return rc;
@@ -194,6 +205,19 @@ int gsr_rasterize_forward(
 {
     return forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations, cov3D_precomp,
                         out_color, out_depth, out_alpha, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+int gsr_rasterize_forward_nosync(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* cov3D_precomp,
+    float* out_color, float* out_depth, float* out_alpha, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int capacity, uint32_t* status_pinned, void* stream)
+{
+    const NoSync ns{capacity, status_pinned};
+    int n = 0;
+    return forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations, cov3D_precomp,
+                        out_color, out_depth, out_alpha, radii, alloc, alloc_user, &n, stream, 1, &ns);
 }
 
 int gsr_rasterize_forward_raw(

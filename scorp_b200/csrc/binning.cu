@@ -18,13 +18,19 @@ namespace gsr {
 
 // ---- 2. exclusive scan over tiles (single CTA, tiles <= a few 10^4) ------------------------
 constexpr int ORDER_BINS = 1024;      // == threads of the scan CTA
+constexpr int SORT_S_CAP_ = 1024;     // == SORT_S_CAP below (segments up to this length go to the small sort kernel)
 __device__ __forceinline__ int order_bin(uint32_t len) { return (int)min(len >> 3, (uint32_t)(ORDER_BINS - 1)); }
+// counters (GeomState::counters): [0] N (summed by the preprocess kernel), [1] longest segment, and for the no-sync
+// forward (gsr_rasterize_forward_nosync) [2] overflow flag (N > capacity: every range is (0,0), nothing is binned or
+// blended), [3] / [4] how many entries at the head of `order` can need the mid / long sort kernel.
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ max_len,
-                 uint32_t* __restrict__ order) {
+tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ counters,
+                 uint32_t* __restrict__ order, uint32_t capacity) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
     __shared__ uint32_t bins[ORDER_BINS];
+    uint32_t* const max_len = counters + 1;
+    const bool overflow = counters[0] > capacity;
     bins[threadIdx.x] = 0;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry_s = 0;
@@ -49,7 +55,7 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         __syncthreads();
         const uint32_t carry = carry_s;
         const uint32_t incl = carry + v + (wid ? warp_sums[wid - 1] : 0u);
-        if (t < tiles) ranges[t] = c ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
+        if (t < tiles) ranges[t] = (c && !overflow) ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
         __syncthreads();
         if (threadIdx.x == 1023) carry_s = incl;
         __syncthreads();
@@ -76,6 +82,14 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         __syncthreads();
         bins[ORDER_BINS - 1 - threadIdx.x] = v - c + (wid ? warp_sums[wid - 1] : 0u);   // first slot of the class
         __syncthreads();
+        if (threadIdx.x == 0) {
+            // classes are 8 lengths wide: every segment of >= 1024 entries sits before the first slot of class 127,
+            // every segment of >= 8184 in class 1023, which ends where class 1022 starts
+            counters[2] = overflow ? 1u : 0u;
+            counters[3] = overflow ? 0u : bins[(SORT_S_CAP_ >> 3) - 1];
+            counters[4] = overflow ? 0u : bins[ORDER_BINS - 2];
+        }
+        __syncthreads();
         for (int t = threadIdx.x; t < tiles; t += 1024) order[atomicAdd(&bins[order_bin(count[t])], 1u)] = (uint32_t)t;
     }
 }
@@ -90,7 +104,9 @@ constexpr uint32_t SMALL_RECT = 4;
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
                const int32_t* __restrict__ radii,
-               uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys) {
+               uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
+               const uint32_t* __restrict__ overflow) {
+    if (overflow && *overflow) return;        // no-sync forward whose instances exceed the caller's capacity: nothing is binned
     const int idx = blockIdx.x * 256 + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, w = 0, cnt = 0;
@@ -220,12 +236,11 @@ __device__ __forceinline__ void sort_pass(uint64_t* s, int L, int n, int k, int 
 }
 
 // Segments with lo_len < L <= CAP. Dynamic shared memory: sphys(CAP) keys.
+// (every return below is taken by the whole CTA: L is CTA-uniform)
 template <int THREADS, int CAP>
-__global__ void __launch_bounds__(THREADS)
-tile_sort_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
-                 uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
-    extern __shared__ uint64_t s[];
-    const int tile = blockIdx.x;
+__device__ __forceinline__ void tile_sort_one(uint64_t* s, int tile, int lo_len, const uint2* __restrict__ ranges,
+                                              const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                                              uint64_t* __restrict__ point_list_keys) {
     const uint2 rg = ranges[tile];
     const int L = (int)(rg.y - rg.x);
     if (L <= lo_len || L > CAP) return;
@@ -264,6 +279,27 @@ tile_sort_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* _
         }
     }
 }
+template <int THREADS, int CAP>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                 uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    extern __shared__ uint64_t s[];
+    tile_sort_one<THREADS, CAP>(s, blockIdx.x, lo_len, ranges, keys, point_list, point_list_keys);
+}
+// No-sync forward: the host does not know the segment lengths, so a fixed grid walks the first *n_work entries of
+// `order` (tiles by decreasing length; tile_scan_kernel counted how many of them can belong to this size class).
+template <int THREADS, int CAP>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const uint32_t* __restrict__ order,
+                        const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                        uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    extern __shared__ uint64_t s[];
+    const uint32_t n = *n_work;
+    for (uint32_t k = blockIdx.x; k < n; k += gridDim.x) {
+        tile_sort_one<THREADS, CAP>(s, (int)order[k], lo_len, ranges, keys, point_list, point_list_keys);
+        __syncthreads();
+    }
+}
 
 // Segments longer than LONG_MIN (rare: > 8192 splats on one tile): chunks sorted in shared memory, merge
 // steps with stride >= LONG_CAP in global (L2-resident) memory, the tail of every merge per chunk in shared memory.
@@ -290,11 +326,9 @@ __device__ __forceinline__ void half_step(uint64_t* a, int L, int n, int j) {
     }
     __syncthreads();
 }
-__global__ void __launch_bounds__(LONG_THREADS)
-tile_sort_long_kernel(int lo_len, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
-                      uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
-    __shared__ uint64_t s[LONG_CAP];
-    const int tile = blockIdx.x;
+__device__ __forceinline__ void tile_sort_long_one(uint64_t* s, int tile, int lo_len, const uint2* __restrict__ ranges,
+                                                   uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                                                   uint64_t* __restrict__ point_list_keys) {
     const uint2 r = ranges[tile];
     const int L = (int)(r.y - r.x);
     if (L <= lo_len) return;
@@ -330,23 +364,63 @@ tile_sort_long_kernel(int lo_len, const uint2* __restrict__ ranges, uint64_t* __
         point_list_keys[r.x + i] = tile_hi | (k >> 32);
     }
 }
+__global__ void __launch_bounds__(LONG_THREADS)
+tile_sort_long_kernel(int lo_len, const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
+                      uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    __shared__ uint64_t s[LONG_CAP];
+    tile_sort_long_one(s, blockIdx.x, lo_len, ranges, keys, point_list, point_list_keys);
+}
+__global__ void __launch_bounds__(LONG_THREADS)
+tile_sort_long_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const uint32_t* __restrict__ order,
+                             const uint2* __restrict__ ranges, uint64_t* __restrict__ keys,
+                             uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    __shared__ uint64_t s[LONG_CAP];
+    const uint32_t n = *n_work;
+    for (uint32_t k = blockIdx.x; k < n; k += gridDim.x) {
+        tile_sort_long_one(s, (int)order[k], lo_len, ranges, keys, point_list, point_list_keys);
+        __syncthreads();
+    }
+}
 
 constexpr int SORT_S_CAP = 1024, SORT_S_THREADS = 128;       // most tiles
 constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // crowded tiles (one CTA of 32 warps each)
 
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, uint32_t* order,
-                             cudaStream_t st) {
-    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, max_len, order);
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
+                             cudaStream_t st, uint32_t capacity) {
+    tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, counters, order, capacity);
     return cudaGetLastError();
 }
 
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
-                           cudaStream_t st, int views) {
+                           cudaStream_t st, int views, const uint32_t* counters, const uint32_t* order) {
     const int tiles = gx * gy * views;
     if (N <= 0) return cudaSuccess;
+    if (counters) {
+        // no-sync forward: N is the caller's capacity, the real counts live on the device (counters, see tile_scan_kernel)
+        scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
+                                                        tile_count, ranges, bin.scratch, counters + 2);
+        tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
+            0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+        static bool attr_set[64] = {};
+        int dev = 0;
+        cudaError_t e = cudaGetDevice(&dev);
+        if (e != cudaSuccess) return e;
+        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+            e = cudaFuncSetAttribute(tile_sort_queued_kernel<SORT_M_THREADS, SORT_M_CAP>,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sphys_host(SORT_M_CAP) * 8));
+            if (e != cudaSuccess) return e;
+            attr_set[dev] = true;
+        }
+        const int grid = tiles < 148 * 2 ? tiles : 148 * 2;      // two CTAs of 1024 threads per SM; exits at once when *n_work == 0
+        tile_sort_queued_kernel<SORT_M_THREADS, SORT_M_CAP><<<grid, SORT_M_THREADS, sphys_host(SORT_M_CAP) * 8, st>>>(
+            SORT_S_CAP, counters + 3, order, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+        tile_sort_long_queued_kernel<<<grid, LONG_THREADS, 0, st>>>(SORT_M_CAP, counters + 4, order, ranges, bin.scratch,
+                                                                    bin.point_list, bin.point_list_keys);
+        return cudaGetLastError();
+    }
     scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
-                                                    tile_count, ranges, bin.scratch);
+                                                    tile_count, ranges, bin.scratch, nullptr);
     tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
         0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
     if (max_len > SORT_S_CAP) {

@@ -17,6 +17,7 @@ namespace gsr {
 constexpr int TILE = 16;            // BLOCK_X == BLOCK_Y == 16 (config.h:16-17)
 constexpr int TILE_PIX = TILE * TILE;
 constexpr int BATCH = 256;          // Gaussians staged per round (== BLOCK_SIZE in the reference)
+constexpr int GEOM_COUNTERS = 8;    // uint32 slots in GeomState::counters / SurfelGeom::counters (binning.cu: tile_scan_kernel)
 
 // Per-Gaussian render record, 48 bytes, 16-byte aligned: what the blend kernels stage.
 struct __align__(16) GaussRec {
@@ -65,7 +66,7 @@ inline size_t carve_geom(char* base, int P, int tiles, GeomState* g, size_t* off
     size_t a2 = take((size_t)P);
     size_t a3 = take((size_t)P * 4);
     size_t a4 = take((size_t)tiles * 4);
-    size_t a5 = take(16);
+    size_t a5 = take(GEOM_COUNTERS * 4);
     if (g) {
         g->rec = (GaussRec*)(base + a0); g->cov3D = (float*)(base + a1);
         g->clamped = (uint8_t*)(base + a2); g->tiles_touched = (uint32_t*)(base + a3);
@@ -142,6 +143,10 @@ inline cudaError_t launch_in_row_chunks(int P, int tile, const PeerHead& ph, Lau
     return cudaSuccess;
 }
 uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the calling host thread (NULL if it cannot be had)
+
+// gsr_*_forward_nosync: the binning buffer is sized by the caller (capacity instances) instead of by a device->host
+// readback of N; status = pinned host uint32[4] that receives {N, longest segment, overflow flag, 0} asynchronously
+struct NoSync { int capacity; uint32_t* status; };
 
 // error plumbing (api.cu)
 void set_error(const char* fmt, ...);
@@ -273,13 +278,15 @@ struct FwdArgs {
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views = 1);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* max_len, uint32_t* order,
-                             cudaStream_t st);
+// counters = GeomState::counters ([0] N in, [1] longest segment out, [2..4] see binning.cu); capacity: instances the
+// binning buffer holds (no-sync forward), beyond it the overflow flag is raised and every range is left empty
+cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
+                             cudaStream_t st, uint32_t capacity = 0xffffffffu);
 // views > 1: P is the TOTAL record count (views * Gaussians), record v*Pv + i belongs to view v and its tiles are
 // numbered v * gx*gy + local tile
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
-                           cudaStream_t st, int views = 1);
+                           cudaStream_t st, int views = 1, const uint32_t* counters = nullptr, const uint32_t* order = nullptr);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st, int views = 1);

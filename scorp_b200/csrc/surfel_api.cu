@@ -21,7 +21,7 @@ static int surfel_forward_impl(
     const float* means3D, const float* shs, const float* shs_rest, bool raw, const float* colors_precomp,
     const float* opacities, const float* scales, const float* rotations, const float* transMat_precomp,
     float* out_color, float* out_others, int32_t* radii,
-    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream)
+    gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, const NoSync* nosync = nullptr)
 {
     cudaStream_t st = (cudaStream_t)stream;
     if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
@@ -51,7 +51,7 @@ static int surfel_forward_impl(
     if (!gbase || !ibase) { set_error("allocator returned NULL"); return GSR_EALLOC; }
     carve_surfel_geom(gbase, P, tiles, &g);
     carve_surfel_image(ibase, W, H, &img);
-    const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + 16;
+    const size_t zero_bytes = (size_t)((char*)g.counters - (char*)g.tile_count) + GEOM_COUNTERS * 4;
     if ((rc = check_cuda(cudaMemsetAsync(g.tile_count, 0, zero_bytes, st), "memset tile counters"))) return rc;
 
     prof_mark(0, st);
@@ -69,19 +69,27 @@ static int surfel_forward_impl(
 
     // the scan over tiles needs nothing from the host, so it runs ahead of the readback and adds the longest
     // tile segment (counters[1]) to it
-    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters + 1, img.tile_order, st), "tile scan launch"))) return rc;
-    uint32_t n_stack[2] = {0, 0};
-    uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
-    if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
-    if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
-    const int N = (int)n_host[0], max_len = (int)n_host[1];
+    if (nosync && (nosync->capacity < 1 || !nosync->status)) { set_error("no-sync forward needs capacity >= 1 and a pinned status slot"); return GSR_EINVAL; }
+    if ((rc = check_cuda(launch_tile_scan(gx * gy, g.tile_count, img.ranges, g.counters, img.tile_order, st,
+                                          nosync ? (uint32_t)nosync->capacity : 0xffffffffu), "tile scan launch"))) return rc;
+    int N, max_len = 0;
+    if (nosync) {       // see gsr_rasterize_forward_nosync (api.cu)
+        if ((rc = check_cuda(cudaMemcpyAsync(nosync->status, g.counters, 12, cudaMemcpyDeviceToHost, st), "copy status"))) return rc;
+        N = nosync->capacity;
+    } else {
+        uint32_t n_stack[2] = {0, 0};
+        uint32_t* n_host = readback_pad() ? readback_pad() : n_stack;
+        if ((rc = check_cuda(cudaMemcpyAsync(n_host, g.counters, 8, cudaMemcpyDeviceToHost, st), "copy num_rendered"))) return rc;
+        if ((rc = check_cuda(cudaStreamSynchronize(st), "sync num_rendered"))) return rc;
+        N = (int)n_host[0]; max_len = (int)n_host[1];
+    }
     *num_rendered = N;
 
     char* bbase = (char*)alloc(alloc_user, GSR_BUF_BINNING, carve_binning(nullptr, N, nullptr, nullptr, gx * gy));
     if (!bbase) { set_error("allocator returned NULL (binning)"); return GSR_EALLOC; }
     carve_binning(bbase, N, &bin, nullptr, gx * gy);
     if ((rc = check_cuda(launch_binning(P, gx, gy, N, max_len, g.rec, (int)sizeof(SurfelRec), SURFEL_DEPTH_OFF, g.tile_count, radii,
-                                        img.ranges, bin, st), "binning launch"))) return rc;
+                                        img.ranges, bin, st, 1, nosync ? g.counters : nullptr, img.tile_order), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
     if ((rc = check_cuda(launch_surfel_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_others, st),
@@ -99,6 +107,19 @@ int gsr_surfel_forward(
 {
     return surfel_forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations,
                                transMat_precomp, out_color, out_others, radii, alloc, alloc_user, num_rendered, stream);
+}
+
+int gsr_surfel_forward_nosync(
+    const GsrSettings* s, int P, int M,
+    const float* means3D, const float* shs, const float* colors_precomp,
+    const float* opacities, const float* scales, const float* rotations, const float* transMat_precomp,
+    float* out_color, float* out_others, int32_t* radii,
+    gsr_alloc_fn alloc, void* alloc_user, int capacity, uint32_t* status_pinned, void* stream)
+{
+    const NoSync ns{capacity, status_pinned};
+    int n = 0;
+    return surfel_forward_impl(s, P, M, means3D, shs, nullptr, false, colors_precomp, opacities, scales, rotations,
+                               transMat_precomp, out_color, out_others, radii, alloc, alloc_user, &n, stream, &ns);
 }
 
 static bool model_params_ok(int P, int M, const GsrModelParams* mp) {

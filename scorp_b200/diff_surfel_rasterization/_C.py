@@ -54,6 +54,44 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             arena.get(_lib.GSR_BUF_GEOM), arena.get(_lib.GSR_BUF_BINNING), arena.get(_lib.GSR_BUF_IMAGE))
 
 
+def rasterize_gaussians_nosync(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                               transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                               image_width, sh, degree, campos, prefiltered, debug, capacity, status):
+    """rasterize_gaussians without the host round trip (gsr_surfel_forward_nosync; see the 3DGS `_C` level and
+    scorp_b200/capacity.py). Returns the same tuple with num_rendered replaced by `capacity`."""
+    if means3D.dim() != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if not means3D.is_cuda:
+        raise _lib.GsrError("means3D must be a CUDA tensor: this rasterizer has no CPU path")
+    if not (status.is_pinned() and status.dtype == torch.int32 and status.numel() >= 4 and status.is_contiguous()):
+        raise _lib.GsrError("status must be a pinned, contiguous int32 tensor of 4 elements")
+    lib = _lib.lib()
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    means3D = _f32c(means3D, dev); colors = _f32c(colors, dev); opacity = _f32c(opacity, dev)
+    scales = _f32c(scales, dev); rotations = _f32c(rotations, dev); transMat_precomp = _f32c(transMat_precomp, dev)
+    sh = _f32c(sh, dev)
+    background = _f32c(background, dev); viewmatrix = _f32c(viewmatrix, dev)
+    projmatrix = _f32c(projmatrix, dev); campos = _f32c(campos, dev)
+    out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+    out_others = torch.empty((NUM_OTHERS, H, W), dtype=torch.float32, device=dev)
+    radii = torch.empty((P,), dtype=torch.int32, device=dev)
+    arena = _Arena(dev)
+    s = _settings(background, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy, H, W, scale_modifier,
+                  degree, prefiltered, debug)
+    with torch.cuda.device(dev):
+        rc = lib.gsr_surfel_forward_nosync(
+            C.byref(s), P, M, ptr(means3D), ptr(sh), ptr(colors), ptr(opacity), ptr(scales), ptr(rotations),
+            ptr(transMat_precomp), out_color.data_ptr(), out_others.data_ptr(), ptr(radii),
+            arena.fn, None, int(capacity), status.data_ptr(), _stream(dev))
+    if arena.error is not None:
+        raise arena.error
+    _lib.check(rc, "gsr_surfel_forward_nosync")
+    return (int(capacity), out_color, out_others, radii,
+            arena.get(_lib.GSR_BUF_GEOM), arena.get(_lib.GSR_BUF_BINNING), arena.get(_lib.GSR_BUF_IMAGE))
+
+
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_others, sh, degree, campos,
