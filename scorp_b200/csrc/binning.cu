@@ -13,6 +13,7 @@
 // The output lists are bit-identical to the reference's and cost ~20 B/instance of traffic
 // instead of ~150 B/instance for a 6-pass radix sort.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace gsr {
 
@@ -301,6 +302,160 @@ tile_sort_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const u
     }
 }
 
+// ---- 4b. per-tile LSD radix sort (segments of more than RADIX_MIN entries) ------------------------------------------
+// The 64-bit keys of a segment are unique (depth bits << 32 | Gaussian index) and the reference's order is (depth bits,
+// index). Sorting on the 32 depth bits alone takes four 8-bit passes instead of the ~log^2(n)/2 compare-exchange steps of
+// the network above; the index rides along as the payload. The segment arrives in arbitrary order (scatter_kernel's
+// cursor is an atomic), so stability cannot deliver the index order of equal depths: a last step ranks every run of
+// equal depth bits by index (runs are short: cloned Gaussians share a depth, nothing else does).
+//
+// One pass, CTA of W warps, every warp owns 32*K consecutive positions (K rounds of 32): per round the lanes holding the
+// same digit find each other with match.any; the lowest of them reads-and-bumps the warp's counter of that digit, so a
+// key's rank among the SAME-digit keys of its warp is (counter before) + (same-digit lanes below it) -- stable. A scan
+// over (digit, warp) turns the counters into destinations.
+constexpr int RADIX_K = 8;                     // positions per thread
+template <int THREADS> struct RadixSmem {
+    static constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
+    uint2 a[CAP], b[CAP];                      // .x = Gaussian index, .y = depth bits
+    uint16_t cnt[W][256];
+    uint32_t base[256];
+    uint32_t total[256];
+    uint32_t skip[4];                          // per pass: every key has the same digit (the pass is the identity)
+};
+template <int THREADS>
+__device__ __forceinline__ void tile_radix_one(RadixSmem<THREADS>& sm, int tile, int lo_len, const uint2* __restrict__ ranges,
+                                               const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
+                                               uint64_t* __restrict__ point_list_keys) {
+    constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
+    const uint2 rg = ranges[tile];
+    const int L = (int)(rg.y - rg.x);
+    if (L <= lo_len || L > CAP) return;         // CTA-uniform
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint64_t* seg = keys + rg.x;
+    for (int p = tid; p < L; p += THREADS) {
+        const uint64_t k = seg[p];
+        sm.a[p] = make_uint2((uint32_t)k, (uint32_t)(k >> 32));
+    }
+    uint2* src = sm.a;
+    uint2* dst = sm.b;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int p0 = w * 32 * RADIX_K + lane;      // this thread's position in round 0
+    if (tid < 4) sm.skip[tid] = 0u;
+#pragma unroll 1
+    for (int shift = 0; shift < 32; shift += 8) {
+        for (int i = tid; i < W * 128; i += THREADS) reinterpret_cast<uint32_t*>(&sm.cnt[0][0])[i] = 0u;
+        __syncthreads();                        // counters cleared; src complete (load or previous scatter)
+        uint2 key[RADIX_K];
+        uint32_t rank[RADIX_K];
+#pragma unroll
+        for (int r = 0; r < RADIX_K; ++r) {
+            const int p = p0 + r * 32;
+            if (p - lane >= L) { rank[r] = 0; key[r] = make_uint2(0u, 0u); continue; }      // warp-uniform: nothing left for this warp
+            const bool valid = p < L;
+            if (valid) key[r] = src[p];
+            const uint32_t dig = valid ? ((key[r].y >> shift) & 255u) : 256u;
+            const uint32_t peers = __match_any_sync(0xffffffffu, dig);
+            const int leader = __ffs(peers) - 1;
+            uint32_t prior = 0;
+            if (lane == leader && valid) {
+                prior = sm.cnt[w][dig];
+                sm.cnt[w][dig] = (uint16_t)(prior + __popc(peers));
+            }
+            prior = __shfl_sync(0xffffffffu, prior, leader);
+            rank[r] = prior + __popc(peers & lt);
+            __syncwarp();                        // the next round reads the counters this one wrote
+        }
+        __syncthreads();
+        // counters -> exclusive prefix over the warps, per digit; totals per digit
+        for (int d = tid; d < 256; d += THREADS) {
+            uint32_t run = 0;
+#pragma unroll 4
+            for (int ww = 0; ww < W; ++ww) { const uint32_t c = sm.cnt[ww][d]; sm.cnt[ww][d] = (uint16_t)run; run += c; }
+            sm.total[d] = run;
+            if (run == (uint32_t)L) sm.skip[shift >> 3] = 1u;
+        }
+        __syncthreads();
+        if (sm.skip[shift >> 3]) continue;       // CTA-uniform; nobody reads the counters any more
+        if (w == 0) {                            // exclusive scan of the 256 totals: 8 per lane
+            uint32_t t[8], sum = 0;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { t[e] = sm.total[lane * 8 + e]; sum += t[e]; }
+            uint32_t incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+            uint32_t run = incl - sum;
+#pragma unroll
+            for (int e = 0; e < 8; ++e) { sm.base[lane * 8 + e] = run; run += t[e]; }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < RADIX_K; ++r) {
+            const int p = p0 + r * 32;
+            if (p < L) {
+                const uint32_t dig = (key[r].y >> shift) & 255u;
+                dst[sm.base[dig] + sm.cnt[w][dig] + rank[r]] = key[r];
+            }
+        }
+        uint2* t = src; src = dst; dst = t;
+        __syncthreads();                         // scatter done: counters and bases may be overwritten, src is complete
+    }
+    // emit; runs of equal depth bits are put in index order (rank by counting inside the run)
+    const uint64_t tile_hi = (uint64_t)tile << 32;
+    uint32_t* out_list = point_list + rg.x;
+    uint64_t* out_keys = point_list_keys + rg.x;
+    for (int p = tid; p < L; p += THREADS) {
+        const uint2 k = src[p];
+        int at = p;
+        const bool tie = (p > 0 && src[p - 1].y == k.y) || (p + 1 < L && src[p + 1].y == k.y);
+        if (tie) {
+            int s0 = p;
+            while (s0 > 0 && src[s0 - 1].y == k.y) --s0;
+            int below = 0;
+            for (int q = s0; q < L && src[q].y == k.y; ++q) below += src[q].x < k.x;
+            at = s0 + below;
+        }
+        out_list[at] = k.x;
+        out_keys[at] = tile_hi | k.y;
+    }
+}
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+tile_radix_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                  uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    extern __shared__ __align__(16) unsigned char radix_smem[];
+    tile_radix_one<THREADS>(*reinterpret_cast<RadixSmem<THREADS>*>(radix_smem), blockIdx.x, lo_len, ranges, keys, point_list,
+                            point_list_keys);
+}
+template <int THREADS>
+__global__ void __launch_bounds__(THREADS)
+tile_radix_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const uint32_t* __restrict__ order,
+                         const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                         uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    extern __shared__ __align__(16) unsigned char radix_smem[];
+    const uint32_t n = *n_work;
+    for (uint32_t k = blockIdx.x; k < n; k += gridDim.x) {
+        tile_radix_one<THREADS>(*reinterpret_cast<RadixSmem<THREADS>*>(radix_smem), (int)order[k], lo_len, ranges, keys,
+                                point_list, point_list_keys);
+        __syncthreads();
+    }
+}
+
+// Segments of up to SORT_S_CAP entries: the network for the short ones, the radix sort above radix_min.
+template <int THREADS, int CAP>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_small_kernel(int radix_min, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
+                       uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
+    static_assert(CAP == THREADS * RADIX_K, "one radix CTA covers the size class");
+    extern __shared__ __align__(16) unsigned char small_smem[];
+    const uint2 rg = ranges[blockIdx.x];
+    const int L = (int)(rg.y - rg.x);
+    if (L <= radix_min)
+        tile_sort_one<THREADS, CAP>(reinterpret_cast<uint64_t*>(small_smem), blockIdx.x, 0, ranges, keys, point_list, point_list_keys);
+    else
+        tile_radix_one<THREADS>(*reinterpret_cast<RadixSmem<THREADS>*>(small_smem), blockIdx.x, radix_min, ranges, keys, point_list,
+                                point_list_keys);
+}
+
 // Segments longer than LONG_MIN (rare: > 8192 splats on one tile): chunks sorted in shared memory, merge
 // steps with stride >= LONG_CAP in global (L2-resident) memory, the tail of every merge per chunk in shared memory.
 constexpr int LONG_CAP = 4096;
@@ -383,7 +538,10 @@ tile_sort_long_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, co
 }
 
 constexpr int SORT_S_CAP = 1024, SORT_S_THREADS = 128;       // most tiles
-constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // crowded tiles (one CTA of 32 warps each)
+constexpr int SORT_M1_CAP = 4096, SORT_M1_THREADS = 512;     // crowded tiles: radix sort, three CTAs per SM
+constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // very crowded tiles: radix sort, one CTA of 32 warps per SM
+static_assert(SORT_S_CAP == SORT_S_CAP_ && SORT_S_CAP == SORT_S_THREADS * RADIX_K && SORT_M1_CAP == SORT_M1_THREADS * RADIX_K &&
+              SORT_M_CAP == SORT_M_THREADS * RADIX_K, "size classes");
 
 cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
                              cudaStream_t st, uint32_t capacity) {
@@ -391,46 +549,67 @@ cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* range
     return cudaGetLastError();
 }
 
+// Shorter segments than this go through the network instead of the radix sort (tunable: GSR_RADIX_MIN; a value >= 1024
+// sends the whole small class through the network). Measured on B200: see DESIGN.md 5.
+static int radix_min() {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("GSR_RADIX_MIN"); v = e ? atoi(e) : 512; if (v < 8) v = 8; if (v > SORT_S_CAP) v = SORT_S_CAP; }
+    return v;
+}
+static size_t small_smem_bytes() {
+    const size_t a = sphys_host(SORT_S_CAP) * 8, b = sizeof(RadixSmem<SORT_S_THREADS>);
+    return a > b ? a : b;
+}
+// dynamic shared memory above 48 KB has to be requested per kernel and device
+static cudaError_t set_radix_attrs() {
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || done[dev]) return cudaSuccess;
+    const int m1 = (int)sizeof(RadixSmem<SORT_M1_THREADS>), m = (int)sizeof(RadixSmem<SORT_M_THREADS>);
+    if ((e = cudaFuncSetAttribute(tile_radix_kernel<SORT_M1_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, m1)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tile_radix_kernel<SORT_M_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, m)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tile_radix_queued_kernel<SORT_M1_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, m1)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tile_radix_queued_kernel<SORT_M_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, m)) != cudaSuccess) return e;
+    done[dev] = true;
+    return cudaSuccess;
+}
+
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
                            cudaStream_t st, int views, const uint32_t* counters, const uint32_t* order) {
     const int tiles = gx * gy * views;
     if (N <= 0) return cudaSuccess;
+    cudaError_t e;
+    scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
+                                                    tile_count, ranges, bin.scratch, counters ? counters + 2 : nullptr);
+    tile_sort_small_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, small_smem_bytes(), st>>>(
+        radix_min(), ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+    const size_t m1 = sizeof(RadixSmem<SORT_M1_THREADS>), m = sizeof(RadixSmem<SORT_M_THREADS>);
     if (counters) {
-        // no-sync forward: N is the caller's capacity, the real counts live on the device (counters, see tile_scan_kernel)
-        scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
-                                                        tile_count, ranges, bin.scratch, counters + 2);
-        tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
-            0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
-        static bool attr_set[64] = {};
-        int dev = 0;
-        cudaError_t e = cudaGetDevice(&dev);
-        if (e != cudaSuccess) return e;
-        if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-            e = cudaFuncSetAttribute(tile_sort_queued_kernel<SORT_M_THREADS, SORT_M_CAP>,
-                                     cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sphys_host(SORT_M_CAP) * 8));
-            if (e != cudaSuccess) return e;
-            attr_set[dev] = true;
-        }
-        const int grid = tiles < 148 * 2 ? tiles : 148 * 2;      // two CTAs of 1024 threads per SM; exits at once when *n_work == 0
-        tile_sort_queued_kernel<SORT_M_THREADS, SORT_M_CAP><<<grid, SORT_M_THREADS, sphys_host(SORT_M_CAP) * 8, st>>>(
+        // no-sync forward: N is the caller's capacity and the host knows no segment length; fixed grids walk the head of
+        // `order` (counters[3] tiles can have more than SORT_S_CAP entries, counters[4] more than SORT_M_CAP) and leave at
+        // once when there is nothing for them
+        if ((e = set_radix_attrs()) != cudaSuccess) return e;
+        const int g1 = tiles < 148 * 3 ? tiles : 148 * 3, g2 = tiles < 148 ? tiles : 148, g3 = tiles < 148 * 2 ? tiles : 148 * 2;
+        tile_radix_queued_kernel<SORT_M1_THREADS><<<g1, SORT_M1_THREADS, m1, st>>>(
             SORT_S_CAP, counters + 3, order, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
-        tile_sort_long_queued_kernel<<<grid, LONG_THREADS, 0, st>>>(SORT_M_CAP, counters + 4, order, ranges, bin.scratch,
-                                                                    bin.point_list, bin.point_list_keys);
+        tile_radix_queued_kernel<SORT_M_THREADS><<<g2, SORT_M_THREADS, m, st>>>(
+            SORT_M1_CAP, counters + 3, order, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+        tile_sort_long_queued_kernel<<<g3, LONG_THREADS, 0, st>>>(SORT_M_CAP, counters + 4, order, ranges, bin.scratch,
+                                                                  bin.point_list, bin.point_list_keys);
         return cudaGetLastError();
     }
-    scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,
-                                                    tile_count, ranges, bin.scratch, nullptr);
-    tile_sort_kernel<SORT_S_THREADS, SORT_S_CAP><<<tiles, SORT_S_THREADS, sphys_host(SORT_S_CAP) * 8, st>>>(
-        0, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+    // the host read the longest segment back with N: only the kernels that have work are launched
     if (max_len > SORT_S_CAP) {
-        // per device and cheap; only scenes with crowded tiles come here
-        cudaError_t e = cudaFuncSetAttribute(tile_sort_kernel<SORT_M_THREADS, SORT_M_CAP>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sphys_host(SORT_M_CAP) * 8));
-        if (e != cudaSuccess) return e;
-        tile_sort_kernel<SORT_M_THREADS, SORT_M_CAP><<<tiles, SORT_M_THREADS, sphys_host(SORT_M_CAP) * 8, st>>>(
-            SORT_S_CAP, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
+        if ((e = set_radix_attrs()) != cudaSuccess) return e;
+        tile_radix_kernel<SORT_M1_THREADS><<<tiles, SORT_M1_THREADS, m1, st>>>(SORT_S_CAP, ranges, bin.scratch, bin.point_list,
+                                                                                bin.point_list_keys);
     }
+    if (max_len > SORT_M1_CAP)
+        tile_radix_kernel<SORT_M_THREADS><<<tiles, SORT_M_THREADS, m, st>>>(SORT_M1_CAP, ranges, bin.scratch, bin.point_list,
+                                                                            bin.point_list_keys);
     if (max_len > SORT_M_CAP)
         tile_sort_long_kernel<<<tiles, LONG_THREADS, 0, st>>>(SORT_M_CAP, ranges, bin.scratch, bin.point_list, bin.point_list_keys);
     return cudaGetLastError();

@@ -212,3 +212,35 @@ def test_against_cpu_oracle():
         a = go[k].cpu().numpy().reshape(-1); b = g[k].reshape(-1)
         scale = np.abs(b).max()
         assert np.abs(a - b).max() <= 2e-3 * scale + 1e-12, k
+
+
+@pytest.mark.parametrize("name,P,W,H,plane", [
+    ("clones_small_lists", 40_000, 320, 208, False),     # lists of a few hundred entries
+    ("clones_mid_lists", 60_000, 96, 64, False),         # 1024 < L <= 8192: the radix classes
+    ("one_depth_plane", 12_000, 96, 64, True),           # EVERY Gaussian at the same depth: runs as long as the lists
+])
+def test_equal_depths_come_out_in_index_order(name, P, W, H, plane):
+    """The reference's order inside a tile is (depth bits, Gaussian index): its radix sort is stable and
+    duplicateWithKeys emits instances in index order (rasterizer_impl.cu:98-109,301-309). Cloned Gaussians
+    (densify_and_clone copies xyz) share their depth bit for bit, so ties are a real input; here half of the Gaussians
+    are clones of the other half at shuffled indices, or all of them lie in one plane facing the camera."""
+    ref_cuda = _need_ref()
+    sc = h.make("C1", P=P, W=W, H=H, random_bg=True); cam = sc.cameras[0]
+    g = torch.Generator().manual_seed(12)
+    if plane:
+        sc.means3D[:, 2] = 6.0                           # camera 0 is the identity: depth = z exactly
+    else:
+        perm = torch.randperm(P, generator=g).cuda()
+        src, dst = perm[: P // 2], perm[P // 2: 2 * (P // 2)]
+        sc.means3D[dst] = sc.means3D[src]                # same position, different scale / rotation / colour
+    fo = h.ours_forward(sc, cam); fr = h.ref_forward(sc, cam)
+    assert fo["num_rendered"] == fr["num_rendered"]
+    io, ir = h.ours_intermediates(fo), ref_cuda.dgr_intermediates(fr)
+    keys = ir["point_list_keys"]
+    ties = int((keys[1:] == keys[:-1]).sum())
+    assert ties > (fo["num_rendered"] // 4 if not plane else fo["num_rendered"] // 2), ties
+    _assert_exact("point_list_keys", io["point_list_keys"], ir["point_list_keys"])
+    _assert_exact("point_list", io["point_list"], ir["point_list"])
+    _assert_exact("n_contrib", io["n_contrib"], ir["n_contrib"])
+    for k in ("color", "depth", "alpha"):
+        _assert_exact(k, fo[k], fr[k])
