@@ -167,11 +167,17 @@ def time_steps(step, K, W, world, sampler=None):
         ev[k + 1].record()
     torch.cuda.synchronize(); barrier(world); torch.cuda.synchronize()
     ms = torch.tensor([ev[0].elapsed_time(ev[K])], device="cuda", dtype=torch.float64)
+    spread = {}
     if world > 1:
+        # every rank's own time for the K steps: with one DIFFERENT camera per rank the slowest view sets the step
+        allms = [torch.zeros_like(ms) for _ in range(world)]
+        dist.all_gather(allms, ms)
+        spread["rank_ms_per_step"] = [float(t) / K for t in allms]
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     per = sorted(ev[k].elapsed_time(ev[k + 1]) for k in range(K))
     clocks = sampler.stop() if sampler else None
-    return float(ms.item()), clocks, {"median": per[K // 2], "min": per[0], "max": per[-1]}
+    spread.update({"median": per[K // 2], "min": per[0], "max": per[-1]})
+    return float(ms.item()), clocks, spread
 
 
 def stage_bytes(P, M, Pvis, N, W, H, surfel=False):
@@ -555,6 +561,12 @@ def run(arm, args, rank, world, local):
     in_sha = inputs_sha(sc, cams[0])
     bin_sha, n_first = arm.binning_sha(sc, cams[0])
     n, radii, _ = step_resident()
+    rank_instances = None
+    if world > 1 and not batched:
+        t_n = torch.tensor([int(n)], device=dev, dtype=torch.int64)
+        all_n = [torch.zeros_like(t_n) for _ in range(world)]
+        dist.all_gather(all_n, t_n)
+        rank_instances = [int(x) for x in all_n]          # (Gaussian, tile) instances of each rank's (last) view
     Pvis = int((radii > 0).sum())          # batched: radii is [V, P] and n the total, so the stage bytes cover all views
     prime(step_resident, world)
     sampler = ClockSampler(local) if rank == 0 else None
@@ -705,7 +717,8 @@ def run(arm, args, rank, world, local):
                 clocks=clocks, per=per, per_e2e=per_e2e, views=n_views, vpr=vpr, surfel=surfel, fwd_only=fwd_only,
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
                 d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched,
-                inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck, e2e_modes=e2e_modes, e2e_mode=best)
+                inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck, e2e_modes=e2e_modes, e2e_mode=best,
+                rank_instances=rank_instances)
 
 
 def main():
@@ -764,6 +777,8 @@ def main():
         line["exchange"] = r["exch"]
     if r.get("xcheck"):
         line["exchange_check"] = r["xcheck"]
+    if r.get("rank_instances"):
+        line["config"]["num_rendered_per_rank"] = r["rank_instances"]
     if r["tstats"]:
         line["config"]["tile_lists"] = r["tstats"]
     if args.impl == "ours":

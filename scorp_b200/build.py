@@ -23,6 +23,7 @@ FLAGS = [
     "-O3", "-std=c++17", "-lineinfo", "-shared",
     "-Xcompiler", "-fPIC,-O2,-Wall",
     "-Xptxas", "-v",
+    "-ldl",          # nvtx3 (header-only) loads its injection library on demand
 ]
 
 

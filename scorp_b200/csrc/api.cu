@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <nvtx3/nvToolsExt.h>      // header-only; the ranges cost nothing unless a tool (nsys, ncu --nvtx) is attached
 
 namespace gsr {
 
@@ -36,8 +37,20 @@ struct StageProf {
 static StageProf g_prof;
 // events: 0 start fwd, 1 after preprocess, 2 after binning, 3 after blend fwd,
 //         4 start bwd, 5 after blend bwd, 6 after preprocess bwd
+// NVTX range per stage (SURVEY.md 5 "tracing"), only while gsr_profile_enable(1) is in force: prof_mark(i) closes the
+// range of the stage that just ended and opens the next one; StageRanges closes whatever is open when the entry point
+// returns (also on an error path).
+static thread_local bool g_nvtx_open = false;
+static void nvtx_stage(const char* name) {
+    if (g_nvtx_open) { nvtxRangePop(); g_nvtx_open = false; }
+    if (name) { nvtxRangePushA(name); g_nvtx_open = true; }
+}
+StageRanges::~StageRanges() { nvtx_stage(nullptr); }
 void prof_mark(int i, cudaStream_t st) {
-    if (!g_prof.on) return;
+    if (!g_prof.on) { return; }
+    static const char* const kNext[PROF_EV] = { "gsr:preprocess", "gsr:binning", "gsr:blend_forward", nullptr,
+                                                "gsr:blend_backward", "gsr:preprocess_backward", nullptr };
+    nvtx_stage(kNext[i]);
     if (!g_prof.made) { for (auto& r : g_prof.ev) for (auto& e : r) cudaEventCreate(&e); g_prof.made = true; }
     const int slot = (i < 4 ? g_prof.n_fwd : g_prof.n_bwd) % PROF_RING;
     cudaEventRecord(g_prof.ev[slot][i], st);
@@ -108,6 +121,7 @@ static int forward_impl(
     gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, int views = 1, const NoSync* nosync = nullptr)
 {
     cudaStream_t st = (cudaStream_t)stream;
+    StageRanges nvtx_guard;
     if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
     if (nosync && (nosync->capacity < 1 || !nosync->status)) { set_error("no-sync forward needs capacity >= 1 and a pinned status slot"); return GSR_EINVAL; }
     if (views < 1 || (long long)views * P > 0x7fffffffLL) { set_error("bad view count %d for P=%d", views, P); return GSR_EINVAL; }
@@ -310,6 +324,7 @@ static int backward_impl(
     cudaStream_t st = (cudaStream_t)stream;
     // whatever was armed for "the next backward of this thread" is consumed by THIS call, also when it returns early:
     // the armed state holds raw pointers into a caller-owned gradient arena and into peer buffers
+    StageRanges nvtx_guard;
     const EarlyRgb e = take_early_rgb();
     const PeerHead peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }

@@ -148,6 +148,8 @@ uint32_t* readback_pad();           // api.cu: pinned 64-byte buffer of the call
 // readback of N; status = pinned host uint32[4] that receives {N, longest segment, overflow flag, 0} asynchronously
 struct NoSync { int capacity; uint32_t* status; };
 
+struct StageRanges { ~StageRanges(); };   // api.cu: closes the NVTX stage range an entry point may leave open
+
 // error plumbing (api.cu)
 void set_error(const char* fmt, ...);
 int  check_cuda(cudaError_t e, const char* what);

@@ -24,6 +24,7 @@ static int surfel_forward_impl(
     gsr_alloc_fn alloc, void* alloc_user, int* num_rendered, void* stream, const NoSync* nosync = nullptr)
 {
     cudaStream_t st = (cudaStream_t)stream;
+    StageRanges nvtx_guard;
     if (!s || !alloc || !num_rendered) { set_error("null settings/allocator/num_rendered"); return GSR_EINVAL; }
     *num_rendered = 0;
     const int W = s->image_width, H = s->image_height;
@@ -197,6 +198,7 @@ static int surfel_backward_impl(
     void* workspace, size_t workspace_bytes, void* stream, const SurfelRawBwd* raw)
 {
     cudaStream_t st = (cudaStream_t)stream;
+    StageRanges nvtx_guard;
     const EarlyRgb e = take_early_rgb();         // consumed by THIS call, also when it returns early (see api.cu)
     const PeerHead peer_head = take_peer_head();
     if (!s) { set_error("null settings"); return GSR_EINVAL; }
