@@ -277,6 +277,7 @@ struct FwdArgs {
     // opacities / scales / rotations hold the stored (pre-activation) parameters
     const float* shs_rest = nullptr;
     bool raw = false;
+    bool skip_histogram = false;       // batched views: launch_views_histogram counts the instances per tile instead
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views = 1);
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
@@ -289,6 +290,11 @@ cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* range
 cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void* recs, int rec_stride, int depth_off,
                            uint32_t* tile_count, const int32_t* radii, const uint2* ranges, const BinningState& bin,
                            cudaStream_t st, int views = 1, const uint32_t* counters = nullptr, const uint32_t* order = nullptr);
+// batched views with a small tile grid: preprocess leaves the per-tile histogram to launch_views_histogram (atomics
+// aggregated per CTA in shared memory, binning.cu 3b) and launch_binning scatters the same way
+bool views_aggregated(int views, int tiles_per_view);
+cudaError_t launch_views_histogram(int P_total, int views, int gx, int gy, const void* recs, int rec_stride, const int32_t* radii,
+                                   uint32_t* tile_count, cudaStream_t st);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
                                   const BinningState& bin, const float* bg,
                                   float* out_color, float* out_depth, float* out_alpha, cudaStream_t st, int views = 1);

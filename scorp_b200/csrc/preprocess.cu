@@ -172,7 +172,7 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     }
     // per-tile instance histogram (replaces the reference's scan over tiles_touched + duplicateWithKeys counting):
     // small rectangles by their own lane, large ones spread over the warp so one big splat does not serialise it
-    tile_histogram(g.tile_count, a.gx, rx0, ry0, rw, tiles);
+    if (!a.skip_histogram) tile_histogram(g.tile_count, a.gx, rx0, ry0, rw, tiles);
     // total instance count: one atomic per warp
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);
