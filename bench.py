@@ -682,6 +682,32 @@ def run(arm, args, rank, world, local):
     best = min((m for m in e2e_modes if "ms_per_step" in e2e_modes[m]), key=lambda m: e2e_modes[m]["ms_per_step"])
     ms_e2e_total, per_e2e = e2e_modes[best]["ms_per_step"] * args.steps, e2e_modes[best]["spread"]
     exch, xcheck = None, None
+    local_ms = None
+    if world > 1 and not fwd_only and arm.name == "ours":
+        # what each rank's own view costs WITHOUT any exchange: the slowest of them bounds the view-sharded step from
+        # below (one different camera per rank), the rest of ms_per_step is the exchange
+        from scorp_b200.diff_gaussian_rasterization import _C as _c3x
+        from scorp_b200.diff_surfel_rasterization import _C as _c2x
+        saved = (_c3x._factored[0], _c2x._factored[0], _c3x._backward_hook[0], _c2x._backward_hook[0])
+        _c3x._factored[0] = _c2x._factored[0] = None
+        _c3x._backward_hook[0] = _c2x._backward_hook[0] = None
+        was_factored, arm.factored = arm.factored, True         # Ours.reduce() returns at once
+        try:
+            for _ in range(3):
+                step_resident()
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(10):
+                step_resident()
+            e1.record(); torch.cuda.synchronize()
+            t_loc = torch.tensor([e0.elapsed_time(e1) / 10], device=dev, dtype=torch.float64)
+            allt = [torch.zeros_like(t_loc) for _ in range(world)]
+            dist.all_gather(allt, t_loc)
+            local_ms = [float(t) for t in allt]
+        finally:
+            arm.factored = was_factored
+            _c3x._factored[0], _c2x._factored[0], _c3x._backward_hook[0], _c2x._backward_hook[0] = saved
     if world > 1 and not fwd_only:
         exch = time_exchange(arm, P, M, surfel, world, dev)
         if arm.name == "ours":
@@ -718,7 +744,7 @@ def run(arm, args, rank, world, local):
                 h2d=sum(h.numel() for h in h_cams) * 4 + (0 if fwd_only else sum(h.numel() for h in h_grads) * 4),
                 d2h=4, launches=launches, exchange=exchange, exch=exch, tstats=tstats, batched=batched,
                 inputs_sha=in_sha, binning_sha=bin_sha, n_first=n_first, xcheck=xcheck, e2e_modes=e2e_modes, e2e_mode=best,
-                rank_instances=rank_instances)
+                rank_instances=rank_instances, local_ms=local_ms)
 
 
 def main():
@@ -779,6 +805,10 @@ def main():
         line["exchange_check"] = r["xcheck"]
     if r.get("rank_instances"):
         line["config"]["num_rendered_per_rank"] = r["rank_instances"]
+    if r.get("local_ms"):
+        line["view_sharding"] = {"rank_ms_without_exchange": r["local_ms"], "slowest_view_ms": max(r["local_ms"]),
+                                 "exchange_overhead_ms": r["ms_step"] - max(r["local_ms"]),
+                                 "note": "every rank renders a different camera: the slowest view bounds the step from below; the overhead is what the gradient exchange adds to it"}
     if r["tstats"]:
         line["config"]["tile_lists"] = r["tstats"]
     if args.impl == "ours":
