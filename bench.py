@@ -227,6 +227,16 @@ def inputs_sha(sc, cam):
     return sha_of([sc.means3D, sc.scales, sc.rotations, sc.opacities, sc.shs, cam.viewmatrix, cam.projmatrix])
 
 
+def ncu_issue(cfg_name, stage):
+    """warp instructions / active lanes / issue-slot use of the stage's largest kernel from the committed `ncu --set full`
+    capture (profiles/ncu_issue.json, written by tools/ncu_table.py); None when not captured."""
+    p = ROOT / "profiles" / "ncu_issue.json"
+    try:
+        return json.loads(p.read_text()).get(cfg_name, {}).get(stage)
+    except Exception:
+        return None
+
+
 def out_channels(surfel):
     return (3, 7) if surfel else (3, 1, 1)
 
@@ -827,6 +837,18 @@ def main():
                             "traffic": ncu_traffic(args.config, dom["stage"]),
                             "note": "per view, last view of the step; blend stages are SM-issue bound (DESIGN.md 5), the HBM fraction is reported for the contract",
                             "stages": stages}
+        # the roof that actually binds the blends: instruction issue, one warp instruction per clock per SM sub-partition
+        # (4 x 148 per clock; measured with tools/ubench/f32x2.cu). Instruction count and lane occupancy come
+        # from the committed ncu capture of the same kernel and config, the time is this run's CUDA-event stage time.
+        iss = ncu_issue(args.config, dom["stage"])
+        if iss and dom["ms"]:
+            f_clk = ((r["clocks"] or {}).get("sm_mhz") or 1965.0) * 1e6
+            peak_g = 4 * 148 * f_clk / 1e9
+            ach_g = iss["warp_inst"] / (dom["ms"] * 1e-3) / 1e9
+            line["roofline"]["issue"] = {"kernel": iss["kernel"], "warp_inst": iss["warp_inst"], "achieved_ginst_s": ach_g,
+                                         "peak_ginst_s": peak_g, "frac": ach_g / peak_g, "lanes_active": iss["lanes_active"],
+                                         "ncu_issue_active_pct": iss["issue_active_pct"], "sm_mhz": f_clk / 1e6,
+                                         "source": "profiles/ncu_issue.json (ncu --set full) + live stage time"}
         if not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline(args.config, W, H)
