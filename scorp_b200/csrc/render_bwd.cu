@@ -80,8 +80,12 @@ render_backward_kernel(int W, int H, int gx,
     const float nddelx = -0.5f * W, nddely = -0.5f * H;
 
     // which reduced value this lane commits (see bfly order below)
-    const bool b1 = lane & 2, b2 = lane & 4, b3 = lane & 8, b4 = lane & 16;
-    const bool writer = !(lane & 1) && (!b1 || (!b2 && !b3));
+    // the lane id in an opaque register: the role bits are then one LOP3-with-predicate each where they are used, instead
+    // of being re-derived from SR_TID.X inside every visit (ptxas cannot keep five predicates alive across the loop)
+    uint32_t lane_o;
+    asm volatile("mov.u32 %0, %1;" : "=r"(lane_o) : "r"((uint32_t)lane));
+    const bool b1 = lane_o & 2, b2 = lane_o & 4, b3 = lane_o & 8, b4 = lane_o & 16;
+    const bool writer = !(lane_o & 1) && (!b1 || (!b2 && !b3));
     const int slot = b1 ? (8 + (b4 ? 1 : 0)) : ((b2 ? 4 : 0) + (b3 ? 2 : 0) + (b4 ? 1 : 0));
 
     auto issue = [&](int r) {
@@ -106,7 +110,10 @@ render_backward_kernel(int W, int H, int gx,
         if (r > 0) { issue(r - 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
         __syncthreads();
 
-        const GaussRec* buf = s_rec[r & 1];
+        // shared-window address of this round's buffer, made opaque so that it stays in ONE register for the round: left
+        // to itself ptxas re-derives it (S2R SR_CgaCtaId, LEA, 2 x IMAD ...) in front of every visit's loads
+        uint32_t buf_s;
+        asm volatile("mov.u32 %0, %1;" : "=r"(buf_s) : "r"((uint32_t)__cvta_generic_to_shared(s_rec[r & 1])));
         // which entries to visit: the forward recorded, per warp block, the entries that blended into some pixel
         // of the block (render_fwd.cu); everything else contributes nothing here either
         if (tid < 32) {
@@ -125,8 +132,9 @@ render_backward_kernel(int W, int H, int gx,
                 const uint32_t pos = (uint32_t)(r * BATCH + j);      // 0-based list position
                 if (pos >= warp_max) continue;
 
-                const float4 g0 = *reinterpret_cast<const float4*>(&buf[j]);
-                const float4 g1 = *(reinterpret_cast<const float4*>(&buf[j]) + 1);
+                const uint32_t rec_s = buf_s + (uint32_t)j * (uint32_t)sizeof(GaussRec);
+                const float4 g0 = lds128(rec_s);
+                const float4 g1 = lds128(rec_s + 16);
                 float dx; float2 dy;
                 const float2 power = pair_power(g0.x, g0.y, g0.z, g0.w, g1.x, pxf, npy, dx, dy);
                 bool a0 = (pos < last0) && !(power.x > 0.0f) && !(power.x < g1.w);
@@ -149,7 +157,7 @@ render_backward_kernel(int W, int H, int gx,
                     // below is then zero and its state unchanged (finite colours and depth assumed)
                     if (!a0) { G.x = 0.f; alpha.x = 0.f; }
                     if (!a1) { G.y = 0.f; alpha.y = 0.f; }
-                    const float4 g2 = *(reinterpret_cast<const float4*>(&buf[j]) + 2);
+                    const float4 g2 = lds128(rec_s + 32);
                     const float2 oma = __ffma2_rn(alpha, bc(-1.0f), bc(1.0f));
                     const float2 inv = make_float2(a0 ? rcp_approx(oma.x) : 1.0f, a1 ? rcp_approx(oma.y) : 1.0f);
                     T = __fmul2_rn(T, inv);

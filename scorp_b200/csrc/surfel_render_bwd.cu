@@ -7,6 +7,7 @@
 // opacity 1) are reduced over the warp with a multi-value butterfly (20 shuffles for 18 values) and
 // committed as one red.global.add.f32 per term per (warp, surfel) into an 80-byte accumulator slot.
 #include "surfel.cuh"
+#include "blend.cuh"
 
 namespace gsr {
 
@@ -193,7 +194,10 @@ surfel_render_backward_kernel(int W, int H, int gx,
                     const float4 q4 = q[4];
                     const float nrm0 = q2.w, nrm1 = q3.x, nrm2 = q3.y, opa = q3.z;
                     const float col0 = q3.w, col1 = q4.x, col2 = q4.y;
-                    const float inv_1ma = __frcp_rn(1.f - alpha);     // shared by the two divisions below (gradients: rtol 1e-4)
+                    // Gradient-only quotients use the bare MUFU.RCP (rcp.approx.ftz, relative error 2^-23 against a tolerance of
+                    // 1e-4; every operand is a normal number: 1 - alpha in [0.01, 1], c_d >= 0.2). The two divisions above that
+                    // form sx, sy stay IEEE: they decide branches and must reproduce the forward bit for bit.
+                    const float inv_1ma = rcp_approx(1.f - alpha);
                     T = T * inv_1ma;
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;
@@ -206,8 +210,9 @@ surfel_render_backward_kernel(int W, int H, int gx,
 
                     float dL_dz = 0.0f;
                     float dL_dweight = 0;
-                    const float m_d = kFarB / (kFarB - kNearB) * (1 - kNearB / c_d);
-                    const float dmd_dd = (kFarB * kNearB) / ((kFarB - kNearB) * c_d * c_d);
+                    const float inv_cd = rcp_approx(c_d);
+                    const float m_d = kFarB / (kFarB - kNearB) * (1 - kNearB * inv_cd);
+                    const float dmd_dd = ((kFarB * kNearB) / (kFarB - kNearB)) * (inv_cd * inv_cd);
                     if (pos == median_contributor - 1u) dL_dz += dL_dmedian_depth;
                     dL_dweight += (final_D2 + m_d * m_d * final_A - 2 * m_d * final_D) * dL_dreg;
                     dL_dalpha += dL_dweight - last_dL_dT;
@@ -239,8 +244,9 @@ surfel_render_backward_kernel(int W, int H, int gx,
                         // backward.cu:399-429
                         const float dLdsx = dL_dG * -G * sx + dL_dz * Tw.x;
                         const float dLdsy = dL_dG * -G * sy + dL_dz * Tw.y;
-                        const float dsx_pz = dLdsx / p.z;
-                        const float dsy_pz = dLdsy / p.z;
+                        const float inv_pz = rcp_approx(p.z);
+                        const float dsx_pz = dLdsx * inv_pz;
+                        const float dsy_pz = dLdsy * inv_pz;
                         const float3 dL_dp = make_float3(dsx_pz, dsy_pz, -(dsx_pz * sx + dsy_pz * sy));
                         const float3 dL_dk = make_float3(l.y * dL_dp.z - l.z * dL_dp.y, l.z * dL_dp.x - l.x * dL_dp.z,
                                                          l.x * dL_dp.y - l.y * dL_dp.x);
