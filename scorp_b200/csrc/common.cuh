@@ -85,13 +85,16 @@ inline size_t carve_image(char* base, int W, int H, ImageState* s, size_t* off =
     return o;
 }
 inline size_t contrib_slots(int N, int tiles) { return (size_t)(N > 0 ? N : 0) / 32 + (size_t)tiles + 2; }
+// one slot = 32 list entries of a tile; 3DGS tiles have 4 warp blocks (4 words per slot), surfel tiles 8 (8 words per slot)
+constexpr int CONTRIB_WORDS_MAX = 8;
+inline size_t contrib_bytes(int N, int tiles) { return contrib_slots(N, tiles) * CONTRIB_WORDS_MAX * sizeof(uint32_t); }
 inline size_t carve_binning(char* base, int N, BinningState* b, size_t* off = nullptr, int tiles = 0) {
     size_t n = (size_t)(N > 0 ? N : 1);
     size_t o = 0;
     size_t a0 = o; o = align_up(o + n * 4);
     size_t a1 = o; o = align_up(o + n * 8);
     size_t a2 = o; o = align_up(o + n * 8);
-    size_t a3 = o; o = align_up(o + contrib_slots(N, tiles) * sizeof(uint4));     // last: the public offsets do not move
+    size_t a3 = o; o = align_up(o + contrib_bytes(N, tiles));                     // last: the public offsets do not move
     if (off) { off[0] = a0; off[1] = a1; off[2] = a2; }
     if (b) { b->point_list = (uint32_t*)(base + a0); b->point_list_keys = (uint64_t*)(base + a1);
              b->scratch = (uint64_t*)(base + a2); b->contrib = (uint4*)(base + a3); }

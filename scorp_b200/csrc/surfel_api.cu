@@ -93,6 +93,7 @@ static int surfel_forward_impl(
                                         img.ranges, bin, st, 1, nosync ? g.counters : nullptr, img.tile_order), "binning launch"))) return rc;
     if ((rc = stage_check(s, st, "binning"))) return rc;
     prof_mark(2, st);
+    if ((rc = check_cuda(cudaMemsetAsync(bin.contrib, 0, contrib_bytes(N, gx * gy), st), "memset contribution masks"))) return rc;
     if ((rc = check_cuda(launch_surfel_render_forward(W, H, gx, gy, g, img, bin, s->bg, out_color, out_others, st),
                          "surfel render forward launch"))) return rc;
     prof_mark(3, st);

@@ -2,7 +2,7 @@
 //
 // Replaces renderCUDA (reference diff-surfel-rasterization/cuda_rasterizer/backward.cu:145-446).
 // Same structure as render_bwd.cu: traversal starts at the tile's largest n_contrib, records are
-// staged with cp.async, warps skip entries whose contribution box misses their 8x4 pixel block,
+// staged with cp.async, a warp visits only the entries the forward recorded as contributing to its 8x4 pixel block,
 // and the up-to-16 per-pair gradient terms (colour 3, normal 3, transMat 9 or mean2D 2 + transMat 3,
 // opacity 1) are reduced over the warp with a multi-value butterfly (20 shuffles for 18 values) and
 // committed as one red.global.add.f32 per term per (warp, surfel) into an 80-byte accumulator slot.
@@ -51,7 +51,7 @@ surfel_render_backward_kernel(int W, int H, int gx,
                               const float* __restrict__ final_Ts, const float* __restrict__ in_M1,
                               const float* __restrict__ in_M2,
                               const float* __restrict__ dL_dpixels, const float* __restrict__ dL_dothers,
-                              float* __restrict__ acc, int direct_max) {
+                              float* __restrict__ acc, int direct_max, const uint32_t* __restrict__ contrib) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SurfelRec (*s_rec)[BATCH] = reinterpret_cast<SurfelRec (*)[BATCH]>(smem_raw);
     uint32_t (*s_bal)[8] = reinterpret_cast<uint32_t (*)[8]>(smem_raw + 2 * BATCH * sizeof(SurfelRec));
@@ -122,6 +122,7 @@ surfel_render_backward_kernel(int W, int H, int gx,
         cp_async_commit();
     };
 
+    const uint32_t* my_contrib = contrib + contrib_base(range.x, tile) * 8;
     const int r_start = (int)((max_contrib - 1) / BATCH);
     issue(r_start);
     for (int r = r_start; r >= 0; --r) {
@@ -129,23 +130,12 @@ surfel_render_backward_kernel(int W, int H, int gx,
         if (r > 0) { issue(r - 1); cp_async_wait<1>(); } else { cp_async_wait<0>(); }
         __syncthreads();
 
-        const int n_here = min(BATCH, total - r * BATCH);
         const SurfelRec* buf = s_rec[r & 1];
-        {
-            uint32_t mask = 0;
-            if (tid < n_here) {
-                const float4 box = *(reinterpret_cast<const float4*>(&buf[tid]) + 5);
-#pragma unroll
-                for (int w = 0; w < 8; ++w) {
-                    const float x0 = (float)(tile_x + (w & 1) * 8), y0 = (float)(tile_y + (w >> 1) * 4);
-                    if (box.x <= x0 + 7.0f && box.y >= x0 && box.z <= y0 + 3.0f && box.w >= y0) mask |= 1u << w;
-                }
-            }
-#pragma unroll
-            for (int w = 0; w < 8; ++w) {
-                const uint32_t bal = __ballot_sync(0xffffffffu, (mask >> w) & 1u);
-                if (lane == 0) s_bal[w][wid] = bal;
-            }
+        // which entries to visit: the forward recorded, per warp block, the entries that blended into some pixel of the
+        // block (surfel_render_fwd.cu); everything else contributes nothing here either
+        if (tid < 64) {
+            const int w = tid >> 3, v = tid & 7;
+            s_bal[w][v] = (r * BATCH + v * 32 < total) ? __ldg(my_contrib + (size_t)(r * 8 + v) * 8 + w) : 0u;
         }
         __syncthreads();
 
@@ -299,7 +289,8 @@ cudaError_t launch_surfel_render_backward(int W, int H, int gx, int gy, const Su
     if (e != cudaSuccess) return e;
     surfel_render_backward_kernel<<<gx * gy, 256, SURFEL_SMEM_B, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                                       img.n_contrib, img.median_contrib, img.final_T,
-                                                                      img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(0));
+                                                                      img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(0),
+                                                                      reinterpret_cast<const uint32_t*>(bin.contrib));
     return cudaGetLastError();
 }
 

@@ -18,7 +18,7 @@ surfel_render_forward_kernel(int W, int H, int gx,
                              const SurfelRec* __restrict__ recs, const float* __restrict__ bg,
                              uint32_t* __restrict__ n_contrib, uint32_t* __restrict__ median_contrib,
                              float* __restrict__ final_T, float* __restrict__ out_M1, float* __restrict__ out_M2,
-                             float* __restrict__ out_color, float* __restrict__ out_others) {
+                             float* __restrict__ out_color, float* __restrict__ out_others, uint32_t* __restrict__ contrib) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SurfelRec (*s_rec)[BATCH] = reinterpret_cast<SurfelRec (*)[BATCH]>(smem_raw);
     uint32_t (*s_bal)[8] = reinterpret_cast<uint32_t (*)[8]>(smem_raw + 2 * BATCH * sizeof(SurfelRec));
@@ -35,6 +35,9 @@ surfel_render_forward_kernel(int W, int H, int gx,
     const uint2 range = ranges[tile];
     const int total = (int)(range.y - range.x);
     const int rounds = (total + BATCH - 1) / BATCH;
+    // contribution words of this warp block for the backward (zero-initialised by the caller): bit = list entry that
+    // blended into some pixel of the block, i.e. exactly the (warp block, entry) visits the backward has work for
+    uint32_t* my_contrib = contrib + contrib_base(range.x, tile) * 8 + wid;
 
     float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f;
     float N0 = 0.f, N1 = 0.f, N2 = 0.f, D = 0.f, M1 = 0.f, M2 = 0.f, distortion = 0.f, median_depth = 0.f;
@@ -82,9 +85,12 @@ surfel_render_forward_kernel(int W, int H, int gx,
         if (!__all_sync(0xffffffffu, done)) {
             for (int v = 0; v < 8; ++v) {
                 uint32_t bits = s_bal[wid][v];
+                uint32_t took_bits = 0;           // per lane; OR-reduced over the warp after the word
                 while (bits) {
                     const int j = v * 32 + __ffs(bits) - 1;
-                    bits &= bits - 1;
+                    const uint32_t rest = bits & (bits - 1);
+                    const uint32_t bit = bits ^ rest;
+                    bits = rest;
                     if (done) continue;
                     const float4* q = reinterpret_cast<const float4*>(&buf[j]);
                     const float4 q0 = q[0], q1 = q[1], q2 = q[2];
@@ -124,7 +130,10 @@ surfel_render_forward_kernel(int W, int H, int gx,
                     C0 += q3.w * w; C1 += q4.x * w; C2 += q4.y * w;
                     T = test_T;
                     last_contributor = contributor;
+                    took_bits |= bit;
                 }
+                took_bits = __reduce_or_sync(0xffffffffu, took_bits);
+                if (lane == 0 && took_bits) my_contrib[(size_t)(r * 8 + v) * 8] = took_bits;
                 if (__all_sync(0xffffffffu, done)) break;
             }
         }
@@ -162,7 +171,8 @@ cudaError_t launch_surfel_render_forward(int W, int H, int gx, int gy, const Sur
     }
     surfel_render_forward_kernel<<<gx * gy, 256, SURFEL_SMEM, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                                     img.n_contrib, img.median_contrib, img.final_T, img.M1,
-                                                                    img.M2, out_color, out_others);
+                                                                    img.M2, out_color, out_others,
+                                                                    reinterpret_cast<uint32_t*>(bin.contrib));
     return cudaGetLastError();
 }
 
