@@ -43,7 +43,7 @@ __device__ __forceinline__ void bfly_owner18(int lane, int& slot, bool& writer) 
     slot = idx;
 }
 
-__global__ void __launch_bounds__(256, 3)      // 80 registers: 3 CTAs/SM; measured 2.29 -> 1.97 ms at C4 (4 CTAs/SM spills: 2.60)
+__global__ void __launch_bounds__(256, 3)      // 80 registers, 48 B of spill: 3 CTAs/SM. Measured at C4: 2 CTAs/SM (105 registers, no spill) 1.63 ms, 3 CTAs/SM 1.50 ms, 4 CTAs/SM 2.60 ms (round 1)
 surfel_render_backward_kernel(int W, int H, int gx,
                               const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order, const uint32_t* __restrict__ point_list,
                               const SurfelRec* __restrict__ recs, const float* __restrict__ bg,
