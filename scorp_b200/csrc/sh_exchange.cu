@@ -163,19 +163,31 @@ sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ m
     if (g < P) {
         if (head) head_row_to_planar(head, head_dst, P, g, surfel);
         const V3 m = ld3(means3D + 3 * (size_t)g);
-        for (int v = 0; v < n_views; ++v) {
-            const V3 d = ld3(drgb + ((size_t)v * P + g) * 3);
-            if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) continue;      // not visible in view v (or fully clamped)
-            const V3 dir = { m.x - __ldg(campos + 3 * v), m.y - __ldg(campos + 3 * v + 1), m.z - __ldg(campos + 3 * v + 2) };
-            const float inv_len = 1.0f / sqrtf(dot(dir, dir));
-            float basis[16];
-            const int used = sh_basis(D, dir.x * inv_len, dir.y * inv_len, dir.z * inv_len, basis);
+        // views in batches of four: the batch's colour gradients are loaded before any arithmetic, so four independent
+        // loads are in flight per thread instead of one (the loop was latency-bound: 9 us per extra view at 1 M Gaussians)
+        for (int v0 = 0; v0 < n_views; v0 += 4) {
+            V3 dv[4];
 #pragma unroll
-            for (int k = 0; k < M; ++k) {
-                if (k < used) {
-                    acc[3 * k] = fmaf(basis[k], d.x, acc[3 * k]);
-                    acc[3 * k + 1] = fmaf(basis[k], d.y, acc[3 * k + 1]);
-                    acc[3 * k + 2] = fmaf(basis[k], d.z, acc[3 * k + 2]);
+            for (int u = 0; u < 4; ++u) {
+                const int v = v0 + u;
+                dv[u] = (v < n_views) ? ld3(drgb + ((size_t)v * P + g) * 3) : V3{0.0f, 0.0f, 0.0f};
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const V3 d = dv[u];
+                if (d.x == 0.0f && d.y == 0.0f && d.z == 0.0f) continue;      // not visible in that view (or fully clamped)
+                const int v = v0 + u;
+                const V3 dir = { m.x - __ldg(campos + 3 * v), m.y - __ldg(campos + 3 * v + 1), m.z - __ldg(campos + 3 * v + 2) };
+                const float inv_len = 1.0f / sqrtf(dot(dir, dir));
+                float basis[16];
+                const int used = sh_basis(D, dir.x * inv_len, dir.y * inv_len, dir.z * inv_len, basis);
+#pragma unroll
+                for (int k = 0; k < M; ++k) {
+                    if (k < used) {
+                        acc[3 * k] = fmaf(basis[k], d.x, acc[3 * k]);
+                        acc[3 * k + 1] = fmaf(basis[k], d.y, acc[3 * k + 1]);
+                        acc[3 * k + 2] = fmaf(basis[k], d.z, acc[3 * k + 2]);
+                    }
                 }
             }
         }
