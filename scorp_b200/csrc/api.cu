@@ -31,6 +31,7 @@ int stage_check(const GsrSettings* s, cudaStream_t st, const char* what) {
 constexpr int PROF_RING = 64, PROF_EV = 7;
 struct StageProf {
     bool on = false, made = false;
+    int device = -1;                          // device the events were created on
     int n_fwd = 0, n_bwd = 0;                 // passes recorded since enable (ring of PROF_RING)
     cudaEvent_t ev[PROF_RING][PROF_EV] = {};
 };
@@ -51,7 +52,15 @@ void prof_mark(int i, cudaStream_t st) {
     static const char* const kNext[PROF_EV] = { "gsr:preprocess", "gsr:binning", "gsr:blend_forward", nullptr,
                                                 "gsr:blend_backward", "gsr:preprocess_backward", nullptr };
     nvtx_stage(kNext[i]);
-    if (!g_prof.made) { for (auto& r : g_prof.ev) for (auto& e : r) cudaEventCreate(&e); g_prof.made = true; }
+    // the events belong to the device that is current when profiling is first used; a later call on another device
+    // re-creates them there (profiling is a single-device diagnostic: bench.py enables it on the rank's own GPU)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (g_prof.made && dev != g_prof.device) {
+        for (auto& r : g_prof.ev) for (auto& e : r) cudaEventDestroy(e);
+        g_prof.made = false; g_prof.n_fwd = g_prof.n_bwd = 0;
+    }
+    if (!g_prof.made) { for (auto& r : g_prof.ev) for (auto& e : r) cudaEventCreate(&e); g_prof.made = true; g_prof.device = dev; }
     const int slot = (i < 4 ? g_prof.n_fwd : g_prof.n_bwd) % PROF_RING;
     cudaEventRecord(g_prof.ev[slot][i], st);
     if (i == 3) ++g_prof.n_fwd;

@@ -87,8 +87,13 @@ clamped_rgb_push_mc_kernel(int P, const int32_t* __restrict__ radii, const uint8
 
 cudaError_t launch_clamped_rgb_push(int P, const int32_t* radii, const uint8_t* clamped, const float* acc, int stride,
                                     int rgb_off, const PeerDst& dst, cudaStream_t main) {
-    static thread_local cudaEvent_t ev = nullptr;
+    // one event per (host thread, device): an event belongs to the device that was current when it was created
+    static thread_local cudaEvent_t evs[64] = {};
     cudaError_t e;
+    int dev = 0;
+    if ((e = cudaGetDevice(&dev)) != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    cudaEvent_t& ev = evs[dev];
     if (!ev && (e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming)) != cudaSuccess) return e;
     if ((e = cudaEventRecord(ev, main)) != cudaSuccess) return e;
     if ((e = cudaStreamWaitEvent(dst.side, ev, 0)) != cudaSuccess) return e;

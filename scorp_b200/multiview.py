@@ -200,7 +200,7 @@ class PeerExchange(FactoredExchange):
     # row ranges the preprocess-backward kernel is split into for the pipelined head reduce (GSR_PEER_CHUNKS overrides).
     # Measured at C2 on 2 GPUs (profiles/r02_mg2_chunks.md): 1 range 1.750 ms/step, 2 ranges 1.743, 4 ranges 1.792 -- what
     # the pipelining takes off the tail mostly comes back as a slower preprocess-backward stage; at 8 GPUs 1 range 1.925,
-    # 2 ranges 1.853 (profiles/r02_mg8_chunks.md). Default: 2.
+    # 2 ranges 1.853 (profiles/r02_mg2_chunks.md, last lines). Default: 2.
     CHUNKS = int(os.environ.get("GSR_PEER_CHUNKS", "2"))
 
     def stage_ms(self):
