@@ -397,18 +397,21 @@ tile_sort_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const u
     }
 }
 
-// ---- 4b. per-tile LSD radix sort (segments of more than RADIX_MIN entries) ------------------------------------------
+// ---- 4b. per-tile radix sort (segments of more than RADIX_MIN entries) ----------------------------------------------
 // The 64-bit keys of a segment are unique (depth bits << 32 | Gaussian index) and the reference's order is (depth bits,
-// index). Sorting on the 32 depth bits alone takes four 8-bit passes instead of the ~log^2(n)/2 compare-exchange steps of
-// the network above; the index rides along as the payload. The segment arrives in arbitrary order (scatter_kernel's
-// cursor is an atomic), so stability cannot deliver the index order of equal depths: a last step ranks every run of
-// equal depth bits by index (runs are short: cloned Gaussians share a depth, nothing else does).
+// index); the segment arrives in arbitrary order (scatter_kernel's cursor is an atomic).
 //
-// One pass, CTA of W warps, every warp owns 32*K consecutive positions (K rounds of 32): per round the lanes holding the
-// same digit find each other with match.any; the lowest of them reads-and-bumps the warp's counter of that digit, so a
-// key's rank among the SAME-digit keys of its warp is (counter before) + (same-digit lanes below it) -- stable. A scan
-// over (digit, warp) turns the counters into destinations.
+// A stable 8-bit pass ranks with match.any (same-digit lanes of a warp find each other; a warp-private counter per digit
+// makes the rank stable) -- and match.any is what binds: ncu shows the ADU pipe at 71 % with the issue slots at 31 % when
+// all 32 depth bits are sorted that way in four passes (profiles/r02_ncu_C3_kernels.md). So the sort is done on a 16-bit
+// key instead: u = floor((depth - dmin) * 65535 / (dmax - dmin)), a monotone map of the depth over the TILE's own depth
+// range (clustered depths still spread over the 65536 values). LSD needs stability only from the second pass on, so the
+// low byte is ranked with plain shared-memory atomics and only the high byte with match.any: one match pass, not four.
+// A last step puts every run of equal u in (depth bits, index) order by counting inside the run (runs are a few entries
+// long). A tile whose entries all share one depth, or that holds a run longer than RUN_MAX, is sorted by the full
+// four-pass sort on the depth bits (followed by the same ranking step, which then orders equal depths by index).
 constexpr int RADIX_K = 8;                     // positions per thread
+constexpr int RUN_MAX = 48;
 template <int THREADS> struct RadixSmem {
     static constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
     uint2 a[CAP], b[CAP];                      // .x = Gaussian index, .y = depth bits
@@ -416,106 +419,201 @@ template <int THREADS> struct RadixSmem {
     uint32_t base[256];
     uint32_t total[256];
     uint32_t skip[4];                          // per pass: every key has the same digit (the pass is the identity)
+    uint32_t dmin, dmax, long_run;
 };
+// exclusive scan of sm.total[256] -> sm.base[256], by warp 0 (8 digits per lane)
+template <int THREADS>
+__device__ __forceinline__ void radix_scan_totals(RadixSmem<THREADS>& sm, int lane, int w) {
+    if (w == 0) {
+        uint32_t t[8], sum = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { t[e] = sm.total[lane * 8 + e]; sum += t[e]; }
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+        uint32_t run = incl - sum;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { sm.base[lane * 8 + e] = run; run += t[e]; }
+    }
+}
+// One STABLE pass on digit(key) from src to dst. Entered and left with the CTA in step (barrier inside and at the end).
+// Returns false when every key had the same digit (nothing was moved).
+template <int THREADS, class Digit>
+__device__ __forceinline__ bool radix_pass_stable(RadixSmem<THREADS>& sm, const uint2* src, uint2* dst, int L, int pass, Digit digit) {
+    constexpr int W = THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    const int p0 = w * 32 * RADIX_K + lane;      // this thread's position in round 0
+    for (int i = tid; i < W * 128; i += THREADS) reinterpret_cast<uint32_t*>(&sm.cnt[0][0])[i] = 0u;
+    __syncthreads();                            // counters cleared; src complete
+    uint2 key[RADIX_K];
+    uint32_t rank[RADIX_K];
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = p0 + r * 32;
+        if (p - lane >= L) { rank[r] = 0; key[r] = make_uint2(0u, 0u); continue; }      // warp-uniform: nothing left for this warp
+        const bool valid = p < L;
+        if (valid) key[r] = src[p];
+        const uint32_t dig = valid ? digit(key[r]) : 256u;
+        const uint32_t peers = __match_any_sync(0xffffffffu, dig);
+        const int leader = __ffs(peers) - 1;
+        uint32_t prior = 0;
+        if (lane == leader && valid) {
+            prior = sm.cnt[w][dig];
+            sm.cnt[w][dig] = (uint16_t)(prior + __popc(peers));
+        }
+        prior = __shfl_sync(0xffffffffu, prior, leader);
+        rank[r] = prior + __popc(peers & lt);
+        __syncwarp();                            // the next round reads the counters this one wrote
+    }
+    __syncthreads();
+    // counters -> exclusive prefix over the warps, per digit; totals per digit
+    for (int d = tid; d < 256; d += THREADS) {
+        uint32_t run = 0;
+#pragma unroll 4
+        for (int ww = 0; ww < W; ++ww) { const uint32_t c = sm.cnt[ww][d]; sm.cnt[ww][d] = (uint16_t)run; run += c; }
+        sm.total[d] = run;
+        if (run == (uint32_t)L) sm.skip[pass] = 1u;
+    }
+    __syncthreads();
+    if (sm.skip[pass]) return false;             // CTA-uniform; nobody reads the counters any more
+    radix_scan_totals<THREADS>(sm, lane, w);
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = p0 + r * 32;
+        if (p < L) {
+            const uint32_t dig = digit(key[r]);
+            dst[sm.base[dig] + sm.cnt[w][dig] + rank[r]] = key[r];
+        }
+    }
+    __syncthreads();                             // scatter done: counters and bases may be overwritten, dst is complete
+    return true;
+}
+// One pass on digit(key) whose order inside a digit is arbitrary (first pass of an LSD sort): slots from shared atomics.
+template <int THREADS, class Digit>
+__device__ __forceinline__ void radix_pass_unstable(RadixSmem<THREADS>& sm, const uint2* src, uint2* dst, int L, Digit digit) {
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    for (int d = tid; d < 256; d += THREADS) sm.total[d] = 0u;
+    __syncthreads();
+    uint2 key[RADIX_K];
+    uint32_t slot[RADIX_K];
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = tid + r * THREADS;         // any assignment of positions to threads will do here
+        slot[r] = 0;
+        if (p < L) { key[r] = src[p]; slot[r] = atomicAdd(&sm.total[digit(key[r])], 1u); }
+    }
+    __syncthreads();
+    radix_scan_totals<THREADS>(sm, lane, w);
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = tid + r * THREADS;
+        if (p < L) dst[sm.base[digit(key[r])] + slot[r]] = key[r];
+    }
+    __syncthreads();
+}
 template <int THREADS>
 __device__ __forceinline__ void tile_radix_one(RadixSmem<THREADS>& sm, int tile, int lo_len, const uint2* __restrict__ ranges,
                                                const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
                                                uint64_t* __restrict__ point_list_keys) {
-    constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
+    constexpr int CAP = THREADS * RADIX_K;
     const uint2 rg = ranges[tile];
     const int L = (int)(rg.y - rg.x);
     if (L <= lo_len || L > CAP) return;         // CTA-uniform
-    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int tid = threadIdx.x;
     const uint64_t* seg = keys + rg.x;
-    for (int p = tid; p < L; p += THREADS) {
-        const uint64_t k = seg[p];
-        sm.a[p] = make_uint2((uint32_t)k, (uint32_t)(k >> 32));
+    if (tid < 4) sm.skip[tid] = 0u;
+    if (tid == 0) { sm.dmin = 0xffffffffu; sm.dmax = 0u; sm.long_run = 0u; }
+    __syncthreads();
+    {   // load; depth range of the tile (depths are positive floats: their bit patterns order like the values)
+        uint32_t lo = 0xffffffffu, hi = 0u;
+        for (int p = tid; p < L; p += THREADS) {
+            const uint64_t k = seg[p];
+            const uint32_t d = (uint32_t)(k >> 32);
+            sm.a[p] = make_uint2((uint32_t)k, d);
+            lo = min(lo, d); hi = max(hi, d);
+        }
+        lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+        if ((tid & 31) == 0) { atomicMin(&sm.dmin, lo); atomicMax(&sm.dmax, hi); }
     }
+    __syncthreads();
+    const uint32_t dmin_b = sm.dmin, dmax_b = sm.dmax;
+    const float dmin = __uint_as_float(dmin_b);
+    const float scale = __fdividef(65535.0f, __uint_as_float(dmax_b) - dmin);
+    auto mapped = [&](const uint2& k) { return min(65535u, (uint32_t)(__fsub_rn(__uint_as_float(k.y), dmin) * scale)); };
     uint2* src = sm.a;
     uint2* dst = sm.b;
-    const uint32_t lt = (1u << lane) - 1u;
-    const int p0 = w * 32 * RADIX_K + lane;      // this thread's position in round 0
-    if (tid < 4) sm.skip[tid] = 0u;
-#pragma unroll 1
-    for (int shift = 0; shift < 32; shift += 8) {
-        for (int i = tid; i < W * 128; i += THREADS) reinterpret_cast<uint32_t*>(&sm.cnt[0][0])[i] = 0u;
-        __syncthreads();                        // counters cleared; src complete (load or previous scatter)
-        uint2 key[RADIX_K];
-        uint32_t rank[RADIX_K];
-#pragma unroll
-        for (int r = 0; r < RADIX_K; ++r) {
-            const int p = p0 + r * 32;
-            if (p - lane >= L) { rank[r] = 0; key[r] = make_uint2(0u, 0u); continue; }      // warp-uniform: nothing left for this warp
-            const bool valid = p < L;
-            if (valid) key[r] = src[p];
-            const uint32_t dig = valid ? ((key[r].y >> shift) & 255u) : 256u;
-            // (nine votes instead of one match.any measured 5 % faster at C3 and equal at C2: the instruction is not the limit)
-            const uint32_t peers = __match_any_sync(0xffffffffu, dig);
-            const int leader = __ffs(peers) - 1;
-            uint32_t prior = 0;
-            if (lane == leader && valid) {
-                prior = sm.cnt[w][dig];
-                sm.cnt[w][dig] = (uint16_t)(prior + __popc(peers));
-            }
-            prior = __shfl_sync(0xffffffffu, prior, leader);
-            rank[r] = prior + __popc(peers & lt);
-            __syncwarp();                        // the next round reads the counters this one wrote
-        }
-        __syncthreads();
-        // counters -> exclusive prefix over the warps, per digit; totals per digit
-        for (int d = tid; d < 256; d += THREADS) {
-            uint32_t run = 0;
-#pragma unroll 4
-            for (int ww = 0; ww < W; ++ww) { const uint32_t c = sm.cnt[ww][d]; sm.cnt[ww][d] = (uint16_t)run; run += c; }
-            sm.total[d] = run;
-            if (run == (uint32_t)L) sm.skip[shift >> 3] = 1u;
-        }
-        __syncthreads();
-        if (sm.skip[shift >> 3]) continue;       // CTA-uniform; nobody reads the counters any more
-        if (w == 0) {                            // exclusive scan of the 256 totals: 8 per lane
-            uint32_t t[8], sum = 0;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) { t[e] = sm.total[lane * 8 + e]; sum += t[e]; }
-            uint32_t incl = sum;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
-            uint32_t run = incl - sum;
-#pragma unroll
-            for (int e = 0; e < 8; ++e) { sm.base[lane * 8 + e] = run; run += t[e]; }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int r = 0; r < RADIX_K; ++r) {
-            const int p = p0 + r * 32;
-            if (p < L) {
-                const uint32_t dig = (key[r].y >> shift) & 255u;
-                dst[sm.base[dig] + sm.cnt[w][dig] + rank[r]] = key[r];
-            }
-        }
-        uint2* t = src; src = dst; dst = t;
-        __syncthreads();                         // scatter done: counters and bases may be overwritten, src is complete
+    bool full = (dmin_b == dmax_b);             // one depth for the whole tile: order by index through the full sort
+    if (!full) {
+        radix_pass_unstable<THREADS>(sm, src, dst, L, [&](const uint2& k) { return mapped(k) & 255u; });
+        { uint2* t = src; src = dst; dst = t; }
+        if (radix_pass_stable<THREADS>(sm, src, dst, L, 0, [&](const uint2& k) { return mapped(k) >> 8; })) { uint2* t = src; src = dst; dst = t; }
     }
-    // emit; runs of equal depth bits are put in index order (rank by counting inside the run)
     const uint64_t tile_hi = (uint64_t)tile << 32;
     uint32_t* out_list = point_list + rg.x;
     uint64_t* out_keys = point_list_keys + rg.x;
-    for (int p = tid; p < L; p += THREADS) {
-        const uint2 k = src[p];
-        int at = p;
-        const bool tie = (p > 0 && src[p - 1].y == k.y) || (p + 1 < L && src[p + 1].y == k.y);
-        if (tie) {
-            int s0 = p;
-            while (s0 > 0 && src[s0 - 1].y == k.y) --s0;
-            int below = 0;
-            for (int q = s0; q < L && src[q].y == k.y; ++q) below += src[q].x < k.x;
-            at = s0 + below;
+    for (int attempt = 0; attempt < 2; ++attempt) {
+        if (full) {
+            // four stable 8-bit passes on the depth bits, from the segment as it arrived
+            if (attempt) {
+                for (int p = tid; p < L; p += THREADS) { const uint64_t k = seg[p]; sm.a[p] = make_uint2((uint32_t)k, (uint32_t)(k >> 32)); }
+                if (tid < 4) sm.skip[tid] = 0u;
+                src = sm.a; dst = sm.b;
+                __syncthreads();
+            }
+#pragma unroll 1
+            for (int pass = 0; pass < 4; ++pass) {
+                const int shift = 8 * pass;
+                if (radix_pass_stable<THREADS>(sm, src, dst, L, pass, [&](const uint2& k) { return (k.y >> shift) & 255u; })) {
+                    uint2* t = src; src = dst; dst = t;
+                }
+            }
         }
-        out_list[at] = k.x;
-        out_keys[at] = tile_hi | k.y;
+        // final positions: runs of equal sort key are put in (depth bits, index) order by counting inside the run
+        int at[RADIX_K];
+        bool too_long = false;
+#pragma unroll
+        for (int r = 0; r < RADIX_K; ++r) {
+            const int p = tid + r * THREADS;
+            at[r] = p;
+            if (p >= L) continue;
+            const uint2 k = src[p];
+            const uint32_t mine = full ? k.y : mapped(k);
+            auto same = [&](int q) { const uint2 o = src[q]; return (full ? o.y : mapped(o)) == mine; };
+            if ((p > 0 && same(p - 1)) || (p + 1 < L && same(p + 1))) {
+                // (the mapped sort gives up on a run of more than ~RUN_MAX entries; exact ties of the full sort may be as
+                // long as the list -- a whole plane at one depth -- and are counted to the end)
+                int s0 = p, n = 0, below = 0;
+                bool give_up = false;
+                while (s0 > 0 && same(s0 - 1)) { --s0; if (!full && ++n > RUN_MAX) { give_up = true; break; } }
+                if (!give_up) {
+                    for (int q = s0; q < L && same(q); ++q) {
+                        const uint2 o = src[q];
+                        below += (o.y < k.y) || (o.y == k.y && o.x < k.x);
+                        if (!full && ++n > 2 * RUN_MAX) { give_up = true; break; }
+                    }
+                }
+                too_long = too_long || give_up;
+                at[r] = s0 + below;
+            }
+        }
+        if (!full) {
+            if (too_long) sm.long_run = 1u;
+            __syncthreads();
+            if (sm.long_run) { full = true; continue; }            // CTA-uniform: redo this tile with the full sort
+        }
+#pragma unroll
+        for (int r = 0; r < RADIX_K; ++r) {
+            const int p = tid + r * THREADS;
+            if (p < L) { const uint2 k = src[p]; out_list[at[r]] = k.x; out_keys[at[r]] = tile_hi | k.y; }
+        }
+        break;
     }
 }
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, THREADS <= 512 ? 1024 / THREADS : 1)      // at most 64 registers
 tile_radix_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
                   uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
     extern __shared__ __align__(16) unsigned char radix_smem[];
@@ -523,7 +621,7 @@ tile_radix_kernel(int lo_len, const uint2* __restrict__ ranges, const uint64_t* 
                             point_list_keys);
 }
 template <int THREADS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, THREADS <= 512 ? 1024 / THREADS : 1)
 tile_radix_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const uint32_t* __restrict__ order,
                          const uint2* __restrict__ ranges, const uint64_t* __restrict__ keys,
                          uint32_t* __restrict__ point_list, uint64_t* __restrict__ point_list_keys) {
@@ -646,10 +744,11 @@ cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* range
 }
 
 // Shorter segments than this go through the network instead of the radix sort (tunable: GSR_RADIX_MIN; a value >= 1024
-// sends the whole small class through the network). Measured on B200: see DESIGN.md 5.
+// sends the whole small class through the network). Measured on B200, binning stage at C2: 1024 -> 0.200 ms, 512 -> 0.154,
+// 256 -> 0.153, 128 -> 0.152, 64 -> 0.153; at C1: 512 -> 0.064, 256 -> 0.060.
 static int radix_min() {
     static int v = -1;
-    if (v < 0) { const char* e = getenv("GSR_RADIX_MIN"); v = e ? atoi(e) : 512; if (v < 8) v = 8; if (v > SORT_S_CAP) v = SORT_S_CAP; }
+    if (v < 0) { const char* e = getenv("GSR_RADIX_MIN"); v = e ? atoi(e) : 256; if (v < 8) v = 8; if (v > SORT_S_CAP) v = SORT_S_CAP; }
     return v;
 }
 static size_t small_smem_bytes() {
