@@ -39,7 +39,7 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
     uint32_t longest = 0;
     for (int base = 0; base < tiles; base += 1024) {
         const int t = base + threadIdx.x;
-        const uint32_t c = (t < tiles) ? count[t] : 0u;
+        const uint32_t c = (t < tiles) ? count[tc(t)] : 0u;
         longest = max(longest, c);
         if (t < tiles) atomicAdd(&bins[order_bin(c)], 1u);
         uint32_t v = c;
@@ -91,7 +91,7 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
             counters[4] = overflow ? 0u : bins[ORDER_BINS - 2];
         }
         __syncthreads();
-        for (int t = threadIdx.x; t < tiles; t += 1024) order[atomicAdd(&bins[order_bin(count[t])], 1u)] = (uint32_t)t;
+        for (int t = threadIdx.x; t < tiles; t += 1024) order[atomicAdd(&bins[order_bin(count[tc(t)])], 1u)] = (uint32_t)t;
     }
 }
 
@@ -129,7 +129,7 @@ scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ rec
         }
     }
     auto put = [&](uint32_t t, uint64_t k) {
-        const uint32_t slot = atomicSub(tile_count + t, 1u) - 1u;
+        const uint32_t slot = atomicSub(tile_count + tc(t), 1u) - 1u;
         keys[ranges[t].x + slot] = k;
     };
     if (cnt > 0 && cnt <= SMALL_RECT) {
@@ -139,7 +139,7 @@ scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ rec
         for (uint32_t i = 0; i < SMALL_RECT; ++i) {
             if (i < cnt) {
                 t[i] = tbase + (y0 + i / w) * gx + x0 + i % w;
-                at[i] = __ldg(&ranges[t[i]].x) + atomicSub(tile_count + t[i], 1u) - 1u;
+                at[i] = __ldg(&ranges[t[i]].x) + atomicSub(tile_count + tc(t[i]), 1u) - 1u;
             }
         }
 #pragma unroll
@@ -213,8 +213,8 @@ views_histogram_kernel(int per_view, int gx, int gy, const char* __restrict__ re
         warp_rect_foreach(gx, x0, y0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(&s_cnt[t], 1u); });
     }
     __syncthreads();
-    uint32_t* out = tile_count + (size_t)view * tiles;
-    for (int t = threadIdx.x; t < tiles; t += 256) { const uint32_t c = s_cnt[t]; if (c) atomicAdd(out + t, c); }
+    uint32_t* out = tile_count + tc((size_t)view * tiles);
+    for (int t = threadIdx.x; t < tiles; t += 256) { const uint32_t c = s_cnt[t]; if (c) atomicAdd(out + tc(t), c); }
 }
 __global__ void __launch_bounds__(256)
 views_scatter_kernel(int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
@@ -238,7 +238,7 @@ views_scatter_kernel(int per_view, int gx, int gy, const char* __restrict__ recs
     const size_t vt = (size_t)view * tiles;
     for (int t = threadIdx.x; t < tiles; t += 256) {
         const uint32_t c = s_cnt[t];
-        if (c) s_base[t] = ranges[vt + t].x + atomicSub(tile_count + vt + t, c) - c;
+        if (c) s_base[t] = ranges[vt + t].x + atomicSub(tile_count + tc(vt + t), c) - c;
         s_cnt[t] = 0u;
     }
     __syncthreads();

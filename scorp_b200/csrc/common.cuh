@@ -17,6 +17,13 @@ namespace gsr {
 constexpr int TILE = 16;            // BLOCK_X == BLOCK_Y == 16 (config.h:16-17)
 constexpr int TILE_PIX = TILE * TILE;
 constexpr int BATCH = 256;          // Gaussians staged per round (== BLOCK_SIZE in the reference)
+// Per-tile instance counters (histogram in preprocess, cursor in scatter) sit TC_STRIDE words apart, one per 32-byte
+// sector: packed 4 bytes apart, the counters of a whole view share a few hundred cache lines, and atomics to one line
+// serialise in L2. Measured on B200 (binning stage, C3 / C2 / C1): packed 0.919 / 0.153 / 0.060 ms, one per 32-byte sector
+// 0.850 / 0.140 / 0.054 ms, one per 128-byte line 0.867 / 0.145 / 0.055 ms; preprocess (histogram atomics) gains too
+// (C1: 0.020 -> 0.013 ms). Index with tc(tile).
+constexpr int TC_STRIDE = 8;
+__host__ __device__ inline size_t tc(size_t tile) { return tile * TC_STRIDE; }
 constexpr int GEOM_COUNTERS = 8;    // uint32 slots in GeomState::counters / SurfelGeom::counters (binning.cu: tile_scan_kernel)
 
 // Per-Gaussian render record, 48 bytes, 16-byte aligned: what the blend kernels stage.
@@ -65,7 +72,7 @@ inline size_t carve_geom(char* base, int P, int tiles, GeomState* g, size_t* off
     size_t a1 = take((size_t)P * 6 * sizeof(float));
     size_t a2 = take((size_t)P);
     size_t a3 = take((size_t)P * 4);
-    size_t a4 = take((size_t)tiles * 4);
+    size_t a4 = take((size_t)tiles * 4 * TC_STRIDE);
     size_t a5 = take(GEOM_COUNTERS * 4);
     if (g) {
         g->rec = (GaussRec*)(base + a0); g->cov3D = (float*)(base + a1);
@@ -214,7 +221,7 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx
 constexpr uint32_t HIST_SMALL = 4;
 __device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uint32_t x0, uint32_t y0, uint32_t w, uint32_t cnt) {
     if (cnt > 0 && cnt <= HIST_SMALL) {
-        for (uint32_t i = 0; i < cnt; ++i) atomicAdd(tile_count + (y0 + i / w) * gx + x0 + i % w, 1u);
+        for (uint32_t i = 0; i < cnt; ++i) atomicAdd(tile_count + tc((y0 + i / w) * gx + x0 + i % w), 1u);
     }
     uint32_t big = __ballot_sync(0xffffffffu, cnt > HIST_SMALL);
     const uint32_t lane = threadIdx.x & 31;
@@ -223,7 +230,7 @@ __device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uin
         big &= big - 1;
         const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
         const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
-        for (uint32_t i = lane; i < bcnt; i += 32) atomicAdd(tile_count + (by0 + i / bw) * gx + bx0 + i % bw, 1u);
+        for (uint32_t i = lane; i < bcnt; i += 32) atomicAdd(tile_count + tc((by0 + i / bw) * gx + bx0 + i % bw), 1u);
     }
 }
 

@@ -81,7 +81,7 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     if (view_id) {
         a.view += 16 * view_id; a.proj += 16 * view_id; a.campos += 3 * view_id;
         g.rec += (size_t)view_id * a.P; g.clamped += (size_t)view_id * a.P; g.tiles_touched += (size_t)view_id * a.P;
-        g.tile_count += (size_t)view_id * a.gx * a.gy;
+        g.tile_count += tc((size_t)view_id * a.gx * a.gy);
         radii += (size_t)view_id * a.P;
     }
     uint32_t tiles = 0, rx0 = 0, ry0 = 0, rw = 0;

@@ -48,7 +48,7 @@ inline size_t carve_surfel_geom(char* base, int P, int tiles, SurfelGeom* g, siz
     size_t a0 = take((size_t)P * sizeof(SurfelRec));
     size_t a1 = take((size_t)P);
     size_t a2 = take((size_t)P * 4);
-    size_t a3 = take((size_t)tiles * 4);
+    size_t a3 = take((size_t)tiles * 4 * TC_STRIDE);
     size_t a4 = take(GEOM_COUNTERS * 4);
     if (off) off[5] = o;
     if (g) {
