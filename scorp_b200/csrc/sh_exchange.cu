@@ -10,6 +10,7 @@
 // With n views in flight the exchange per Gaussian is 12 n bytes instead of 192 (M = 16): worth it up to ~8-12
 // views per step; scorp_b200/multiview.py picks. The backward is then called with dL_dsh = NULL and does not
 // write the SH rows at all.
+#include <cstdlib>
 #include "sh.cuh"
 #include "surfel.cuh"
 
@@ -267,7 +268,9 @@ extern "C" int gsr_peer_reduce_shard(float* multicast_head, int row0, int rows, 
     const size_t want = (q1 - q0 + 256 * U - 1) / (256 * U);
     // grid-stride, one CTA of 256 threads per SM, 8 groups per thread: 4.8 MB in flight (the link's bandwidth x the
     // round trip through the switch), and a footprint small enough to co-reside with the kernel it is pipelined with
-    const int blocks = (int)(want < 148 ? want : 148);
+    static int cap = -1;             // CTAs (tunable for the measurement in profiles/: GSR_REDUCE_BLOCKS)
+    if (cap < 0) { const char* e = getenv("GSR_REDUCE_BLOCKS"); cap = e ? atoi(e) : 148; if (cap < 1) cap = 148; }
+    const int blocks = (int)(want < (size_t)cap ? want : (size_t)cap);
     peer_reduce_shard_kernel<U><<<blocks, 256, 0, (cudaStream_t)stream>>>(reinterpret_cast<float4*>(multicast_head), q0, q1);
     return check_cuda(cudaGetLastError(), "peer head reduce launch");
 }
