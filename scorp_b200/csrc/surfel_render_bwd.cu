@@ -100,11 +100,13 @@ surfel_render_backward_kernel(int W, int H, int gx,
     if (max_contrib == 0 || total == 0) return;
     const uint32_t warp_max = s_max[wid];
 
+    // Running state per pixel. The reference carries (last_alpha, last_value, accum_rec) per blended quantity and forms
+    // accum_rec = last_alpha * last_value + (1 - last_alpha) * accum_rec at the NEXT contributor (backward.cu:334-372);
+    // B below is that value formed one step earlier, B <- B + alpha * (value - B): one register per quantity instead of
+    // two plus the shared last_alpha (render_bwd.cu does the same for 3DGS).
     float T = T_final;
-    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;
-    float last_depth = 0.f, accum_depth_rec = 0.f, accum_alpha_rec = 0.f;
-    float ln0 = 0.f, ln1 = 0.f, ln2 = 0.f, anr0 = 0.f, anr1 = 0.f, anr2 = 0.f;
-    float last_dL_dT = 0.f, last_alpha = 0.f;
+    float B0 = 0.f, B1 = 0.f, B2 = 0.f, Bd = 0.f, Ba = 0.f, Bn0 = 0.f, Bn1 = 0.f, Bn2 = 0.f;
+    float last_dL_dT = 0.f;
 
     int slot; bool writer;
     bfly_owner18(lane, slot, writer);
@@ -191,11 +193,12 @@ surfel_render_backward_kernel(int W, int H, int gx,
                     T = T * inv_1ma;
                     const float dchannel_dcolor = alpha * T;
                     float dL_dalpha = 0.0f;
-                    ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0; lc0 = col0; dL_dalpha += (col0 - ar0) * dpix0;
+                    const float e0 = col0 - B0, e1 = col1 - B1, e2 = col2 - B2;
+                    dL_dalpha += e0 * dpix0; B0 += alpha * e0;
                     val[SACC_R] = dchannel_dcolor * dpix0;
-                    ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1; lc1 = col1; dL_dalpha += (col1 - ar1) * dpix1;
+                    dL_dalpha += e1 * dpix1; B1 += alpha * e1;
                     val[SACC_G] = dchannel_dcolor * dpix1;
-                    ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2; lc2 = col2; dL_dalpha += (col2 - ar2) * dpix2;
+                    dL_dalpha += e2 * dpix2; B2 += alpha * e2;
                     val[SACC_B] = dchannel_dcolor * dpix2;
 
                     float dL_dz = 0.0f;
@@ -210,21 +213,19 @@ surfel_render_backward_kernel(int W, int H, int gx,
                     const float dL_dmd = 2.0f * (T * alpha) * (m_d * final_A - final_D) * dL_dreg;
                     dL_dz += dL_dmd * dmd_dd;
 
-                    accum_depth_rec = last_alpha * last_depth + (1.f - last_alpha) * accum_depth_rec;
-                    last_depth = c_d;
-                    dL_dalpha += (c_d - accum_depth_rec) * dL_ddepth;
-                    accum_alpha_rec = last_alpha * 1.0f + (1.f - last_alpha) * accum_alpha_rec;
-                    dL_dalpha += (1 - accum_alpha_rec) * dL_daccum;
+                    const float ed = c_d - Bd, ea = 1.0f - Ba;
+                    dL_dalpha += ed * dL_ddepth; Bd += alpha * ed;
+                    dL_dalpha += ea * dL_daccum; Ba += alpha * ea;
 
-                    anr0 = last_alpha * ln0 + (1.f - last_alpha) * anr0; ln0 = nrm0; dL_dalpha += (nrm0 - anr0) * dn0;
+                    const float n0 = nrm0 - Bn0, n1 = nrm1 - Bn1, n2 = nrm2 - Bn2;
+                    dL_dalpha += n0 * dn0; Bn0 += alpha * n0;
                     val[SACC_NX] = alpha * T * dn0;
-                    anr1 = last_alpha * ln1 + (1.f - last_alpha) * anr1; ln1 = nrm1; dL_dalpha += (nrm1 - anr1) * dn1;
+                    dL_dalpha += n1 * dn1; Bn1 += alpha * n1;
                     val[SACC_NY] = alpha * T * dn1;
-                    anr2 = last_alpha * ln2 + (1.f - last_alpha) * anr2; ln2 = nrm2; dL_dalpha += (nrm2 - anr2) * dn2;
+                    dL_dalpha += n2 * dn2; Bn2 += alpha * n2;
                     val[SACC_NZ] = alpha * T * dn2;
 
                     dL_dalpha *= T;
-                    last_alpha = alpha;
                     dL_dalpha += (-T_final * inv_1ma) * bg_dot_dpixel;
 
                     const float dL_dG = opa * dL_dalpha;
