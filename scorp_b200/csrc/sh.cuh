@@ -239,4 +239,96 @@ __device__ __forceinline__ void sh_tile_store(float* __restrict__ dsh, size_t ro
     }
 }
 
+// ---- 16-byte variant of the staging for M3 == 48 (degree-3 storage, the headline configs) -------------------------
+// The 4-byte tile above spends ~24 instructions per Gaussian-float4 on index arithmetic (ncu, C3: the two copies were
+// 55 % of the kernel's instructions). Here a row is 12 float4 chunks at stride 48 floats and chunk q of row g sits at
+// chunk (q + g) mod 12 of that row: a quarter warp (the unit a 128-bit shared access is served in) reading "its own
+// row, chunk q" then hits 8 different 16-byte bank groups, so both the unit-stride copies and the per-Gaussian
+// accesses are 128-bit and conflict-free. Needs the global rows 16-byte aligned (the launcher checks the bases).
+__device__ __forceinline__ int sh48_chunk(int g, int q) {      // q in [0, 12)
+    int p = q + g % 12;
+    p -= (p >= 12) ? 12 : 0;
+    return g * 12 + p;
+}
+__device__ __forceinline__ void sh48_load_async(const float* __restrict__ shs, size_t row0, int nrows,
+                                                const uint8_t* s_vis, float4* s4) {
+    const float4* src = reinterpret_cast<const float4*>(shs + row0 * 48);
+#pragma unroll 12
+    for (int e = threadIdx.x; e < nrows * 12; e += SH_TILE) {
+        const int g = e / 12, q = e - g * 12;
+        if (s_vis[g]) cp_async16(s4 + sh48_chunk(g, q), src + e);
+    }
+    cp_async_commit();
+}
+__device__ __forceinline__ void sh48_store(float* __restrict__ dsh, size_t row0, int nrows,
+                                           const uint8_t* s_vis, const float4* s4) {
+    float4* dst = reinterpret_cast<float4*>(dsh + row0 * 48);
+#pragma unroll 12
+    for (int e = threadIdx.x; e < nrows * 12; e += SH_TILE) {
+        const int g = e / 12, q = e - g * 12;
+        dst[e] = s_vis[g] ? s4[sh48_chunk(g, q)] : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+}
+// sh_backward on one row of that tile, in place. Same mathematics, organised per stored float j = 3k + channel so that
+// a chunk is read once, used and overwritten with its gradients: d RGB_c / d(x,y,z) accumulate w{x,y,z}[k] * sh[j].
+__device__ __forceinline__ V3 sh48_backward(int D, float4* row4, int g, V3 pos, V3 campos, V3 dRGB) {
+    const V3 dir_orig = { pos.x - campos.x, pos.y - campos.y, pos.z - campos.z };
+    const float inv_len = 1.0f / sqrtf(dot(dir_orig, dir_orig));
+    const float x = dir_orig.x * inv_len, y = dir_orig.y * inv_len, z = dir_orig.z * inv_len;
+    const float C1 = 0.4886025119029199f;
+    const float C2[5] = { 1.0925484305920792f, -1.0925484305920792f, 0.31539156525252005f, -1.0925484305920792f, 0.5462742152960396f };
+    const float C3[7] = { -0.5900435899266435f, 2.890611442640554f, -0.4570457994644658f, 0.3731763325901154f,
+                          -0.4570457994644658f, 1.445305721320277f, -0.5900435899266435f };
+    float basis[16];
+    const int used = sh_basis(D, x, y, z, basis);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) basis[k] = (k < used) ? basis[k] : 0.0f;
+    const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+    const float d1 = D > 0 ? 1.f : 0.f, d2 = D > 1 ? 1.f : 0.f, d3 = D > 2 ? 1.f : 0.f;
+    // weights of coefficient k in dRGB/dx, /dy, /dz (backward.cu:58-127); entries that are identically zero are skipped
+    const float wx[16] = { 0.f, 0.f, 0.f, -C1 * d1,
+                           d2 * C2[0] * y, 0.f, d2 * C2[2] * 2.f * -x, d2 * C2[3] * z, d2 * C2[4] * 2.f * x,
+                           d3 * C3[0] * 3.f * 2.f * xy, d3 * C3[1] * yz, d3 * C3[2] * -2.f * xy, d3 * C3[3] * -3.f * 2.f * xz,
+                           d3 * C3[4] * (-3.f * xx + 4.f * zz - yy), d3 * C3[5] * 2.f * xz, d3 * C3[6] * 3.f * (xx - yy) };
+    const float wy[16] = { 0.f, -C1 * d1, 0.f, 0.f,
+                           d2 * C2[0] * x, d2 * C2[1] * z, d2 * C2[2] * 2.f * -y, 0.f, d2 * C2[4] * 2.f * -y,
+                           d3 * C3[0] * 3.f * (xx - yy), d3 * C3[1] * xz, d3 * C3[2] * (-3.f * yy + 4.f * zz - xx), d3 * C3[3] * -3.f * 2.f * yz,
+                           d3 * C3[4] * -2.f * xy, d3 * C3[5] * -2.f * yz, d3 * C3[6] * -3.f * 2.f * xy };
+    const float wz[16] = { 0.f, 0.f, C1 * d1, 0.f,
+                           0.f, d2 * C2[1] * y, d2 * C2[2] * 2.f * 2.f * z, d2 * C2[3] * x, 0.f,
+                           0.f, d3 * C3[1] * xy, d3 * C3[2] * 4.f * 2.f * yz, d3 * C3[3] * 3.f * (2.f * zz - xx - yy),
+                           d3 * C3[4] * 4.f * 2.f * xz, d3 * C3[5] * (xx - yy), 0.f };
+    constexpr unsigned NZX = 0xFFD8u, NZY = 0xFF72u, NZZ = 0x7CE4u;      // bit k: w?[k] is not identically zero
+    float gx[3] = { 0, 0, 0 }, gy[3] = { 0, 0, 0 }, gz[3] = { 0, 0, 0 };
+    const float dr[3] = { dRGB.x, dRGB.y, dRGB.z };
+    const int rot = g % 12;
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+        int p = q + rot;
+        p -= (p >= 12) ? 12 : 0;
+        const float4 v = row4[p];
+        const float f[4] = { v.x, v.y, v.z, v.w };
+        float o[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int j = 4 * q + i, k = j / 3, c = j - 3 * k;
+            if ((NZX >> k) & 1) gx[c] = fmaf(wx[k], f[i], gx[c]);
+            if ((NZY >> k) & 1) gy[c] = fmaf(wy[k], f[i], gy[c]);
+            if ((NZZ >> k) & 1) gz[c] = fmaf(wz[k], f[i], gz[c]);
+            o[i] = basis[k] * dr[c];
+        }
+        row4[p] = make_float4(o[0], o[1], o[2], o[3]);
+    }
+    const V3 ddir = { gx[0] * dr[0] + gx[1] * dr[1] + gx[2] * dr[2], gy[0] * dr[0] + gy[1] * dr[1] + gy[2] * dr[2],
+                      gz[0] * dr[0] + gz[1] * dr[1] + gz[2] * dr[2] };
+    const V3 v = dir_orig;
+    const float sum2 = dot(v, v);
+    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    V3 dmean;
+    dmean.x = ((sum2 - v.x * v.x) * ddir.x - v.y * v.x * ddir.y - v.z * v.x * ddir.z) * invsum32;
+    dmean.y = (-v.x * v.y * ddir.x + (sum2 - v.y * v.y) * ddir.y - v.z * v.y * ddir.z) * invsum32;
+    dmean.z = (-v.x * v.z * ddir.x - v.y * v.z * ddir.y + (sum2 - v.z * v.z) * ddir.z) * invsum32;
+    return dmean;
+}
+
 }  // namespace gsr

@@ -13,10 +13,11 @@ namespace gsr {
 
 // M3: 3 * SH coefficients per surfel (0: colours were precomputed). RAW: model-space variant (split SH rows,
 // gradients taken through sigmoid / exp / normalize to the stored parameters), as in preprocess_bwd.cu.
-template <int M3, bool RAW>
+template <int M3, bool RAW, bool V4 = false>
 __global__ void __launch_bounds__(SH_TILE, 8)
 surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
-    constexpr int TILE_FLOATS = M3 ? SH_TILE * ShTile<M3>::STRIDE : 4;
+    static_assert(!V4 || (M3 == 48 && !RAW), "the 16-byte tile is for whole 48-float rows");
+    constexpr int TILE_FLOATS = M3 ? SH_TILE * (V4 ? 48 : ShTile<M3>::STRIDE) : 4;
     __shared__ __align__(16) float s_sh[TILE_FLOATS];
     __shared__ uint8_t s_vis[SH_TILE];
     const size_t row0 = (size_t)a.row_begin + (size_t)blockIdx.x * SH_TILE;     // this launch covers rows [row_begin, row_end)
@@ -28,7 +29,8 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         s_vis[threadIdx.x] = vis;
         __syncthreads();
         // asynchronous (LDGSTS): in flight while the per-surfel inputs are fetched and the transMat part is computed
-        if constexpr (RAW) sh_tile_load_async_split<M3>(a.shs, a.shs_rest, row0, nrows, s_vis, s_sh);
+        if constexpr (V4)  sh48_load_async(a.shs, row0, nrows, s_vis, reinterpret_cast<float4*>(s_sh));
+        else if constexpr (RAW) sh_tile_load_async_split<M3>(a.shs, a.shs_rest, row0, nrows, s_vis, s_sh);
         else               sh_tile_load_async<M3>(a.shs, row0, nrows, s_vis, s_sh);
     }
 
@@ -36,7 +38,7 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
     V3 dmean = { 0, 0, 0 }, dm2d = { 0, 0, 0 }, dcol = { 0, 0, 0 }, m = { 0, 0, 0 };
     float dscale0 = 0.f, dscale1 = 0.f, dop = 0.f;
     float4 drot = { 0, 0, 0, 0 };
-    float* const my_sh = s_sh + threadIdx.x * ShTile<M3>::STRIDE;      // coefficients in, gradients out (in place)
+    float* const my_sh = s_sh + threadIdx.x * (V4 ? 48 : ShTile<M3>::STRIDE);      // coefficients in, gradients out (in place)
 
     if (vis) {
         const float* ac = a.acc + (size_t)idx * SACC_STRIDE;
@@ -208,10 +210,12 @@ surfel_preprocess_backward_kernel(SurfelBwdArgs a) {
         __syncthreads();
         if (vis) {
             const V3 dRGB = { (cl & 1) ? 0.f : dcol.x, (cl & 2) ? 0.f : dcol.y, (cl & 4) ? 0.f : dcol.z };
-            dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
+            if constexpr (V4) dmean = dmean + sh48_backward(a.D, reinterpret_cast<float4*>(my_sh), threadIdx.x, m, ld3(a.campos), dRGB);
+            else              dmean = dmean + sh_backward(a.D, a.M, my_sh, m, ld3(a.campos), dRGB, my_sh);
         }
         __syncthreads();
-        if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
+        if constexpr (V4) { if (a.dL_dsh) sh48_store(a.dL_dsh, row0, nrows, s_vis, reinterpret_cast<const float4*>(s_sh)); }
+        else if constexpr (RAW) sh_tile_store_split<M3>(a.dL_dsh, a.dL_dsh_rest, row0, nrows, s_vis, s_sh);
         else if (a.dL_dsh) sh_tile_store<M3>(a.dL_dsh, row0, nrows, s_vis, s_sh);    // NULL: the caller rebuilds it (sh_exchange.cu)
     }
     if (!valid) return;
@@ -253,7 +257,10 @@ cudaError_t launch_surfel_preprocess_backward(const SurfelBwdArgs& a, cudaStream
     case 3:  surfel_preprocess_backward_kernel<3, false><<<blocks, SH_TILE, 0, st>>>(a); break;
     case 12: surfel_preprocess_backward_kernel<12, false><<<blocks, SH_TILE, 0, st>>>(a); break;
     case 27: surfel_preprocess_backward_kernel<27, false><<<blocks, SH_TILE, 0, st>>>(a); break;
-    case 48: surfel_preprocess_backward_kernel<48, false><<<blocks, SH_TILE, 0, st>>>(a); break;
+    case 48:      // whole rows at 16-byte granularity when the two bases allow it (sh.cuh)
+        if ((((uintptr_t)a.shs | (uintptr_t)a.dL_dsh) & 15) == 0) surfel_preprocess_backward_kernel<48, false, true><<<blocks, SH_TILE, 0, st>>>(a);
+        else surfel_preprocess_backward_kernel<48, false><<<blocks, SH_TILE, 0, st>>>(a);
+        break;
     default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
