@@ -180,7 +180,7 @@ static int forward_impl(
     a.view = s->viewmatrix; a.proj = s->projmatrix; a.campos = s->campos; a.bg = s->bg;
     a.prefiltered = s->prefiltered != 0;
     a.shs_rest = shs_rest; a.raw = raw;
-    a.skip_histogram = views_aggregated(views, gx * gy);
+    a.skip_histogram = views_aggregated(views, gx * gy, PV / views);
     if ((rc = check_cuda(launch_preprocess(a, g, radii, st, views), "preprocess launch"))) return rc;
     if (a.skip_histogram && (rc = check_cuda(launch_views_histogram(PV, views, gx, gy, g.rec, (int)sizeof(GaussRec), radii, g.tile_count, st),
                                              "views histogram launch"))) return rc;

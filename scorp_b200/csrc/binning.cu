@@ -25,7 +25,7 @@ __device__ __forceinline__ int order_bin(uint32_t len) { return (int)min(len >> 
 // forward (gsr_rasterize_forward_nosync) [2] overflow flag (N > capacity: every range is (0,0), nothing is binned or
 // blended), [3] / [4] how many entries at the head of `order` can need the mid / long sort kernel.
 __global__ void __launch_bounds__(1024)
-tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ counters,
+tile_scan_kernel(int tiles, uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ counters,
                  uint32_t* __restrict__ order, uint32_t capacity) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry_s;
@@ -41,7 +41,7 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         const int t = base + threadIdx.x;
         const uint32_t c = (t < tiles) ? count[tc(t)] : 0u;
         longest = max(longest, c);
-        if (t < tiles) atomicAdd(&bins[order_bin(c)], 1u);
+        if (t < tiles) atomicAdd(&bins[order_bin(overflow ? 0u : c)], 1u);      // the class the order loop below will find in ranges[]
         uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
@@ -56,7 +56,10 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
         __syncthreads();
         const uint32_t carry = carry_s;
         const uint32_t incl = carry + v + (wid ? warp_sums[wid - 1] : 0u);
-        if (t < tiles) ranges[t] = (c && !overflow) ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
+        if (t < tiles) {
+            ranges[t] = (c && !overflow) ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
+            count[tc(t)] = incl;         // from here on the scatter's cursor: absolute END of the tile's segment, counted down
+        }
         __syncthreads();
         if (threadIdx.x == 1023) carry_s = incl;
         __syncthreads();
@@ -91,17 +94,19 @@ tile_scan_kernel(int tiles, const uint32_t* __restrict__ count, uint2* __restric
             counters[4] = overflow ? 0u : bins[ORDER_BINS - 2];
         }
         __syncthreads();
-        for (int t = threadIdx.x; t < tiles; t += 1024) order[atomicAdd(&bins[order_bin(count[tc(t)])], 1u)] = (uint32_t)t;
+        for (int t = threadIdx.x; t < tiles; t += 1024) {
+            const uint2 r = ranges[t];           // (count[] holds the cursors by now)
+            order[atomicAdd(&bins[order_bin(r.y - r.x)], 1u)] = (uint32_t)t;
+        }
     }
 }
 
 // ---- 3. scatter instances into tile segments ----------------------------------------------
-// tile_count is consumed as a cursor (atomicSub), leaving it zero. One lane per Gaussian computes the
-// tile rectangle; rectangles of up to SMALL_RECT tiles are written by their own lane, larger ones are
-// spread over the whole warp (32 tiles per round), so one screen-filling splat does not serialise
-// hundreds of returning atomics behind a single thread.
-constexpr uint32_t SMALL_RECT = 4;
-
+// tile_count is consumed as a cursor: tile_scan replaced each count by the absolute end of the tile's segment, and
+// every instance takes the slot below it (atomicSub), so no range lookup is needed. One lane per Gaussian computes the
+// tile rectangle; the warp then walks the tiles of its 32 rectangles 32 at a time (warp_rects_packed), so a
+// screen-filling splat does not serialise hundreds of returning atomics behind a single thread and a warp of
+// medium splats does not take one round trip per splat.
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
                const int32_t* __restrict__ radii,
@@ -109,7 +114,6 @@ scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ rec
                const uint32_t* __restrict__ overflow) {
     if (overflow && *overflow) return;        // no-sync forward whose instances exceed the caller's capacity: nothing is binned
     const int idx = blockIdx.x * 256 + threadIdx.x;
-    const int lane = threadIdx.x & 31;
     uint32_t x0 = 0, y0 = 0, w = 0, cnt = 0;
     uint32_t tbase = 0;                       // first tile of this record's view (0 for a single view)
     uint64_t key = 0;
@@ -128,34 +132,10 @@ scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ rec
             tbase = (uint32_t)(idx / per_view) * (uint32_t)(gx * gy);
         }
     }
-    auto put = [&](uint32_t t, uint64_t k) {
-        const uint32_t slot = atomicSub(tile_count + tc(t), 1u) - 1u;
-        keys[ranges[t].x + slot] = k;
-    };
-    if (cnt > 0 && cnt <= SMALL_RECT) {
-        // all cursor atomics first, then the dependent stores: one round trip instead of one per tile
-        uint32_t t[SMALL_RECT], at[SMALL_RECT];
-#pragma unroll
-        for (uint32_t i = 0; i < SMALL_RECT; ++i) {
-            if (i < cnt) {
-                t[i] = tbase + (y0 + i / w) * gx + x0 + i % w;
-                at[i] = __ldg(&ranges[t[i]].x) + atomicSub(tile_count + tc(t[i]), 1u) - 1u;
-            }
-        }
-#pragma unroll
-        for (uint32_t i = 0; i < SMALL_RECT; ++i)
-            if (i < cnt) keys[at[i]] = key;
-    }
-    uint32_t big = __ballot_sync(0xffffffffu, cnt > SMALL_RECT);
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-        const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
-        const uint64_t bkey = __shfl_sync(0xffffffffu, key, src);
-        const uint32_t bt = __shfl_sync(0xffffffffu, tbase, src);
-        for (uint32_t i = lane; i < bcnt; i += 32) put(bt + (by0 + i / bw) * gx + bx0 + i % bw, bkey);
-    }
+    // tiles of the warp's 32 rectangles, 32 per round (common.cuh): cursor atomic, then the dependent store
+    warp_rects_packed<true>(gx, tbase + y0 * (uint32_t)gx + x0, w, cnt, key, [&](uint32_t t, uint64_t k) {
+        keys[atomicSub(tile_count + tc(t), 1u) - 1u] = k;        // tile_scan left the END of the tile's segment there
+    });
 }
 
 // ---- 3b. batched views: the same two jobs with the atomics aggregated per CTA ---------------------------------------
@@ -164,27 +144,13 @@ scatter_kernel(int P, int per_view, int gx, int gy, const char* __restrict__ rec
 // scatter (cursor). Gaussians arrive in no spatial order, so a CTA of 256 of them cannot combine anything; here a CTA
 // takes VIEWS_CHUNK Gaussians of ONE view, counts in a shared-memory copy of that view's tile grid and issues one global
 // atomic per non-empty tile: ~17x fewer at C5. The order inside a tile segment is arbitrary either way (the sort fixes it).
+// ONE large view was tried the same way (GSR_AGGREGATE=1, chunks of P/296 Gaussians, tile grids up to AGG_MAX_TILES):
+// C3 binning 0.84 -> 1.39 ms, C2 0.137 -> 0.158. With ~8 k tiles a chunk of 20 k Gaussians combines only ~10 instances
+// per tile and pays for two passes over the records and two sweeps over the grid; left as an experiment switch.
 constexpr int VIEWS_CHUNK = 8192;
-constexpr int VIEWS_MAX_TILES = 6144;          // two uint32 per tile in shared memory (48 KB)
+constexpr int AGG_THREADS = 256;
+constexpr int AGG_MAX_TILES = 24576;           // two uint32 per tile in shared memory (192 KB; 8 K x 3 K pixels)
 
-// every lane brings one rectangle (cnt = 0: none) and a payload; f(tile, payload of the rectangle's lane) is called once
-// per covered tile, rectangles of up to HIST_SMALL tiles by their own lane, larger ones spread over the warp (the
-// payload is broadcast BEFORE the spread loop: the owning lane may have no tile of its own in it). All 32 lanes call.
-template <class F>
-__device__ __forceinline__ void warp_rect_foreach(int gx, uint32_t x0, uint32_t y0, uint32_t w, uint32_t cnt, uint64_t pay, F&& f) {
-    const uint32_t lane = threadIdx.x & 31;
-    if (cnt > 0 && cnt <= HIST_SMALL)
-        for (uint32_t i = 0; i < cnt; ++i) f((y0 + i / w) * gx + x0 + i % w, pay);
-    uint32_t big = __ballot_sync(0xffffffffu, cnt > HIST_SMALL);
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-        const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
-        const uint64_t bpay = __shfl_sync(0xffffffffu, pay, src);
-        for (uint32_t i = lane; i < bcnt; i += 32) f((by0 + i / bw) * gx + bx0 + i % bw, bpay);
-    }
-}
 __device__ __forceinline__ void rect_of_record(const char* __restrict__ recs, int rec_stride, const int32_t* __restrict__ radii,
                                                size_t idx, bool in_range, int gx, int gy, uint32_t& x0, uint32_t& y0, uint32_t& w,
                                                uint32_t& cnt) {
@@ -198,58 +164,58 @@ __device__ __forceinline__ void rect_of_record(const char* __restrict__ recs, in
     w = x1 - x0;
     cnt = w * (y1 - y0);
 }
-__global__ void __launch_bounds__(256)
-views_histogram_kernel(int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride,
+__global__ void __launch_bounds__(AGG_THREADS)
+views_histogram_kernel(int per_view, int chunk, int gx, int gy, const char* __restrict__ recs, int rec_stride,
                        const int32_t* __restrict__ radii, uint32_t* __restrict__ tile_count) {
     extern __shared__ uint32_t s_cnt[];
     const int tiles = gx * gy, view = blockIdx.y;
-    for (int t = threadIdx.x; t < tiles; t += 256) s_cnt[t] = 0u;
+    for (int t = threadIdx.x; t < tiles; t += AGG_THREADS) s_cnt[t] = 0u;
     __syncthreads();
-    const int first = blockIdx.x * VIEWS_CHUNK, last = min(first + VIEWS_CHUNK, per_view);
-    for (int base = first; base < last; base += 256) {            // CTA-uniform trip count
+    const int first = blockIdx.x * chunk, last = min(first + chunk, per_view);
+    for (int base = first; base < last; base += AGG_THREADS) {            // CTA-uniform trip count
         const int i = base + threadIdx.x;
         uint32_t x0, y0, w, cnt;
         rect_of_record(recs, rec_stride, radii, (size_t)view * per_view + i, i < last, gx, gy, x0, y0, w, cnt);
-        warp_rect_foreach(gx, x0, y0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(&s_cnt[t], 1u); });
+        warp_rects_packed<false>(gx, y0 * (uint32_t)gx + x0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(&s_cnt[t], 1u); });
     }
     __syncthreads();
     uint32_t* out = tile_count + tc((size_t)view * tiles);
-    for (int t = threadIdx.x; t < tiles; t += 256) { const uint32_t c = s_cnt[t]; if (c) atomicAdd(out + tc(t), c); }
+    for (int t = threadIdx.x; t < tiles; t += AGG_THREADS) { const uint32_t c = s_cnt[t]; if (c) atomicAdd(out + tc(t), c); }
 }
-__global__ void __launch_bounds__(256)
-views_scatter_kernel(int per_view, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
+__global__ void __launch_bounds__(AGG_THREADS)
+views_scatter_kernel(int per_view, int chunk, int gx, int gy, const char* __restrict__ recs, int rec_stride, int depth_off,
                      const int32_t* __restrict__ radii, uint32_t* __restrict__ tile_count, const uint2* __restrict__ ranges,
                      uint64_t* __restrict__ keys, const uint32_t* __restrict__ overflow) {
     if (overflow && *overflow) return;
     extern __shared__ uint32_t s_cnt[];                           // [tiles] counts, then cursors; [tiles] first slot
     const int tiles = gx * gy, view = blockIdx.y;
     uint32_t* s_base = s_cnt + tiles;
-    for (int t = threadIdx.x; t < tiles; t += 256) s_cnt[t] = 0u;
+    for (int t = threadIdx.x; t < tiles; t += AGG_THREADS) s_cnt[t] = 0u;
     __syncthreads();
-    const int first = blockIdx.x * VIEWS_CHUNK, last = min(first + VIEWS_CHUNK, per_view);
-    for (int base = first; base < last; base += 256) {
+    const int first = blockIdx.x * chunk, last = min(first + chunk, per_view);
+    for (int base = first; base < last; base += AGG_THREADS) {
         const int i = base + threadIdx.x;
         uint32_t x0, y0, w, cnt;
         rect_of_record(recs, rec_stride, radii, (size_t)view * per_view + i, i < last, gx, gy, x0, y0, w, cnt);
-        warp_rect_foreach(gx, x0, y0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(&s_cnt[t], 1u); });
+        warp_rects_packed<false>(gx, y0 * (uint32_t)gx + x0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(&s_cnt[t], 1u); });
     }
     __syncthreads();
     // one cursor atomic per non-empty tile reserves this CTA's block of the tile's segment
     const size_t vt = (size_t)view * tiles;
-    for (int t = threadIdx.x; t < tiles; t += 256) {
+    for (int t = threadIdx.x; t < tiles; t += AGG_THREADS) {
         const uint32_t c = s_cnt[t];
-        if (c) s_base[t] = ranges[vt + t].x + atomicSub(tile_count + tc(vt + t), c) - c;
+        if (c) s_base[t] = atomicSub(tile_count + tc(vt + t), c) - c;
         s_cnt[t] = 0u;
     }
     __syncthreads();
-    for (int base = first; base < last; base += 256) {
+    for (int base = first; base < last; base += AGG_THREADS) {
         const int i = base + threadIdx.x;
         const size_t idx = (size_t)view * per_view + i;
         uint32_t x0, y0, w, cnt;
         rect_of_record(recs, rec_stride, radii, idx, i < last, gx, gy, x0, y0, w, cnt);
         uint64_t key = 0;
         if (cnt) key = ((uint64_t)__float_as_uint(__ldg(reinterpret_cast<const float*>(recs + idx * rec_stride + depth_off))) << 32) | (uint32_t)idx;
-        warp_rect_foreach(gx, x0, y0, w, cnt, key, [&](uint32_t t, uint64_t k) { keys[s_base[t] + atomicAdd(&s_cnt[t], 1u)] = k; });
+        warp_rects_packed<true>(gx, y0 * (uint32_t)gx + x0, w, cnt, key, [&](uint32_t t, uint64_t k) { keys[s_base[t] + atomicAdd(&s_cnt[t], 1u)] = k; });
     }
 }
 
@@ -411,11 +377,17 @@ tile_sort_queued_kernel(int lo_len, const uint32_t* __restrict__ n_work, const u
 // long). A tile whose entries all share one depth, or that holds a run longer than RUN_MAX, is sorted by the full
 // four-pass sort on the depth bits (followed by the same ranking step, which then orders equal depths by index).
 constexpr int RADIX_K = 8;                     // positions per thread
+__device__ int g_bucket_first = 1;             // GSR_BUCKET_SORT=0 (experiments): skip the bucket pass
+__device__ __forceinline__ bool bucket_first() { return g_bucket_first != 0; }
 constexpr int RUN_MAX = 48;
+constexpr uint32_t BUCKET_MAX = 16;          // the bucket pass gives up on a tile with a fuller bucket than this
 template <int THREADS> struct RadixSmem {
     static constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
     uint2 a[CAP], b[CAP];                      // .x = Gaussian index, .y = depth bits
-    uint16_t cnt[W][256];
+    union {
+        uint16_t cnt[W][256];                  // radix passes: per-warp digit counters
+        uint32_t bin[CAP];                     // bucket pass: one counter, then first slot, per bucket
+    };
     uint32_t base[256];
     uint32_t total[256];
     uint32_t skip[4];                          // per pass: every key has the same digit (the pass is the identity)
@@ -514,6 +486,80 @@ __device__ __forceinline__ void radix_pass_unstable(RadixSmem<THREADS>& sm, cons
     }
     __syncthreads();
 }
+// Bucket pass (round 2b): ONE counting pass over CAP buckets of the tile's own depth range, u = floor((depth - dmin) *
+// (CAP - 1) / (dmax - dmin)), slots inside a bucket handed out by shared-memory atomics in arrival order; since u is a
+// monotone map of the depth, every key's final position is its bucket's first slot plus the number of keys in the bucket
+// that are below it in (depth bits, index) order -- buckets hold one or two keys when the depths spread over the range.
+// No match.any, no second pass. Returns false (nothing written) when a bucket holds more than BUCKET_MAX keys: clustered
+// depths, left to the 16-bit two-pass sort below. Keys are read from sm.a, which is left intact.
+template <int THREADS>
+__device__ __forceinline__ bool tile_bucket_sort(RadixSmem<THREADS>& sm, int L, float dmin, float range, uint64_t tile_hi,
+                                                 uint32_t* __restrict__ out_list, uint64_t* __restrict__ out_keys) {
+    constexpr int CAP = THREADS * RADIX_K, W = THREADS / 32;
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const float scale = __fdividef((float)(CAP - 1), range);
+    auto bucket = [&](const uint2& k) { return min((uint32_t)(CAP - 1), (uint32_t)(__fsub_rn(__uint_as_float(k.y), dmin) * scale)); };
+    uint4* bin4 = reinterpret_cast<uint4*>(sm.bin);
+    bin4[2 * tid] = make_uint4(0u, 0u, 0u, 0u); bin4[2 * tid + 1] = make_uint4(0u, 0u, 0u, 0u);     // RADIX_K == 8 buckets per thread
+    __syncthreads();
+    uint2 key[RADIX_K];
+    uint32_t slot[RADIX_K];
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = tid + r * THREADS;
+        slot[r] = 0;
+        if (p < L) { key[r] = sm.a[p]; slot[r] = atomicAdd(&sm.bin[bucket(key[r])], 1u); }
+    }
+    __syncthreads();
+    {   // counts -> first slots (exclusive scan over the CAP buckets, 8 consecutive ones per thread); fullest bucket
+        const uint4 c0 = bin4[2 * tid], c1 = bin4[2 * tid + 1];
+        const uint32_t sum = c0.x + c0.y + c0.z + c0.w + c1.x + c1.y + c1.z + c1.w;
+        const uint32_t most = max(max(max(c0.x, c0.y), max(c0.z, c0.w)), max(max(c1.x, c1.y), max(c1.z, c1.w)));
+        if (most > BUCKET_MAX) sm.long_run = 1u;
+        uint32_t incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += n; }
+        if (lane == 31) sm.total[w] = incl;
+        __syncthreads();
+        if (w == 0) {
+            const uint32_t t = lane < W ? sm.total[lane] : 0u;
+            uint32_t ti = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(0xffffffffu, ti, o); if (lane >= o) ti += n; }
+            if (lane < W) sm.total[lane] = ti - t;
+        }
+        __syncthreads();
+        if (sm.long_run) return false;                 // CTA-uniform
+        uint32_t run = sm.total[w] + incl - sum;
+        uint4 s0, s1;
+        s0.x = run; run += c0.x; s0.y = run; run += c0.y; s0.z = run; run += c0.z; s0.w = run; run += c0.w;
+        s1.x = run; run += c1.x; s1.y = run; run += c1.y; s1.z = run; run += c1.z; s1.w = run;
+        bin4[2 * tid] = s0; bin4[2 * tid + 1] = s1;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = tid + r * THREADS;
+        if (p < L) sm.b[sm.bin[bucket(key[r])] + slot[r]] = key[r];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < RADIX_K; ++r) {
+        const int p = tid + r * THREADS;
+        if (p >= L) continue;
+        const uint2 k = sm.b[p];
+        const uint32_t u = bucket(k);
+        const int s0 = (int)sm.bin[u], e0 = (u + 1 < (uint32_t)CAP) ? (int)sm.bin[u + 1] : L;
+        int at = p;
+        if (e0 - s0 > 1) {
+            int below = 0;
+            for (int q = s0; q < e0; ++q) { const uint2 o = sm.b[q]; below += (o.y < k.y) || (o.y == k.y && o.x < k.x); }
+            at = s0 + below;
+        }
+        out_list[at] = k.x; out_keys[at] = tile_hi | k.y;
+    }
+    return true;
+}
 template <int THREADS>
 __device__ __forceinline__ void tile_radix_one(RadixSmem<THREADS>& sm, int tile, int lo_len, const uint2* __restrict__ ranges,
                                                const uint64_t* __restrict__ keys, uint32_t* __restrict__ point_list,
@@ -546,14 +592,19 @@ __device__ __forceinline__ void tile_radix_one(RadixSmem<THREADS>& sm, int tile,
     uint2* src = sm.a;
     uint2* dst = sm.b;
     bool full = (dmin_b == dmax_b);             // one depth for the whole tile: order by index through the full sort
+    const uint64_t tile_hi = (uint64_t)tile << 32;
+    uint32_t* out_list = point_list + rg.x;
+    uint64_t* out_keys = point_list_keys + rg.x;
+    if (!full && bucket_first()) {
+        if (tile_bucket_sort<THREADS>(sm, L, dmin, __uint_as_float(dmax_b) - dmin, tile_hi, out_list, out_keys)) return;
+        __syncthreads();                        // every thread has read the flag
+        if (tid == 0) sm.long_run = 0u;         // (its next use is behind the barriers of the radix passes)
+    }
     if (!full) {
         radix_pass_unstable<THREADS>(sm, src, dst, L, [&](const uint2& k) { return mapped(k) & 255u; });
         { uint2* t = src; src = dst; dst = t; }
         if (radix_pass_stable<THREADS>(sm, src, dst, L, 0, [&](const uint2& k) { return mapped(k) >> 8; })) { uint2* t = src; src = dst; dst = t; }
     }
-    const uint64_t tile_hi = (uint64_t)tile << 32;
-    uint32_t* out_list = point_list + rg.x;
-    uint64_t* out_keys = point_list_keys + rg.x;
     for (int attempt = 0; attempt < 2; ++attempt) {
         if (full) {
             // four stable 8-bit passes on the depth bits, from the segment as it arrived
@@ -737,7 +788,7 @@ constexpr int SORT_M_CAP = 8192, SORT_M_THREADS = 1024;      // very crowded til
 static_assert(SORT_S_CAP == SORT_S_CAP_ && SORT_S_CAP == SORT_S_THREADS * RADIX_K && SORT_M1_CAP == SORT_M1_THREADS * RADIX_K &&
               SORT_M_CAP == SORT_M_THREADS * RADIX_K, "size classes");
 
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
+cudaError_t launch_tile_scan(int tiles, uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
                              cudaStream_t st, uint32_t capacity) {
     tile_scan_kernel<<<1, 1024, 0, st>>>(tiles, tile_count, ranges, counters, order, capacity);
     return cudaGetLastError();
@@ -756,6 +807,18 @@ static size_t small_smem_bytes() {
     return a > b ? a : b;
 }
 // dynamic shared memory above 48 KB has to be requested per kernel and device
+static cudaError_t apply_bucket_switch() {
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || done[dev]) return cudaSuccess;
+    done[dev] = true;
+    const char* v = getenv("GSR_BUCKET_SORT");
+    if (!v) return cudaSuccess;
+    const int on = atoi(v) ? 1 : 0;
+    return cudaMemcpyToSymbol(g_bucket_first, &on, sizeof(int));
+}
 static cudaError_t set_radix_attrs() {
     static bool done[64] = {};
     int dev = 0;
@@ -771,16 +834,47 @@ static cudaError_t set_radix_attrs() {
     return cudaSuccess;
 }
 
-bool views_aggregated(int views, int tiles_per_view) {
-    static int off = -1;
-    if (off < 0) { const char* e = getenv("GSR_VIEWS_NO_AGGREGATE"); off = (e && atoi(e)) ? 1 : 0; }
-    return !off && views > 1 && tiles_per_view <= VIEWS_MAX_TILES;
+// GSR_AGGREGATE: 0 never, 1 whenever the tile grid fits (experiment), unset: batched views with a small grid
+bool views_aggregated(int views, int tiles_per_view, int per_view) {
+    static int mode = -2;
+    if (mode == -2) {
+        const char* e = getenv("GSR_AGGREGATE");
+        mode = e ? atoi(e) : -1;
+        const char* o = getenv("GSR_VIEWS_NO_AGGREGATE");
+        if (o && atoi(o)) mode = 0;
+    }
+    if (mode == 0 || tiles_per_view > AGG_MAX_TILES) return false;
+    if (mode == 1) return true;
+    (void)per_view;
+    return views > 1 && tiles_per_view <= 6144;
+}
+static int agg_chunk(int views, int per_view) {
+    if (views > 1) return VIEWS_CHUNK;
+    static int forced = -1;
+    if (forced < 0) { const char* e = getenv("GSR_AGG_CHUNK"); forced = e ? atoi(e) : 0; }
+    if (forced > 0) return (forced + AGG_THREADS - 1) / AGG_THREADS * AGG_THREADS;
+    int c = (per_view + 2 * 148 - 1) / (2 * 148);
+    c = (c + AGG_THREADS - 1) / AGG_THREADS * AGG_THREADS;
+    return c < VIEWS_CHUNK ? VIEWS_CHUNK : c;
+}
+static cudaError_t set_agg_attrs() {
+    static bool done[64] = {};
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64 || done[dev]) return cudaSuccess;
+    if ((e = cudaFuncSetAttribute(views_histogram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AGG_MAX_TILES * 4)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(views_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AGG_MAX_TILES * 8)) != cudaSuccess) return e;
+    done[dev] = true;
+    return cudaSuccess;
 }
 cudaError_t launch_views_histogram(int P_total, int views, int gx, int gy, const void* recs, int rec_stride, const int32_t* radii,
                                    uint32_t* tile_count, cudaStream_t st) {
-    const int per_view = P_total / views;
-    views_histogram_kernel<<<dim3((per_view + VIEWS_CHUNK - 1) / VIEWS_CHUNK, views), 256, (size_t)gx * gy * 4, st>>>(
-        per_view, gx, gy, (const char*)recs, rec_stride, radii, tile_count);
+    const int per_view = P_total / views, chunk = agg_chunk(views, per_view);
+    cudaError_t e = set_agg_attrs();
+    if (e != cudaSuccess) return e;
+    views_histogram_kernel<<<dim3((per_view + chunk - 1) / chunk, views), AGG_THREADS, (size_t)gx * gy * 4, st>>>(
+        per_view, chunk, gx, gy, (const char*)recs, rec_stride, radii, tile_count);
     return cudaGetLastError();
 }
 
@@ -790,10 +884,12 @@ cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void
     const int tiles = gx * gy * views;
     if (N <= 0) return cudaSuccess;
     cudaError_t e;
-    if (views_aggregated(views, gx * gy)) {
-        const int per_view = P / views;
-        views_scatter_kernel<<<dim3((per_view + VIEWS_CHUNK - 1) / VIEWS_CHUNK, views), 256, (size_t)gx * gy * 8, st>>>(
-            per_view, gx, gy, (const char*)recs, rec_stride, depth_off, radii, tile_count, ranges, bin.scratch,
+    if ((e = apply_bucket_switch()) != cudaSuccess) return e;
+    if (views_aggregated(views, gx * gy, P / views)) {
+        const int per_view = P / views, chunk = agg_chunk(views, per_view);
+        if ((e = set_agg_attrs()) != cudaSuccess) return e;
+        views_scatter_kernel<<<dim3((per_view + chunk - 1) / chunk, views), AGG_THREADS, (size_t)gx * gy * 8, st>>>(
+            per_view, chunk, gx, gy, (const char*)recs, rec_stride, depth_off, radii, tile_count, ranges, bin.scratch,
             counters ? counters + 2 : nullptr);
     } else
     scatter_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, P / views, gx, gy, (const char*)recs, rec_stride, depth_off, radii,

@@ -215,23 +215,45 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int gx
     y1 = min((uint32_t)gy, (uint32_t)max(0, (int)mulr(addr(addr(addr(py, rf), 16.0f), -1.0f), 0.0625f)));
 }
 
-// Warp-wide: every lane brings one tile rectangle (origin x0,y0, width w, cnt = w*h tiles, cnt = 0 for none) and
-// one is added to tile_count for every tile of every rectangle. Rectangles of up to HIST_SMALL tiles are done by
-// their own lane; larger ones are spread over the 32 lanes. Must be called by all 32 lanes.
-constexpr uint32_t HIST_SMALL = 4;
-__device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uint32_t x0, uint32_t y0, uint32_t w, uint32_t cnt) {
-    if (cnt > 0 && cnt <= HIST_SMALL) {
-        for (uint32_t i = 0; i < cnt; ++i) atomicAdd(tile_count + tc((y0 + i / w) * gx + x0 + i % w), 1u);
-    }
-    uint32_t big = __ballot_sync(0xffffffffu, cnt > HIST_SMALL);
+// Warp-wide walk over the tiles of 32 rectangles. Every lane brings one rectangle -- t0 = index of its first tile,
+// w = width in tiles, cnt = w * h tiles (0: none) -- and, if PAY, a 64-bit payload; f(tile, payload of the rectangle's
+// lane) is called once per covered tile. The tiles of all 32 rectangles are laid end to end (warp prefix sum over cnt) and
+// taken 32 at a time, one per lane: a lane finds the rectangle its slot belongs to with a 5-step binary search over the
+// prefix sums (shuffles), so every round has 32 independent atomics in flight whatever the rectangle sizes are.
+// (Round 1/2a: rectangles of <= 4 tiles by their own lane, each larger one spread over the warp in a round of its own:
+// at C3, ~14 dependent rounds per warp and 45 % of preprocess_kernel's instructions, most of them the i / w, i % w pair;
+// now ceil(sum cnt / 32) = 4.3 rounds and a float reciprocal.) Must be called by all 32 lanes.
+template <bool PAY, class F>
+__device__ __forceinline__ void warp_rects_packed(int gx, uint32_t t0, uint32_t w, uint32_t cnt, uint64_t pay, F&& f) {
+    constexpr uint32_t FULL = 0xffffffffu;
     const uint32_t lane = threadIdx.x & 31;
-    while (big) {
-        const int src = __ffs(big) - 1;
-        big &= big - 1;
-        const uint32_t bx0 = __shfl_sync(0xffffffffu, x0, src), by0 = __shfl_sync(0xffffffffu, y0, src);
-        const uint32_t bw = __shfl_sync(0xffffffffu, w, src), bcnt = __shfl_sync(0xffffffffu, cnt, src);
-        for (uint32_t i = lane; i < bcnt; i += 32) atomicAdd(tile_count + tc((by0 + i / bw) * gx + bx0 + i % bw), 1u);
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { const uint32_t n = __shfl_up_sync(FULL, incl, o); if (lane >= o) incl += n; }
+    const uint32_t total = __shfl_sync(FULL, incl, 31);
+    const uint32_t excl = incl - cnt;
+    const bool fast = total < (1u << 20);       // (i + 0.5) / w in float is then exact enough to floor (error < 0.25 / w)
+    for (uint32_t base = 0; base < total; base += 32) {
+        const uint32_t j = base + lane;
+        uint32_t own = 0, oe = 0;               // the last lane whose first slot is <= j (an empty lane shares its slot with the next)
+#pragma unroll
+        for (int s = 16; s; s >>= 1) {
+            const uint32_t e = __shfl_sync(FULL, excl, own + s);
+            if (e <= j) { own += s; oe = e; }
+        }
+        const uint32_t ot0 = __shfl_sync(FULL, t0, own), ow = __shfl_sync(FULL, w, own);
+        uint64_t opay = 0;
+        if constexpr (PAY) opay = __shfl_sync(FULL, pay, own);
+        if (j < total) {
+            const uint32_t i = j - oe;
+            const uint32_t row = fast ? (uint32_t)__fdividef((float)i + 0.5f, (float)ow) : i / ow;
+            f(ot0 + row * (uint32_t)gx + (i - row * ow), opay);
+        }
     }
+}
+// one is added to tile_count for every tile of every lane's rectangle (origin x0,y0, width w, cnt tiles)
+__device__ __forceinline__ void tile_histogram(uint32_t* tile_count, int gx, uint32_t x0, uint32_t y0, uint32_t w, uint32_t cnt) {
+    warp_rects_packed<false>(gx, y0 * (uint32_t)gx + x0, w, cnt, 0ull, [&](uint32_t t, uint64_t) { atomicAdd(tile_count + tc(t), 1u); });
 }
 
 // ---- view-sharded multi-GPU: the non-SH parameter gradients are summed over ranks in the NVSwitch (NVLS) -------------
@@ -293,7 +315,7 @@ cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* rad
 cudaError_t launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t st);
 // counters = GeomState::counters ([0] N in, [1] longest segment out, [2..4] see binning.cu); capacity: instances the
 // binning buffer holds (no-sync forward), beyond it the overflow flag is raised and every range is left empty
-cudaError_t launch_tile_scan(int tiles, const uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
+cudaError_t launch_tile_scan(int tiles, uint32_t* tile_count, uint2* ranges, uint32_t* counters, uint32_t* order,
                              cudaStream_t st, uint32_t capacity = 0xffffffffu);
 // views > 1: P is the TOTAL record count (views * Gaussians), record v*Pv + i belongs to view v and its tiles are
 // numbered v * gx*gy + local tile
@@ -302,7 +324,7 @@ cudaError_t launch_binning(int P, int gx, int gy, int N, int max_len, const void
                            cudaStream_t st, int views = 1, const uint32_t* counters = nullptr, const uint32_t* order = nullptr);
 // batched views with a small tile grid: preprocess leaves the per-tile histogram to launch_views_histogram (atomics
 // aggregated per CTA in shared memory, binning.cu 3b) and launch_binning scatters the same way
-bool views_aggregated(int views, int tiles_per_view);
+bool views_aggregated(int views, int tiles_per_view, int per_view);
 cudaError_t launch_views_histogram(int P_total, int views, int gx, int gy, const void* recs, int rec_stride, const int32_t* radii,
                                    uint32_t* tile_count, cudaStream_t st);
 cudaError_t launch_render_forward(int W, int H, int gx, int gy, const GeomState& g, const ImageState& img,
