@@ -71,6 +71,10 @@ __device__ __forceinline__ float3 cov2d_from_cov3d(float tx, float ty, float tz,
     return make_float3(addr(cov00, 0.3f), cov01, addr(cov11, 0.3f));
 }
 
+// (Tried in round 2: the CTA's SH rows staged through shared memory with unit-stride 16-byte cp.async, as the backward
+// does (sh.cuh, sh48_*), either right after the depth test or once the rectangle is known: C3 0.36 -> 0.44 ms both ways.
+// 48 KB of shared memory per CTA leaves ~60 KB of L1 for the strided 4-byte reads of means / scales / rotations and the
+// 48-byte record stores, which is what this kernel leans on; the float4 row reads below stay.)
 template <bool VEC, bool RAW>
 __global__ void __launch_bounds__(256, 4)
 preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
@@ -171,7 +175,7 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
         g.tiles_touched[idx] = tiles;
     }
     // per-tile instance histogram (replaces the reference's scan over tiles_touched + duplicateWithKeys counting):
-    // small rectangles by their own lane, large ones spread over the warp so one big splat does not serialise it
+    // the warp's 32 rectangles are walked 32 tiles at a time (common.cuh, warp_rects_packed)
     if (!a.skip_histogram) tile_histogram(g.tile_count, a.gx, rx0, ry0, rw, tiles);
     // total instance count: one atomic per warp
     const uint32_t wsum = __reduce_add_sync(0xffffffffu, tiles);

@@ -250,11 +250,12 @@ __device__ __forceinline__ int sh48_chunk(int g, int q) {      // q in [0, 12)
     p -= (p >= 12) ? 12 : 0;
     return g * 12 + p;
 }
+template <int THREADS = SH_TILE>
 __device__ __forceinline__ void sh48_load_async(const float* __restrict__ shs, size_t row0, int nrows,
                                                 const uint8_t* s_vis, float4* s4) {
     const float4* src = reinterpret_cast<const float4*>(shs + row0 * 48);
 #pragma unroll 12
-    for (int e = threadIdx.x; e < nrows * 12; e += SH_TILE) {
+    for (int e = threadIdx.x; e < nrows * 12; e += THREADS) {
         const int g = e / 12, q = e - g * 12;
         if (s_vis[g]) cp_async16(s4 + sh48_chunk(g, q), src + e);
     }

@@ -244,3 +244,30 @@ def test_equal_depths_come_out_in_index_order(name, P, W, H, plane):
     _assert_exact("n_contrib", io["n_contrib"], ir["n_contrib"])
     for k in ("color", "depth", "alpha"):
         _assert_exact(k, fo[k], fr[k])
+
+
+@pytest.mark.parametrize("name,P,W,H,width", [
+    ("cluster_two_pass", 60_000, 96, 64, 2e-2),          # buckets overflow, the 16-bit map still separates the keys
+    ("cluster_four_pass", 60_000, 96, 64, 2e-6),         # runs of equal 16-bit keys too: the full sort on the depth bits
+    ("cluster_small_lists", 40_000, 320, 208, 2e-4),     # the same in the small size class (lists of a few hundred)
+])
+def test_clustered_depths_take_the_fallback_sorts(name, P, W, H, width):
+    """The per-tile sort first tries ONE counting pass over buckets of the tile's depth range (binning.cu,
+    tile_bucket_sort); 97 % of the Gaussians squeezed into a thin slab with the rest spread over the whole range
+    overfills its buckets, so the tile goes to the 16-bit two-pass sort, and for a thinner slab to the four-pass sort.
+    Every level must give the reference's lists bit for bit."""
+    ref_cuda = _need_ref()
+    sc = h.make("C1", P=P, W=W, H=H, random_bg=True); cam = sc.cameras[0]
+    g = torch.Generator().manual_seed(5)
+    z = sc.means3D[:, 2].clone()
+    slab = (torch.rand(P, generator=g) < 0.97).cuda()
+    z[slab] = 6.0 + width * torch.rand(P, generator=g).cuda()[slab]         # camera 0 is the identity: depth = z
+    sc.means3D[:, 2] = z
+    fo = h.ours_forward(sc, cam); fr = h.ref_forward(sc, cam)
+    assert fo["num_rendered"] == fr["num_rendered"]
+    io, ir = h.ours_intermediates(fo), ref_cuda.dgr_intermediates(fr)
+    _assert_exact("point_list_keys", io["point_list_keys"], ir["point_list_keys"])
+    _assert_exact("point_list", io["point_list"], ir["point_list"])
+    _assert_exact("n_contrib", io["n_contrib"], ir["n_contrib"])
+    for k in ("color", "depth", "alpha"):
+        _assert_exact(k, fo[k], fr[k])
