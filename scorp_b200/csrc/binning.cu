@@ -28,25 +28,23 @@ __global__ void __launch_bounds__(1024)
 tile_scan_kernel(int tiles, uint32_t* __restrict__ count, uint2* __restrict__ ranges, uint32_t* __restrict__ counters,
                  uint32_t* __restrict__ order, uint32_t capacity) {
     __shared__ uint32_t warp_sums[32];
+    __shared__ uint32_t carry_s;
     __shared__ uint32_t bins[ORDER_BINS];
     uint32_t* const max_len = counters + 1;
     const bool overflow = counters[0] > capacity;
     bins[threadIdx.x] = 0;
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry_s = 0;
     __syncthreads();
-    // every thread owns K consecutive tiles: one block-wide scan of the per-thread sums instead of one per 1024 tiles
-    // (C2: 5 rounds of 4 barriers became 2 barriers; the kernel is a single CTA, so its latency is the stage's)
-    uint32_t longest = 0, sum = 0;
-    const int K = (tiles + 1023) >> 10, t0 = threadIdx.x * K, t1 = min(t0 + K, tiles);
-#pragma unroll 4
-    for (int t = t0; t < t1; ++t) {
-        const uint32_t c = count[tc(t)];
-        sum += c;
+    // (one block scan over per-thread runs of K consecutive tiles was tried instead of this loop: 11 -> 13.7 us at C2,
+    // 18 -> 27 us at C3 under ncu; the strided second read of the counters costs more than the barriers)
+    uint32_t longest = 0;
+    for (int base = 0; base < tiles; base += 1024) {
+        const int t = base + threadIdx.x;
+        const uint32_t c = (t < tiles) ? count[tc(t)] : 0u;
         longest = max(longest, c);
-        atomicAdd(&bins[order_bin(overflow ? 0u : c)], 1u);      // the class the order loop below will find in ranges[]
-    }
-    {
-        uint32_t v = sum;
+        if (t < tiles) atomicAdd(&bins[order_bin(overflow ? 0u : c)], 1u);      // the class the order loop below will find in ranges[]
+        uint32_t v = c;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) { uint32_t n = __shfl_up_sync(0xffffffffu, v, o); if (lane >= o) v += n; }
         if (lane == 31) warp_sums[wid] = v;
@@ -58,15 +56,15 @@ tile_scan_kernel(int tiles, uint32_t* __restrict__ count, uint2* __restrict__ ra
             warp_sums[lane] = w;
         }
         __syncthreads();
-        uint32_t run = v - sum + (wid ? warp_sums[wid - 1] : 0u);
-#pragma unroll 4
-        for (int t = t0; t < t1; ++t) {
-            const uint32_t c = count[tc(t)];
-            const uint32_t incl = run + c;
-            ranges[t] = (c && !overflow) ? make_uint2(run, incl) : make_uint2(0u, 0u);
+        const uint32_t carry = carry_s;
+        const uint32_t incl = carry + v + (wid ? warp_sums[wid - 1] : 0u);
+        if (t < tiles) {
+            ranges[t] = (c && !overflow) ? make_uint2(incl - c, incl) : make_uint2(0u, 0u);
             count[tc(t)] = incl;         // from here on the scatter's cursor: absolute END of the tile's segment, counted down
-            run = incl;
         }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = incl;
+        __syncthreads();
     }
     longest = __reduce_max_sync(0xffffffffu, longest);      // the host picks the sort kernels by the longest segment
     if (lane == 0 && longest) atomicMax(max_len, longest);

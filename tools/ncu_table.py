@@ -14,7 +14,9 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 STAGE_OF = {"preprocess_kernel": "preprocess_fwd", "surfel_preprocess_kernel": "preprocess_fwd",
             "render_forward_kernel": "blend_fwd", "surfel_render_forward_kernel": "blend_fwd",
+            "render_forward_warp_kernel": "blend_fwd", "surfel_render_forward_warp_kernel": "blend_fwd",
             "render_backward_kernel": "blend_bwd", "surfel_render_backward_kernel": "blend_bwd",
+            "render_backward_warp_kernel": "blend_bwd", "surfel_render_backward_warp_kernel": "blend_bwd",
             "preprocess_backward_kernel": "preprocess_bwd", "surfel_preprocess_backward_kernel": "preprocess_bwd",
             "scatter_kernel": "binning", "tile_sort_kernel": "binning", "tile_scan_kernel": "binning",
             "tile_sort_small_kernel": "binning", "tile_radix_kernel": "binning", "tile_sort_long_kernel": "binning"}
