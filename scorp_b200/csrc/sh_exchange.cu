@@ -158,7 +158,7 @@ sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ m
                           const float* __restrict__ campos, const float* __restrict__ drgb, float* __restrict__ dsh,
                           const float* __restrict__ head, float* __restrict__ head_dst, bool surfel) {
     constexpr int M = M3 / 3;
-    __shared__ float s_sh[SH_TILE * ShTile<M3>::STRIDE];
+    __shared__ __align__(16) float s_sh[SH_TILE * ShTile<M3>::STRIDE];
     __shared__ uint8_t s_all[SH_TILE];
     const size_t row0 = (size_t)blockIdx.x * SH_TILE;
     const int nrows = min(SH_TILE, P - (int)row0);
@@ -199,6 +199,21 @@ sh_grad_from_views_kernel(int P, int D, int n_views, const float* __restrict__ m
         }
     }
     s_all[threadIdx.x] = 1;
+    if constexpr (M3 == 48) {
+        if ((reinterpret_cast<uintptr_t>(dsh) & 15) == 0) {      // whole rows as swizzled 16-byte chunks (sh.cuh, sh48_*)
+            float4* s4 = reinterpret_cast<float4*>(s_sh);
+            const int rot = threadIdx.x % 12;
+#pragma unroll
+            for (int q = 0; q < 12; ++q) {
+                int p = q + rot;
+                p -= (p >= 12) ? 12 : 0;
+                s4[threadIdx.x * 12 + p] = make_float4(acc[4 * q], acc[4 * q + 1], acc[4 * q + 2], acc[4 * q + 3]);
+            }
+            __syncthreads();
+            sh48_store(dsh, row0, nrows, s_all, s4);
+            return;                                              // (CTA-uniform)
+        }
+    }
     float* mine = s_sh + threadIdx.x * ShTile<M3>::STRIDE;
 #pragma unroll
     for (int i = 0; i < M3; ++i) mine[i] = acc[i];
