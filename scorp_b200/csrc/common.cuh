@@ -289,6 +289,13 @@ __device__ __forceinline__ void peer_head_store(float* head, int idx, const floa
     row[2] = make_float4(v[8], v[9], v[10], v[11]);
 }
 
+// vector reductions (sm_90+): one REDG.E.ADD.F32x4 / F32x2 adds 4 / 2 consecutive floats at a 16- / 8-byte aligned address
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" :: "l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_add_v2(float* p, float a, float b) {
+    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" :: "l"(p), "f"(a), "f"(b) : "memory");
+}
 // cp.async 16-byte global->shared (LDGSTS), L2-only caching: the records are read once per CTA.
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
     unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);

@@ -375,9 +375,8 @@ render_backward_warp_kernel(int W, int H, int gx,
             }
             float* const a = acc + (size_t)__shfl_sync(FULL, id_c, j) * ACC_STRIDE;
             if (__popc(act_mask) <= direct_max) {
-                if (act) {
-                    atomicAdd(a + 0, v0); atomicAdd(a + 1, v1); atomicAdd(a + 2, v2); atomicAdd(a + 3, v3); atomicAdd(a + 4, v4);
-                    atomicAdd(a + 5, v5); atomicAdd(a + 6, v6); atomicAdd(a + 7, v7); atomicAdd(a + 8, v8); atomicAdd(a + 9, v9);
+                if (act) {      // three vector reductions on the 48-byte slot instead of ten scalar ones
+                    red_add_v4(a, v0, v1, v2, v3); red_add_v4(a + 4, v4, v5, v6, v7); red_add_v2(a + 8, v8, v9);
                 }
                 continue;
             }
@@ -394,7 +393,12 @@ render_backward_warp_kernel(int W, int H, int gx,
 }
 
 // Visits with at most this many contributing pixels skip the warp reduction (tunable: GSR_DIRECT_MAX).
-// Measured on B200 at C2: blend backward 1.244 ms (0) -> 1.192 ms (8); the 18-term surfel variant only loses (default 0).
+// Round 1, scalar atomics (the four-warp kernel): C2 1.244 ms (0) -> 1.192 ms (8); the 18-term surfel variant only lost
+// (default 0). Round 2b, the one-warp kernels commit a direct visit with THREE vector reductions (red.global.add.v4.f32,
+// SASS REDG.E.ADD.F32x4: the 48-byte slot is 16-byte aligned) instead of ten scalar ones, which moves the break-even
+// far up: C2 0.647 ms (8, scalar) -> 0.626 (8) -> 0.605 (16) -> 0.590 (24) -> **0.586 (28)** -> 0.587 (31) -> 0.742 (32:
+// full-warp visits are the common case and 96 vector atomics each is too many); 2DGS, five reductions on the 80-byte
+// slot: C4 1.239 ms (0) -> 1.116 (8) -> 1.065 (16) -> **1.058 (20)** -> 1.081 (24) -> 1.299 (31).
 int blend_direct_max(int dflt) {
     static int env = -2;
     if (env == -2) { const char* e = getenv("GSR_DIRECT_MAX"); env = e ? atoi(e) : -1; if (env > 32) env = 32; }
@@ -409,7 +413,7 @@ cudaError_t launch_render_backward(int W, int H, int gx, int gy, const GeomState
     if (per_warp < 0) { const char* e = getenv("GSR_BWD_WARP"); per_warp = e ? (atoi(e) ? 1 : 0) : 1; }
     if (per_warp)
         render_backward_warp_kernel<<<gx * gy * 4, 32, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,
-                                                                img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(8),
+                                                                img.n_contrib, dL_dpix, dL_ddepth, dL_dalpha, acc, blend_direct_max(28),
                                                                 reinterpret_cast<const uint32_t*>(bin.contrib));
     else
     render_backward_kernel<<<gx * gy, BLEND_THREADS, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg, out_alpha,

@@ -505,9 +505,10 @@ surfel_render_backward_warp_kernel(int W, int H, int gx,
             }
             float* const a = acc + (size_t)__shfl_sync(FULL, id_c, j) * SACC_STRIDE;
             if (__popc(act_mask) <= direct_max) {       // splat edges: direct predicated REDs, no warp reduction
-                if (act) {
-#pragma unroll
-                    for (int i = 0; i < 18; ++i) if (val[i] != 0.0f) atomicAdd(a + i, val[i]);
+                if (act) {      // vector reductions on the 80-byte slot (16-byte aligned)
+                    red_add_v4(a, val[0], val[1], val[2], val[3]); red_add_v4(a + 4, val[4], val[5], val[6], val[7]);
+                    red_add_v4(a + 8, val[8], val[9], val[10], val[11]); red_add_v4(a + 12, val[12], val[13], val[14], val[15]);
+                    red_add_v2(a + 16, val[16], val[17]);
                 }
                 continue;
             }
@@ -532,7 +533,7 @@ cudaError_t launch_surfel_render_backward(int W, int H, int gx, int gy, const Su
     if (per_warp) {
         surfel_render_backward_warp_kernel<<<gx * gy * 8, 32, 0, st>>>(W, H, gx, img.ranges, img.tile_order, bin.point_list, g.rec, bg,
                                                                      img.n_contrib, img.median_contrib, img.final_T,
-                                                                     img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(0),
+                                                                     img.M1, img.M2, dL_dpix, dL_dothers, acc, blend_direct_max(20),
                                                                      reinterpret_cast<const uint32_t*>(bin.contrib));
         return cudaGetLastError();
     }
