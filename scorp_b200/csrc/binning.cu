@@ -5,11 +5,15 @@
 // N keys (tile<<32 | depth bits) with a stable LSD radix sort whose input is in Gaussian-index
 // order, so the result within a tile is ordered by (depth bits, Gaussian index). Here:
 //   1. preprocess already counted instances per tile (atomic histogram);
-//   2. tile_scan: exclusive scan of the counts -> ranges[tile] (empty tiles stay (0,0)), and the longest
-//      segment, read back together with N so the host launches only the sort kernels that have work;
-//   3. scatter: every instance goes straight to its tile's segment as (depth bits<<32 | index);
-//   4. tile_sort: one CTA sorts each segment on that unique 64-bit key (register-blocked bitonic in
-//      shared memory, two size classes; global-memory merge steps for segments longer than 8192).
+//   2. tile_scan: exclusive scan of the counts -> ranges[tile] (empty tiles stay (0,0)), the longest
+//      segment, read back together with N so the host launches only the sort kernels that have work, and
+//      in place of each count the absolute END of the tile's segment (the scatter's cursor);
+//   3. scatter: every instance goes straight to its tile's segment as (depth bits<<32 | index), the
+//      rectangles of a warp walked 32 tiles per round (common.cuh, warp_rects_packed);
+//   4. tile_sort: one CTA sorts each segment on that unique 64-bit key: up to 256 entries a register-blocked
+//      bitonic network in shared memory; longer ones a bucket pass over the tile's depth range with the
+//      16-bit two-pass and the 32-bit four-pass radix sorts behind it for clustered depths (three size
+//      classes); global-memory merge steps for segments longer than 8192.
 // The output lists are bit-identical to the reference's and cost ~20 B/instance of traffic
 // instead of ~150 B/instance for a 6-pass radix sort.
 #include "common.cuh"
