@@ -316,6 +316,7 @@ struct FwdArgs {
     // opacities / scales / rotations hold the stored (pre-activation) parameters
     const float* shs_rest = nullptr;
     bool raw = false;
+    bool sh_wide = false;              // SH rows 32-byte aligned: read with 32-byte loads (set by launch_preprocess)
     bool skip_histogram = false;       // batched views: launch_views_histogram counts the instances per tile instead
 };
 cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views = 1);

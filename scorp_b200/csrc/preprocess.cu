@@ -11,6 +11,7 @@
 #include "common.cuh"
 #include "sh.cuh"
 #include <cfloat>
+#include <cstdlib>
 
 namespace gsr {
 
@@ -149,7 +150,10 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
                 sh.rest = RAW ? a.shs_rest + (size_t)idx * (a.M - 1) * 3 : base + 3;
                 if constexpr (VEC) {
 #pragma unroll
-                    for (int k = 0; k < 12; ++k) sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k);
+                    for (int k = 0; k < 12; k += 2) {
+                        if (a.sh_wide) ldg256(base + 4 * k, sh.v[k], sh.v[k + 1]);       // (kernel-uniform)
+                        else { sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k); sh.v[k + 1] = __ldg(reinterpret_cast<const float4*>(base) + k + 1); }
+                    }
                 }
                 const float dx = subr(px, __ldg(a.campos)), dy = subr(py, __ldg(a.campos + 1)), dz = subr(pz, __ldg(a.campos + 2));
                 const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
@@ -182,9 +186,11 @@ preprocess_kernel(FwdArgs a, GeomState g, int32_t* __restrict__ radii) {
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);
 }
 
-cudaError_t launch_preprocess(const FwdArgs& a, const GeomState& g, int32_t* radii, cudaStream_t st, int views) {
+cudaError_t launch_preprocess(const FwdArgs& a_in, const GeomState& g, int32_t* radii, cudaStream_t st, int views) {
+    FwdArgs a = a_in;
     const dim3 blocks((a.P + 255) / 256, views);
     const bool vec = a.shs && a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+    a.sh_wide = vec && ((reinterpret_cast<uintptr_t>(a.shs) & 31) == 0) && !getenv("GSR_SH_LOAD128");
     if (a.raw)    preprocess_kernel<false, true><<<blocks, 256, 0, st>>>(a, g, radii);
     else if (vec) preprocess_kernel<true, false><<<blocks, 256, 0, st>>>(a, g, radii);
     else          preprocess_kernel<false, false><<<blocks, 256, 0, st>>>(a, g, radii);

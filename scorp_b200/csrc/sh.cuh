@@ -11,6 +11,14 @@ constexpr float kC1 = 0.4886025119029199f;
 
 struct Sh3 { float r, g, b; };
 
+// 32-byte read-only load (sm_100: LDG.E.256): a thread-per-Gaussian read of a 192-byte SH row touches one 32-byte sector
+// per lane and instruction; with 16-byte loads every sector is requested twice (the second time out of L1, if it is still
+// there) and the row costs 12 x 32 LSU wavefronts per warp, with 32-byte loads 6 x 32. Needs a 32-byte aligned address.
+__device__ __forceinline__ void ldg256(const float* p, float4& lo, float4& hi) {
+    asm("ld.global.nc.v8.f32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+        : "=f"(lo.x), "=f"(lo.y), "=f"(lo.z), "=f"(lo.w), "=f"(hi.x), "=f"(hi.y), "=f"(hi.z), "=f"(hi.w) : "l"(p));
+}
+
 // Loads coefficient k (3 floats) of one Gaussian. VEC: 48 floats were preloaded as float4s.
 template <bool VEC>
 struct ShReader {

@@ -89,6 +89,7 @@ struct SurfelFwdArgs {
     // model-space variant (gsr_surfel_forward_raw): see FwdArgs in common.cuh
     const float* shs_rest = nullptr;
     bool raw = false;
+    bool sh_wide = false;              // SH rows 32-byte aligned: read with 32-byte loads (set by launch_surfel_preprocess)
 };
 cudaError_t launch_surfel_preprocess(const SurfelFwdArgs& a, const SurfelGeom& g, int32_t* radii, cudaStream_t st);
 cudaError_t launch_surfel_render_forward(int W, int H, int gx, int gy, const SurfelGeom& g, const SurfelImage& img,

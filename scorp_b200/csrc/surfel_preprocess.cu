@@ -9,6 +9,7 @@
 // spelled out) and left to nvcc's default contraction, the same compiler decisions the reference
 // build gets; the depth key uses the explicit sequence proven bit-exact on the 3DGS path.
 #include "surfel.cuh"
+#include <cstdlib>
 #include "sh.cuh"
 #include <cfloat>
 
@@ -180,7 +181,10 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
                 sh.rest = RAW ? a.shs_rest + (size_t)idx * (a.M - 1) * 3 : base + 3;
                 if constexpr (VEC) {
 #pragma unroll
-                    for (int k = 0; k < 12; ++k) sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k);
+                    for (int k = 0; k < 12; k += 2) {
+                        if (a.sh_wide) ldg256(base + 4 * k, sh.v[k], sh.v[k + 1]);       // (kernel-uniform)
+                        else { sh.v[k] = __ldg(reinterpret_cast<const float4*>(base) + k); sh.v[k + 1] = __ldg(reinterpret_cast<const float4*>(base) + k + 1); }
+                    }
                 }
                 const float dx = subr(px, __ldg(a.campos)), dy = subr(py, __ldg(a.campos + 1)), dz = subr(pz, __ldg(a.campos + 2));
                 const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
@@ -209,9 +213,11 @@ surfel_preprocess_kernel(SurfelFwdArgs a, SurfelGeom g, int32_t* __restrict__ ra
     if ((threadIdx.x & 31) == 0 && wsum) atomicAdd(g.counters, wsum);
 }
 
-cudaError_t launch_surfel_preprocess(const SurfelFwdArgs& a, const SurfelGeom& g, int32_t* radii, cudaStream_t st) {
+cudaError_t launch_surfel_preprocess(const SurfelFwdArgs& a_in, const SurfelGeom& g, int32_t* radii, cudaStream_t st) {
+    SurfelFwdArgs a = a_in;
     const int blocks = (a.P + 255) / 256;
     const bool vec = a.shs && a.M == 16 && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+    a.sh_wide = vec && ((reinterpret_cast<uintptr_t>(a.shs) & 31) == 0) && !getenv("GSR_SH_LOAD128");
     if (a.raw)    surfel_preprocess_kernel<false, true><<<blocks, 256, 0, st>>>(a, g, radii);
     else if (vec) surfel_preprocess_kernel<true, false><<<blocks, 256, 0, st>>>(a, g, radii);
     else          surfel_preprocess_kernel<false, false><<<blocks, 256, 0, st>>>(a, g, radii);
