@@ -39,6 +39,8 @@ def main():
             base = op.split(".")[0]
             if base in ("REDG", "RED", "REDUX"):
                 c["RED"] += 1
+                if "F32x4" in op or "F32x2" in op:      # red.global.add.v4/.v2.f32 (backward blends, direct visits)
+                    c["REDvec"] += 1
             elif base in ("ATOMG", "ATOMS", "ATOM"):
                 c["ATOM"] += 1
             elif base in ("HMMA", "IMMA", "DMMA", "QMMA", "OMMA") or base.startswith("UTC") or "MMA" in base:
@@ -47,6 +49,8 @@ def main():
                 c["UTMA"] += 1
             elif base in COLS:
                 c[base] += 1
+            if base == "LDG" and ".256" in op:
+                c["LDG256"] += 1
             if base == "LDGMC" or "MULTIMEM" in op:     # multimem.ld_reduce -> LDGMC.E.ADD.F32 (multimem.st is a plain STG
                 c["MULTIMEM"] += 1                      # .STRONG.SYS to the multicast address)
     log = (ROOT / "scorp_b200" / "build.log").read_text() if (ROOT / "scorp_b200" / "build.log").exists() else ""
@@ -67,6 +71,7 @@ def main():
         tot.update(c)
     print(f"\nAll kernels: {len(kernels)} functions, {tot['total']} instructions; LDGSTS {tot['LDGSTS']}, FFMA2+FMUL2+FADD2 "
           f"{tot['FFMA2'] + tot['FMUL2'] + tot['FADD2']}, MATCH {tot['MATCH']}, multimem.ld_reduce (LDGMC) {tot['MULTIMEM']}, "
+          f"vector REDG (F32x4 / F32x2) {tot['REDvec']}, 32-byte LDG (LDG.E.ENL2.256) {tot['LDG256']}, "
           f"TMA {tot['UTMA']}, tensor-core MMA {tot['MMA']}.")
 
 
