@@ -31,7 +31,7 @@ def main():
         m = re.match(r"\s*Function : (\S+)", line)
         if m:
             cur = m.group(1); kernels[cur] = collections.Counter(); continue
-        m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
+        m = re.match(r"\s*/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Za-z0-9_.]+)", line)
         if m and cur:
             op = m.group(1)
             c = kernels[cur]
