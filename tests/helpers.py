@@ -106,6 +106,20 @@ def close(a, b, rtol=1e-4, atol_scale=1e-6):
     return (not bool(bad.any())), float((err / tol.clamp_min(1e-300)).max()) if b.numel() else 0.0
 
 
+def close_to_runs(a, runs, rtol=1e-4, atol_scale=1e-6):
+    """`a` against SEVERAL runs of the same computation whose results differ only by the order of float atomics: within
+    rtol of their mean, atol = atol_scale * max|mean| + 2 x their own largest run-to-run difference (what
+    test_gpu_dgr_parity.py:_grad_ok does with the reference runs). Returns (ok, max_violation_ratio)."""
+    st = torch.stack([r.double().flatten() for r in runs])
+    mean = st.mean(0)
+    if mean.numel() == 0:
+        return True, 0.0
+    spread = float((st.max(0).values - st.min(0).values).max()) if len(runs) > 1 else 0.0
+    tol = atol_scale * float(mean.abs().max()) + 2.0 * spread + rtol * mean.abs()
+    err = (a.double().flatten() - mean).abs()
+    return (not bool((err > tol).any())), float((err / tol.clamp_min(1e-300)).max())
+
+
 def make(name, device="cuda", **kw):
     return synth.make_scene(name, **kw).to(device)
 

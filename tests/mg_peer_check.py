@@ -70,15 +70,19 @@ def main():
         gcol = torch.Generator().manual_seed(11)
         colors = torch.rand(sc.P, 3, generator=gcol).cuda()
         fo_c = fwd_f(sc, cam, colors_precomp=colors)
-        plain = bwd_f(sc, cam, fo_c, grads)
-        want = {k: plain[k].clone() for k in ("means3D", "opacity", "scales", "rotations")}
-        for k in want:
-            dist.all_reduce(want[k])
+        want_runs = []
+        for _ in range(4):
+            plain = bwd_f(sc, cam, fo_c, grads)
+            w = {k: plain[k].clone() for k in ("means3D", "opacity", "scales", "rotations")}
+            for k in w:
+                dist.all_reduce(w[k])
+            want_runs.append(w)
+        want = want_runs[0]
         mv.install_factored_exchange(enable=True, peer=True)
         try:
             out = bwd_f(sc, cam, fo_c, grads)
             for k in want:
-                good, worst = h.close(out[k], want[k], rtol=1e-3, atol_scale=1e-5)     # two backward runs: atomics noise
+                good, worst = h.close_to_runs(out[k], [w[k] for w in want_runs])       # rtol 1e-4 + the runs' own spread
                 if not good:
                     ok = False
                     print(f"rank {rank} surfel={surfel} precomputed colours {k}: worst ratio {worst}", flush=True)

@@ -50,12 +50,13 @@ def test_debug_and_prefiltered_do_not_change_results(surfel):
     mod = _mods(surfel)
     sc = h.make("C4" if surfel else "C2", P=30_000, W=300, H=200, random_bg=True); cam = sc.cameras[0]
     plain, g_plain = _render(mod, sc, cam, False, False)
+    g_runs = [g_plain] + [_render(mod, sc, cam, False, False)[1] for _ in range(3)]      # run-to-run spread of the atomics
     for prefiltered, debug in ((True, False), (False, True), (True, True)):
         outs, grads = _render(mod, sc, cam, prefiltered, debug)
         for a, b in zip(outs, plain):
             assert torch.equal(a, b), (prefiltered, debug)
-        for a, b in zip(grads, g_plain):
-            assert h.close(a, b, rtol=1e-3, atol_scale=1e-5)[0], (prefiltered, debug)
+        for i, a in enumerate(grads):
+            assert h.close_to_runs(a, [g[i] for g in g_runs])[0], (prefiltered, debug)
     from oracle import ref_cuda
     if ref_cuda.available("dsr" if surfel else "dgr"):
         fr = (h.ref_surfel_forward if surfel else h.ref_forward)(sc, cam)

@@ -18,6 +18,7 @@ def test_single_rank_factored_equals_plain(surfel, deg):
     grads = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 5, channels=(3, 7) if surfel else (3, 1, 1))]
     fo = fwd_f(sc, cam)
     plain = bwd_f(sc, cam, fo, grads)
+    plain_runs = [plain] + [bwd_f(sc, cam, fo, grads) for _ in range(3)]
     mv.install_factored_exchange(enable=True)
     try:
         fact = bwd_f(sc, cam, fo, grads)
@@ -25,7 +26,7 @@ def test_single_rank_factored_equals_plain(surfel, deg):
         mv.install_factored_exchange(enable=False)
     assert fact["sh"].shape == plain["sh"].shape
     for k in plain:                                         # two backward runs: equal up to the order of float atomics
-        assert h.close(fact[k], plain[k], rtol=1e-3, atol_scale=1e-5)[0], k
+        assert h.close_to_runs(fact[k], [r[k] for r in plain_runs])[0], k
     assert int((plain["sh"] != 0).sum()) > 0
     # the rebuild itself, fed with the colour gradient of the SAME backward run: the products basis_k * dL_dRGB the
     # backward wrote (rounding of the basis may differ by contraction, hence 1e-5 instead of bit equality)

@@ -66,9 +66,10 @@ def test_nosync_forward_is_bit_identical_to_the_stock_forward(name, surfel, cfg,
     assert torch.equal(inx["n_contrib"], isx["n_contrib"])
     # backward on the no-sync buffers (R = capacity) against the backward on the stock buffers: atomics noise only
     grads = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 3, channels=(3, 7) if surfel else (3, 1, 1))]
-    gs, gn = bwd_f(sc, cam, fs, grads), bwd_f(sc, cam, fn, grads)
-    for k in gs:
-        assert h.close(gn[k], gs[k], rtol=1e-3, atol_scale=1e-5)[0], k
+    gs_runs = [bwd_f(sc, cam, fs, grads) for _ in range(4)]
+    gn = bwd_f(sc, cam, fn, grads)
+    for k in gn:
+        assert h.close_to_runs(gn[k], [g[k] for g in gs_runs])[0], k
 
 
 @pytest.mark.parametrize("surfel", [False, True], ids=["3dgs", "2dgs"])
@@ -124,11 +125,16 @@ def test_public_api_under_capacity_enable(surfel):
         for p in params:
             p.grad = None
         capacity.disable()
-        imgs = [o for o in _public(mod, sc, sc.cameras[1], params, torch.zeros_like(params[0], requires_grad=True))
-                if o.dtype.is_floating_point]
-        torch.autograd.backward(imgs, [torch.ones_like(o) / o.numel() for o in imgs])
-        for a, p in zip(g_nosync, params):
-            assert h.close(a, p.grad, rtol=1e-3, atol_scale=1e-5)[0]
+        eager = []                      # the stock path, four times: float atomics make every run a little different
+        for _ in range(4):
+            for p in params:
+                p.grad = None
+            imgs = [o for o in _public(mod, sc, sc.cameras[1], params, torch.zeros_like(params[0], requires_grad=True))
+                    if o.dtype.is_floating_point]
+            torch.autograd.backward(imgs, [torch.ones_like(o) / o.numel() for o in imgs])
+            eager.append([p.grad.clone() for p in params])
+        for i, a in enumerate(g_nosync):
+            assert h.close_to_runs(a, [e[i] for e in eager])[0]
         # a view with more instances than the high-water mark allows: flagged, mark raised, the retry succeeds
         capacity.enable(margin=1.0, slack=0)
         key = ("2dgs" if surfel else "3dgs", sc.P, sc.cameras[0].W, sc.cameras[0].H)
@@ -195,14 +201,17 @@ def test_forward_and_backward_captured_in_a_cuda_graph():
         got = [o.clone() for o in g_outs] + [p.grad.clone() for p in params]
         # eager, stock path, same values
         capacity.disable()
-        for p in params:
-            p.grad = None
-        e_outs = step()
-        torch.cuda.synchronize()
+        eager = []
+        for _ in range(4):
+            for p in params:
+                p.grad = None
+            e_outs = step()
+            torch.cuda.synchronize()
+            eager.append([p.grad.clone() for p in params])
         for a, b in zip(got[:4], e_outs):
             assert torch.equal(a, b)
-        for a, p in zip(got[4:], params):
-            assert h.close(a, p.grad, rtol=1e-3, atol_scale=1e-5)[0]
+        for i, a in enumerate(got[4:]):
+            assert h.close_to_runs(a, [e[i] for e in eager])[0]
         assert float(got[4].abs().max()) > 0
     finally:
         capacity.disable(); capacity.reset(); capacity.forget_captured()
