@@ -33,19 +33,19 @@ def test_render_like_gs3dgs_and_autograd_matches_C_level():
     loss = (color * gc).sum() + (depth * gd).sum() + (alpha * ga).sum()
     loss.backward(retain_graph=True)
     fo = h.ours_forward(sc, cam)
-    go = h.ours_backward(sc, cam, fo, [gc, gd, ga])
+    runs = [h.ours_backward(sc, cam, fo, [gc, gd, ga]) for _ in range(4)]
     assert torch.equal(color.detach(), fo["color"]) and torch.equal(radii, fo["radii"])
-    # two separate backward runs: equal up to the order of float atomics
-    def same(a, b):
-        return torch.allclose(a, b, rtol=1e-3, atol=1e-5 * float(b.abs().max()))
+    # separate backward runs: equal up to the order of float atomics, i.e. within the spread of the four C-level runs
+    def same(a, k):
+        return h.close_to_runs(a, [r[k] for r in runs], rtol=1e-3, atol_scale=1e-5)[0]
     for p, k in zip(params, ("means3D", "sh", "opacity", "scales", "rotations")):
-        assert same(p.grad, go[k].view_as(p.grad)), k
-    assert same(screenspace.grad, go["means2D"])
+        assert same(p.grad, k), k
+    assert same(screenspace.grad, "means2D")
     assert float(screenspace.grad[:, 2].abs().max()) == 0.0
-    # backward is re-entrant: a second pass over the same graph doubles the accumulated grads
+    # backward is re-entrant: a second pass over the same graph ADDS its gradients to the accumulated ones
     first = means3D.grad.clone()
     loss.backward()
-    assert same(means3D.grad, 2 * first)
+    assert same(means3D.grad - first, "means3D")
 
 
 def test_override_color_gradient_channels_equal():

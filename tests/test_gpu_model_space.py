@@ -85,18 +85,28 @@ def test_forward_and_backward_match_torch_staging(name, kw, smod):
     assert torch.equal(ca, cb) and torch.equal(da, db) and torch.equal(aa, ab), exact
 
     gc, gd, ga = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 33)]
-    for (c, d, a) in ((ca, da, aa), (cb, db, ab)):
-        ((c * gc).sum() + (d * gd).sum() + (a * ga).sum()).backward()
+    ((cb * gc).sum() + (db * gd).sum() + (ab * ga).sum()).backward()
+    # the stock side four times: two backward runs differ by the order of float atomics in the blend backward, and the
+    # spread of these runs widens the tolerance (helpers.close_to_runs)
+    loss_a = (ca * gc).sum() + (da * gd).sum() + (aa * ga).sum()
+    runs_a, runs_m2a = [], []
+    for _ in range(4):
+        for t in sa.values():
+            t.grad = None
+        m2a.grad = None
+        loss_a.backward(retain_graph=True)
+        runs_a.append({k: (sa[k].grad.clone() if sa[k].grad is not None else None) for k in sa})
+        runs_m2a.append(m2a.grad.clone())
 
-    def same(x, y):      # two backward runs differ by the order of float atomics in the blend backward
-        return torch.allclose(x, y, rtol=1e-3, atol=1e-5 * float(y.abs().max()) + 1e-30)
+    def same(x, ys):
+        return h.close_to_runs(x, ys, rtol=1e-3, atol_scale=1e-5)[0]
     for k in sa:
         if sa[k].numel() == 0:
             assert sb[k].grad is None or sb[k].grad.numel() == 0
             continue
         assert sb[k].grad is not None and sb[k].grad.shape == sa[k].shape, k
-        assert same(sb[k].grad, sa[k].grad), (k, float((sb[k].grad - sa[k].grad).abs().max()), float(sa[k].grad.abs().max()))
-    assert same(m2b.grad, m2a.grad)
+        assert same(sb[k].grad, [r[k] for r in runs_a]), (k, float((sb[k].grad - sa[k].grad).abs().max()), float(sa[k].grad.abs().max()))
+    assert same(m2b.grad, runs_m2a)
     # invisible Gaussians get exact zeros in every gradient row (every row is written, none left uninitialised)
     inv = rb == 0
     for k in sb:
@@ -161,16 +171,24 @@ def test_surfel_model_space_matches_torch_staging(kw, smod):
     assert torch.equal(ra, rb), f"{int((ra != rb).sum())} radii differ"
     assert torch.equal(ca, cb) and torch.equal(oa, ob)
     gc, go = [g.cuda() for g in synth.upstream_grads(cam.W, cam.H, 17, channels=(3, 7))]
-    for c, o in ((ca, oa), (cb, ob)):
-        ((c * gc).sum() + (o * go).sum()).backward()
+    ((cb * gc).sum() + (ob * go).sum()).backward()
+    loss_a = (ca * gc).sum() + (oa * go).sum()
+    runs_a, runs_m2a = [], []          # the stock side four times: the spread of the float atomics widens the tolerance
+    for _ in range(4):
+        for t in sa.values():
+            t.grad = None
+        m2a.grad = None
+        loss_a.backward(retain_graph=True)
+        runs_a.append({k: (sa[k].grad.clone() if sa[k].grad is not None else None) for k in sa})
+        runs_m2a.append(m2a.grad.clone())
 
-    def same(x, y):      # two backward runs differ by the order of float atomics in the blend backward
-        return torch.allclose(x, y, rtol=1e-3, atol=1e-5 * float(y.abs().max()) + 1e-30)
+    def same(x, ys):
+        return h.close_to_runs(x, ys, rtol=1e-3, atol_scale=1e-5)[0]
     for k in sa:
         if sa[k].numel():
-            assert sb[k].grad is not None and same(sb[k].grad, sa[k].grad), \
+            assert sb[k].grad is not None and same(sb[k].grad, [r[k] for r in runs_a]), \
                 (k, float((sb[k].grad - sa[k].grad).abs().max()), float(sa[k].grad.abs().max()))
-    assert same(m2b.grad, m2a.grad)
+    assert same(m2b.grad, runs_m2a)
     inv = rb == 0
     for k in sb:
         if sb[k].numel() and inv.any():

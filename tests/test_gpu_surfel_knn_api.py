@@ -36,18 +36,18 @@ def test_render_like_gs2dgs_and_autograd_matches_C_level():
     loss = (color * gc).sum() + (allmap * go7).sum()
     loss.backward(retain_graph=True)
     fo = h.ours_surfel_forward(sc, cam)
-    go = h.ours_surfel_backward(sc, cam, fo, [gc, go7])
+    runs = [h.ours_surfel_backward(sc, cam, fo, [gc, go7]) for _ in range(4)]
     assert torch.equal(color.detach(), fo["color"]) and torch.equal(allmap.detach(), fo["others"]) and torch.equal(radii, fo["radii"])
 
-    def same(a, b):
-        return torch.allclose(a, b, rtol=1e-3, atol=1e-5 * float(b.abs().max()))
+    def same(a, k):      # separate backward runs: within the spread of the four C-level runs (order of float atomics)
+        return h.close_to_runs(a, [r[k] for r in runs], rtol=1e-3, atol_scale=1e-5)[0]
     for p, k in zip(params, ("means3D", "sh", "opacity", "scales", "rotations")):
-        assert same(p.grad, go[k].view_as(p.grad)), k
-    assert same(screenspace.grad, go["means2D"])
+        assert same(p.grad, k), k
+    assert same(screenspace.grad, "means2D")
     assert float(screenspace.grad[:, 2].abs().max()) == 0.0
     first = means3D.grad.clone()
     loss.backward()
-    assert same(means3D.grad, 2 * first)
+    assert same(means3D.grad - first, "means3D")
 
 
 def test_surfel_validation_empty_and_dropin_names():
